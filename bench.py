@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the optical-flow training hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W [--workload train|loss] [--impl reference]
+
+Workloads (BASELINE.json configs):
+  train  configs[2]/[3]: full unsupervised train step (encoder/decoder fwd+bwd, fused
+         warp+L1 pyramid loss, Adam), batch 8 per GPU at 384x1280 (KITTI shape), synthetic
+         pairs, random-init weights.  metric = image-pairs/s (whole job).
+  loss   configs[1]: fused warp + photometric pyramid loss kernel only (fwd + d_flow),
+         batch 8 at 384x1280.  metric = image-pairs/s through the kernel; roofline = HBM.
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for the definitions.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H_FULL, W_FULL, B_PER_GPU = 384, 1280, 8
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+# --------------------------------------------------------------- algorithmic work --
+def loss_algorithmic_bytes(B, H, W, ns=4):
+    """read image pair once + read flows + write d_flows + loss scalar."""
+    px = sum(B * int(H / 2 ** (s + 1)) * int(W / 2 ** (s + 1)) for s in range(ns))
+    return 4 * (6 * B * H * W + 2 * px + 2 * px) + 4
+
+
+def conv_layer_table(B, H, W):
+    """(name, N, Ho, Wo, Cin, k, Cout, stride) of the 39 convs."""
+    L = [("conv1", 2 * B, H // 2, W // 2, 3, 7, 64, 2)]
+    cin, h, w = 64, H // 4, W // 4
+    for layer_idx, down in ((2, False), (3, True), (4, True)):
+        for blk in (1, 2):
+            ds = down and blk == 1
+            cout = 2 * cin if ds else cin
+            if ds:
+                h, w = h // 2, w // 2
+                L.append(("layer%d_block_%d_shortcut" % (layer_idx, blk), 2 * B, h, w, cin, 1, cout, 2))
+            L.append(("layer%d_block_%d_conv1" % (layer_idx, blk), 2 * B, h, w, cin, 3, cout, 2 if ds else 1))
+            L.append(("layer%d_block_%d_conv2" % (layer_idx, blk), 2 * B, h, w, cout, 3, cout, 1))
+            cin = cout
+    feat = (256, 128, 64, 64)
+    for lvl in range(4):
+        h, w = H // (16 >> lvl), W // (16 >> lvl)
+        c = feat[lvl] + 49 + (2 if lvl else 0)
+        for ci, cout in enumerate((128, 128, 96, 64, 32, 2)):
+            L.append(("flow%d_conv%d" % (lvl, ci + 1), B, h, w, c, 3, cout, 1))
+            c = cout
+    return L
+
+
+def conv_flops(B, H, W, tc_only=False):
+    """Algorithmic conv FLOPs of one train step: fprop + dgrad + wgrad (no dgrad for conv1)."""
+    tot = 0.0
+    for name, n, ho, wo, cin, k, cout, s in conv_layer_table(B, H, W):
+        if tc_only and (cin < 32 or cout < 32):
+            continue
+        f = 2.0 * n * ho * wo * cin * cout * k * k
+        tot += f * (2 if name == "conv1" else 3)
+    return tot
+
+
+# ------------------------------------------------------------------------ clocks --
+class ClockSampler:
+    """nvidia-smi sampled DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU baselines --
+def cpu_loss_baseline(B, budget_s=15.0):
+    """Oracle port (torch-CPU, all host threads) of the warp+loss fwd+bwd on a bounded
+    sample: the same 384x1280 shape, as many batch-1 passes as fit the budget."""
+    import numpy as np
+    import torch
+    from oracle import ref_torch as T
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    imgs = torch.tensor(T.synthetic_pairs(1, H_FULL, W_FULL, seed=1))
+    rng = np.random.default_rng(0)
+    flows = [torch.tensor((rng.standard_normal((1, H_FULL >> (s + 1), W_FULL >> (s + 1), 2)) * (4.0 / 2 ** s)).astype(np.float32),
+                          requires_grad=True) for s in range(4)]
+
+    def one():
+        for f in flows:
+            f.grad = None
+        T.loss_layer(imgs, flows).backward()
+
+    one()
+    t0, n = time.time(), 0
+    while True:
+        one()
+        n += 1
+        if time.time() - t0 > budget_s or n >= 50:
+            break
+    dt = (time.time() - t0) / n
+    return {"value": 1.0 / dt, "unit": "image-pairs/s", "cores": cores, "kind": "port",
+            "sample": "oracle/ref_torch.loss_layer fwd+bwd, batch 1 at %dx%d, %d passes" % (H_FULL, W_FULL, n)}
+
+
+def cpu_train_baseline(budget_s=25.0, height=128, width=416):
+    """Oracle port (torch-CPU fp32 autograd, all host threads) of the full train step
+    (forward + loss + backward; Adam excluded: negligible) on a bounded sample: batch 1 at
+    128x416 (BASELINE configs[0], the reference's CPU-runnable case); pairs/s scale ~1/pixels."""
+    import torch
+    from oracle import ref_torch as T
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    params, stats = T.init_params(seed=42)
+    net = T.FlowNetRef(params, stats)
+    imgs = torch.tensor(T.synthetic_pairs(1, height, width, seed=1))
+    net.loss_and_grads(imgs)
+    t0, n = time.time(), 0
+    while True:
+        net.loss_and_grads(imgs)
+        n += 1
+        if time.time() - t0 > budget_s or n >= 20:
+            break
+    dt = (time.time() - t0) / n
+    return {"value": 1.0 / dt, "unit": "image-pairs/s", "cores": cores, "kind": "port",
+            "sample": "oracle/ref_torch.FlowNetRef fwd+loss+bwd, batch 1 at %dx%d (configs[0]), %d steps" % (height, width, n)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  TensorFlow is not
+    installable here (no network), so this is the oracle port (torch-CPU, all host threads)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(args.steps, 1)
+    if args.workload == "loss":
+        base = cpu_loss_baseline(B_PER_GPU, budget_s=min(60.0, 4.0 * steps))
+        cfg = {"workload": "fused warp+L1 pyramid loss fwd+bwd, 384x1280 (configs[1]); CPU sample: batch 1"}
+    else:
+        base = cpu_train_baseline(budget_s=min(90.0, 6.0 * steps))
+        cfg = {"workload": "full train step fwd+bwd (configs[2]); CPU sample: batch 1 at 128x416 (configs[0])"}
+    line = {"impl": "reference", "metric": "image-pairs/s", "value": base["value"], "unit": "image-pairs/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / base["value"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg, "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "image-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# -------------------------------------------------------------------- GPU arms ----
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="train", choices=["train", "loss"])
+    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--batch", type=int, default=B_PER_GPU)
+    ap.add_argument("--height", type=int, default=H_FULL)
+    ap.add_argument("--width", type=int, default=W_FULL)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from optical_flow_b200 import build
+    if rank == 0:
+        build.build_library()
+    if world > 1:
+        dist.barrier()
+    if args.workload == "loss":
+        line = bench_loss(args, dev, world, rank)
+    else:
+        line = bench_train(args, dev, world, rank)
+    if rank == 0:
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_loss_baseline(args.batch) if args.workload == "loss" else cpu_train_baseline()
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _timed(torch, dist, world, fn_steps, steps):
+    """barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn_steps(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def bench_loss(args, dev, world, rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from optical_flow_b200 import functional as F
+    from optical_flow_b200.train import synthetic_batch
+    B, H, W = args.batch, args.height, args.width
+    peaks = measured_peaks()
+    nsets = 4   # 4 x 115 MB of inputs/outputs rotate through the 126 MB L2
+    sets = []
+    for k in range(nsets):
+        imgs = synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev)
+        g = torch.Generator(device="cpu").manual_seed(77 + k)
+        flows = [(torch.randn((B, H >> (s + 1), W >> (s + 1), 2), generator=g) * (4.0 / 2 ** s)).to(dev) for s in range(4)]
+        d_flows = [torch.empty_like(f) for f in flows]
+        sets.append((imgs, flows, d_flows, torch.empty(1, device=dev)))
+
+    def run(n):
+        for i in range(n):
+            imgs, flows, d_flows, lo = sets[i % nsets]
+            F.loss_l1_pyramid(imgs, flows, need_grads=True, loss_out=lo, d_flows=d_flows)
+
+    run(max(args.warmup, 3))
+    clocks = ClockSampler(dev.index or 0)
+    clocks.start()
+    ms = _timed(torch, dist, world, run, args.steps)
+    ck = clocks.stop()
+    per = ms / args.steps
+    value = world * B / (per * 1e-3)
+    alg = loss_algorithmic_bytes(B, H, W)
+    ach = alg / (per * 1e-3) / 1e9
+    # end to end: host (pinned) images + flows -> device, kernel, loss + d_flows back to host
+    h_imgs = torch.empty((B, H, W, 6), dtype=torch.float32).pin_memory()
+    h_imgs.copy_(sets[0][0].cpu())
+    h_flows = [f.cpu().pin_memory() for f in sets[0][1]]
+    h_dflows = [torch.empty_like(f).pin_memory() for f in h_flows]
+    h_loss = torch.empty(1).pin_memory()
+    d_imgs, d_fl, d_dfl, d_lo = sets[1]
+
+    def run_e2e(n):
+        for _ in range(n):
+            d_imgs.copy_(h_imgs, non_blocking=True)
+            for a, b in zip(d_fl, h_flows):
+                a.copy_(b, non_blocking=True)
+            F.loss_l1_pyramid(d_imgs, d_fl, need_grads=True, loss_out=d_lo, d_flows=d_dfl)
+            h_loss.copy_(d_lo, non_blocking=True)
+            for a, b in zip(h_dflows, d_dfl):
+                a.copy_(b, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    run_e2e(2)
+    ms_e = _timed(torch, dist, world, run_e2e, args.steps)
+    fl_bytes = sum(f.numel() * 4 for f in h_flows)
+    e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
+           "h2d_bytes_per_step": h_imgs.numel() * 4 + fl_bytes, "d2h_bytes_per_step": fl_bytes + 4}
+    return {"metric": "image-pairs/s through fused warp+loss (fwd + d_flow), 384x1280", "value": value,
+            "unit": "image-pairs/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": per, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "fused warp + L1 pyramid loss fwd+bwd, batch %d/GPU at %dx%d (configs[1])" % (B, H, W),
+                       "l2": "4 rotating input/output sets (4 x %.0f MB > 126 MB L2)" % (alg / 1e6)},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": ach / peaks["hbm"], "traffic": None, "kernel": "fused_loss_kernel<0>",
+                         "algorithmic_bytes": alg, "peak_source": peaks["src"]},
+            "e2e": e2e, "gpu_launches": args.steps, "clocks": ck}
+
+
+def bench_train(args, dev, world, rank):
+    import torch
+    import torch.distributed as dist
+    from optical_flow_b200 import _lib as L
+    from optical_flow_b200.train import Trainer, synthetic_batch
+    B, H, W = args.batch, args.height, args.width
+    peaks = measured_peaks()
+    comm = None
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            import ctypes
+            buf = (ctypes.c_char * 128)()
+            L.check(L.load().of_comm_unique_id(buf), "of_comm_unique_id")
+            uid = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        uid = uid.to(dev)
+        dist.broadcast(uid, 0)
+        import ctypes
+        raw = bytes(uid.cpu().numpy().tobytes())
+        out = ctypes.c_void_p()
+        L.check(L.load().of_comm_init(raw, world, rank, ctypes.byref(out)), "of_comm_init")
+        comm = out
+    tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm, world_size=world)
+    nsets = 2
+    batches = [synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev) for k in range(nsets)]
+    loss_acc = torch.zeros(1, device=dev)
+
+    def run(n):
+        for i in range(n):
+            loss, _ = tr.train_step(batches[i % nsets], i)
+
+    run(max(args.warmup, 3))
+    launches_before = L.load().of_launch_count()
+    clocks = ClockSampler(dev.index or 0)
+    clocks.start()
+    ms = _timed(torch, dist, world, run, args.steps)
+    ck = clocks.stop()
+    launches = L.load().of_launch_count() - launches_before
+    per = ms / args.steps
+    value = world * B / (per * 1e-3)
+    # end to end through the public API with HOST batches: pinned host -> device copy of the
+    # step's images and a device -> host read of the loss, every step
+    h_batches = [b.cpu().pin_memory() for b in batches]
+    h_loss = torch.empty(1).pin_memory()
+    d_in = torch.empty_like(batches[0])
+
+    def run_e2e(n):
+        for i in range(n):
+            d_in.copy_(h_batches[i % nsets], non_blocking=True)
+            loss, _ = tr.train_step(d_in, i)
+            h_loss.copy_(loss.reshape(1), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    run_e2e(2)
+    ms_e = _timed(torch, dist, world, run_e2e, args.steps)
+    e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
+           "h2d_bytes_per_step": d_in.numel() * 4, "d2h_bytes_per_step": 4}
+    flops = conv_flops(B, H, W)
+    tc_flops = conv_flops(B, H, W, tc_only=True)
+    prof = tr.flow_net.backend.profile_summary() if hasattr(tr.flow_net.backend, "profile_summary") else None
+    if args.conv_mode == "bf16":
+        peak = peaks["tf_sust"]
+        if prof and prof.get("tc_ms"):
+            ach = tc_flops / (prof["tc_ms"] * 1e-3) / 1e12
+        else:
+            ach = flops / (per * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                "traffic": None, "kernel": "conv_tc (tcgen05 implicit GEMM, all launches of one step)",
+                "algorithmic_flops": tc_flops, "peak_source": peaks["src"] + " (sustained bf16)", "profile": prof}
+    else:
+        ach = flops / (per * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": peaks["tf_sust"], "unit": "TFLOP/s",
+                "frac": ach / peaks["tf_sust"], "traffic": None,
+                "kernel": "gemm_simt_kernel (fp32 SIMT parity mode, whole step)", "algorithmic_flops": flops,
+                "peak_source": peaks["src"]}
+    return {"metric": "image-pairs/s per train step at %dx%d" % (H, W), "value": value, "unit": "image-pairs/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": per,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.conv_mode == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": "full train step fwd+bwd+Adam, ResNet encoder + cost-volume decoder, batch %d/GPU at %dx%d (configs[2])" % (B, H, W),
+                       "global_batch": B * world, "parallelism": "dp%d" % world, "conv_mode": args.conv_mode,
+                       "l2": "activations per step (GBs) far exceed the 126 MB L2; 2 rotating input batches"},
+            "roofline": roof, "e2e": e2e, "gpu_launches": launches if launches else None, "clocks": ck}
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,190 @@
+/*
+ * oflow_b200.h - C ABI of liboflow_b200.so: the B200 (sm_100a) hot path of the
+ * unsupervised optical-flow training step of xianlopez/optical_flow.
+ *
+ * Boundary rules:
+ *   - every pointer is a DEVICE pointer unless the name says host; the caller
+ *     owns all memory (inputs, outputs, gradients, workspaces);
+ *   - tensors are contiguous NHWC; "dtype" selects the storage type of
+ *     activations (OF_F32 = reference layout, OF_BF16 = conv fast path);
+ *     gradients produced by the HBM-bound ops are always float32;
+ *   - functions are asynchronous on `stream` (a cudaStream_t passed as void*),
+ *     re-entrant, and allocate nothing;
+ *   - return value: 0 = ok, < 0 = argument/shape error (the reference's
+ *     trace-time asserts), > 0 = cudaError_t.  of_last_error() describes it.
+ *
+ * Each entry point cites the reference lines it replaces (paths relative to
+ * the reference tree).
+ */
+#ifndef OFLOW_B200_H
+#define OFLOW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { OF_F32 = 0, OF_BF16 = 1 };
+/* OF_WARP_REF_IJ reproduces model.py:65-71 literally (sampling point =
+ * [row, col] + flow, read as (x, y) by the sampler: SURVEY F4);
+ * OF_WARP_XY is the conventional order (x = col + flow[0], y = row + flow[1]). */
+enum { OF_WARP_REF_IJ = 0, OF_WARP_XY = 1 };
+/* conv epilogue activations */
+enum { OF_ACT_NONE = 0, OF_ACT_RELU = 1, OF_ACT_LEAKY = 2 };
+
+#define OF_OK 0
+#define OF_ERR_ARG (-1)
+#define OF_ERR_SHAPE (-2)
+#define OF_ERR_UNSUPPORTED (-3)
+#define OF_ERR_STATE (-4)
+
+int of_version(void);
+const char* of_last_error(void);
+/* number of CUDA kernels this library has launched in this process (bench evidence) */
+unsigned long long of_launch_count(void);
+
+/* ---- sampler ------------------------------------------------------------
+ * transformations.py:85-129 bilinear_interpolation (+ :70-81 gather).
+ * in (B,H,W,C) dtype; pts (B,H,W,2) f32 absolute (x,y); out (B,H,W,C) dtype.
+ * idx (nullable): int32 (B,H,W,4) = clipped x0,x1,y0,y1 (bit-exact check). */
+int of_bilinear_sample_fwd(const void* in, const float* pts, void* out, int32_t* idx,
+                           int B, int H, int W, int C, int dtype, void* stream);
+/* TF autodiff of the above.  d_out f32 (B,H,W,C).  d_in f32 (B,H,W,C),
+ * nullable, zeroed by the callee then scatter-added.  d_pts f32 nullable. */
+int of_bilinear_sample_bwd(const void* in, const float* pts, const float* d_out,
+                           float* d_in, float* d_pts,
+                           int B, int H, int W, int C, int dtype, void* stream);
+
+/* model.py:55-73 warp_features (grid built in-kernel). flow (B,H,W,2) f32. */
+int of_warp_features_fwd(const void* feats, const float* flow, void* out, int32_t* idx,
+                         int B, int H, int W, int C, int mode, int dtype, void* stream);
+int of_warp_features_bwd(const void* feats, const float* flow, const float* d_out,
+                         float* d_feats, float* d_flow,
+                         int B, int H, int W, int C, int mode, int dtype, void* stream);
+
+/* old/image_warp.py:7-78 image_warp (== image_warp_tf :81-153); f32 only. */
+int of_image_warp_fwd(const float* im, const float* flow, float* out, int32_t* idx,
+                      int B, int H, int W, int C, void* stream);
+int of_image_warp_bwd(const float* im, const float* flow, const float* d_out,
+                      float* d_im, float* d_flow,
+                      int B, int H, int W, int C, void* stream);
+
+/* ---- resize -------------------------------------------------------------
+ * tf.image.resize bilinear, half-pixel centres, no antialias
+ * (loss.py:18, old/loss.py:15-22, model.py:77).  f32. */
+int of_resize_bilinear(const float* in, float* out, int B, int H, int W, int C,
+                       int out_h, int out_w, void* stream);
+/* model.py:76-77 upscale_flow: x2 bilinear, values * 2.0.  flow (B,h,w,2). */
+int of_upscale_flow_fwd(const float* flow, float* out, int B, int h, int w, void* stream);
+/* adjoint: d_out (B,2h,2w,2) -> d_flow (B,h,w,2) (overwritten, deterministic). */
+int of_upscale_flow_bwd(const float* d_out, float* d_flow, int B, int h, int w, void* stream);
+
+/* ---- cost volume ----------------------------------------------------------
+ * model.py:29-42 create_cost_volume.  f1,f2 (B,H,W,C) dtype; cv has D=(2m+1)^2
+ * channels written at channel offset 0 of a tensor whose pixel stride is
+ * cv_stride elements (cv_stride >= D; lets the caller place it inside a padded
+ * concat buffer); cv dtype = dtype. */
+int of_cost_volume_fwd(const void* f1, const void* f2, void* cv,
+                       int B, int H, int W, int C, int max_disp, int cv_stride,
+                       int dtype, void* stream);
+/* d_cv (B,H,W,cv_stride) dtype -> d_f1, d_f2 f32 (B,H,W,C), overwritten. */
+int of_cost_volume_bwd(const void* f1, const void* f2, const void* d_cv,
+                       float* d_f1, float* d_f2,
+                       int B, int H, int W, int C, int max_disp, int cv_stride,
+                       int dtype, void* stream);
+
+/* ---- fused pyramid losses -------------------------------------------------
+ * loss.py:5-32 LossLayer: for each scale s, resize the full-res 6-channel
+ * batch to flow s's size, warp frame 2 by the flow (REF_IJ), mean |diff|,
+ * average over scales.  ONE launch computes the scalar loss and (if d_flows
+ * != NULL) d loss / d flow_s for every scale.
+ *   imgs (B,H,W,6) f32; flows/d_flows: HOST arrays of num_scales device
+ *   pointers, flow s is (B,hs[s],ws[s],2) f32; loss: device float[1];
+ *   workspace: of_loss_workspace_bytes() bytes (device). */
+size_t of_loss_workspace_bytes(void);
+int of_loss_l1_pyramid_fwdbwd(const float* imgs, const float* const* flows, float* const* d_flows,
+                              const int* hs, const int* ws, int num_scales,
+                              float* loss, int B, int H, int W, int mode,
+                              void* workspace, void* stream);
+/* old/loss.py:7-105 MyLoss photometric (Charbonnier, image_warp of frame 1)
+ * + 0.2 * first-order Charbonnier flow smoothness, / batch.  Same calling
+ * convention; flows ordered coarse -> fine like y_pred[0] (old/loss.py:24-25). */
+int of_loss_charbonnier_smooth_fwdbwd(const float* imgs, const float* const* flows, float* const* d_flows,
+                                      const int* hs, const int* ws, int num_scales,
+                                      float* loss, int B, int H, int W,
+                                      void* workspace, void* stream);
+
+/* ---- pooling / elementwise ------------------------------------------------
+ * model.py:17 MaxPool2D(): 2x2, stride 2, valid.  in (B,H,W,C) -> (B,H/2,W/2,C) */
+int of_maxpool2_fwd(const void* in, void* out, int B, int H, int W, int C, int dtype, void* stream);
+/* gradient goes to the first maximum in window scan order; d_in overwritten. */
+int of_maxpool2_bwd(const void* in, const void* d_out, void* d_in,
+                    int B, int H, int W, int C, int dtype, void* stream);
+/* resnet/models.py:31-34: out = relu(a + b) */
+int of_add_relu_fwd(const void* a, const void* b, void* out, size_t n, int dtype, void* stream);
+/* d = d_out * (out > 0) */
+int of_relu_bwd(const void* out, const void* d_out, void* d, size_t n, int dtype, void* stream);
+
+/* ---- convolution ------------------------------------------------------------
+ * Keras Conv2D(padding='same') on NHWC / HWIO (model.py:12-15,104-114;
+ * resnet/models.py:17-30).  TF asymmetric SAME padding is computed inside.
+ *
+ * fp32 SIMT path (exact-parity mode; also used for Cin=3 / Cout=2 layers):
+ *   y = act(conv(x, w) + bias);  act per OF_ACT_*, LeakyReLU alpha = 0.3.
+ *   x (N,H,W,Cin), w (KH,KW,Cin,Cout) f32, bias (Cout) f32 nullable.
+ *   in_dtype/out_dtype select the storage type of x / y. */
+int of_conv2d_fprop(const void* x, const float* w, const float* bias, void* y,
+                    int N, int H, int W, int Cin, int KH, int KW, int Cout, int stride,
+                    int act, int in_dtype, int out_dtype, void* stream);
+/* dx = conv_transpose(dy, w); dy (N,Ho,Wo,Cout), dx (N,H,W,Cin) overwritten. */
+int of_conv2d_dgrad(const void* dy, const float* w, void* dx,
+                    int N, int H, int W, int Cin, int KH, int KW, int Cout, int stride,
+                    int dy_dtype, int dx_dtype, void* stream);
+/* dw (KH,KW,Cin,Cout) f32 and db (Cout) f32 (nullable), both overwritten. */
+int of_conv2d_wgrad(const void* x, const void* dy, float* dw, float* db,
+                    int N, int H, int W, int Cin, int KH, int KW, int Cout, int stride,
+                    int x_dtype, int dy_dtype, void* stream);
+/* dz = dy * act'(y)  (y = stored activation output) */
+int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int dtype, void* stream);
+
+/* ---- glue -------------------------------------------------------------------
+ * model.py:122-123,131-132: split (B,H,W,6) into the two frames stacked on the
+ * batch axis, (2B,H,W,3), so the shared-weight encoder runs once. */
+int of_split_image_pair(const float* imgs, void* out, int B, int H, int W, int out_dtype, void* stream);
+/* strided channel-slice copy (tf.concat of model.py:100-102 and its gradient
+ * split): dst[p*dst_stride + c] (=|+=) src[p*src_stride + c], c < nch. */
+int of_copy_channels(const void* src, int src_stride, void* dst, int dst_stride, int nch, size_t npix,
+                     int src_dtype, int dst_dtype, int accumulate, void* stream);
+/* Inference-mode BatchNormalization (model.py:14, resnet/models.py:19,24)
+ * folded into the preceding conv: w' = w*s, b' = (b-mean)*s + beta,
+ * s = gamma/sqrt(var+eps); w is (K, Cout) = HWIO flattened; b nullable. */
+int of_bn_fold_fwd(const float* w, const float* b, const float* gamma, const float* beta, const float* mean,
+                   const float* var, float eps, float* w_folded, float* b_folded, int K, int Cout, void* stream);
+/* exact chain rule from (dw', db') back to (dw, db, dgamma, dbeta); db nullable. */
+int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const float* mean, const float* var,
+                   float eps, const float* dw_folded, const float* db_folded, float* dw, float* db, float* dgamma,
+                   float* dbeta, int K, int Cout, void* stream);
+
+/* ---- optimiser ------------------------------------------------------------
+ * train.py:34,56 tf.keras.optimizers.Adam: p -= lr_t * m / (sqrt(v) + eps),
+ * lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t); grad is multiplied by grad_scale
+ * first (1/world_size after the sum-allreduce). */
+int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n,
+                 int step, float lr, float beta1, float beta2, float eps,
+                 float grad_scale, void* stream);
+
+/* ---- collectives (NCCL over NVLink; nothing in the reference) --------------
+ * One communicator per process (rank == GPU).  unique_id is the 128-byte
+ * ncclUniqueId produced by of_comm_unique_id() on rank 0 and shipped to the
+ * other ranks by the caller (torch.distributed broadcast). */
+int of_comm_unique_id(void* host_id128);
+int of_comm_init(const void* host_id128, int world_size, int rank, void** comm_out);
+int of_comm_allreduce_sum_f32(void* comm, float* buf, size_t n, void* stream);
+int of_comm_destroy(void* comm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OFLOW_B200_H */

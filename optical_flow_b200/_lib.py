@@ -1,0 +1,128 @@
+"""ctypes binding of liboflow_b200.so (the C ABI declared in include/oflow_b200.h).
+
+The product path has NO CPU fallback: if the shared library is missing or a
+call fails, this module raises.  torch tensors are used only as device buffers
+(``data_ptr()``) and for the current CUDA stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liboflow_b200.so")
+
+OF_F32, OF_BF16 = 0, 1
+OF_WARP_REF_IJ, OF_WARP_XY = 0, 1
+OF_ACT_NONE, OF_ACT_RELU, OF_ACT_LEAKY = 0, 1, 2
+
+_vp, _i, _sz, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_float
+_pp = C.POINTER(C.c_void_p)
+_ip = C.POINTER(C.c_int)
+
+# name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
+PROTOTYPES = {
+    "of_version": (_i, []),
+    "of_last_error": (C.c_char_p, []),
+    "of_launch_count": (C.c_ulonglong, []),
+    "of_bilinear_sample_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "of_bilinear_sample_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "of_warp_features_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_warp_features_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_image_warp_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "of_image_warp_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "of_resize_bilinear": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_upscale_flow_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "of_upscale_flow_bwd": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "of_cost_volume_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_cost_volume_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_loss_workspace_bytes": (_sz, []),
+    "of_loss_l1_pyramid_fwdbwd": (_i, [_vp, _pp, _pp, _ip, _ip, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "of_loss_charbonnier_smooth_fwdbwd": (_i, [_vp, _pp, _pp, _ip, _ip, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "of_maxpool2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "of_maxpool2_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "of_add_relu_fwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
+    "of_relu_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
+    "of_act_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),
+    "of_conv2d_fprop": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_conv2d_dgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_conv2d_wgrad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_split_image_pair": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "of_copy_channels": (_i, [_vp, _i, _vp, _i, _i, _sz, _i, _i, _i, _vp]),
+    "of_bn_fold_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _i, _vp]),
+    "of_bn_fold_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
+    "of_comm_unique_id": (_i, [_vp]),
+    "of_comm_init": (_i, [_vp, _i, _i, _pp]),
+    "of_comm_allreduce_sum_f32": (_i, [_vp, _vp, _sz, _vp]),
+    "of_comm_destroy": (_i, [_vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once) and set every prototype.  Raises if the
+    library is absent: there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "liboflow_b200.so is missing (%s). Build it with `python -m optical_flow_b200.build`; "
+            "there is no CPU / PyTorch fallback for this path." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)   # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = ""):
+    """Error convention of the C ABI -> Python exceptions:
+    < 0 argument/shape error == the reference's trace-time asserts -> AssertionError,
+    > 0 cudaError_t -> RuntimeError."""
+    if rc == 0:
+        return
+    msg = load().of_last_error().decode("utf-8", "replace")
+    if rc < 0:
+        raise AssertionError("%s: %s (code %d)" % (what, msg, rc))
+    raise RuntimeError("%s: CUDA error %d: %s" % (what, rc, msg))
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return OF_F32
+    if t.dtype == torch.bfloat16:
+        return OF_BF16
+    raise AssertionError("unsupported dtype %s (float32 / bfloat16 only)" % t.dtype)
+
+
+def ptr(t):
+    if t is None:
+        return None
+    assert t.is_cuda, "tensor must live on a CUDA device (no CPU path)"
+    assert t.is_contiguous(), "tensor must be contiguous NHWC"
+    return t.data_ptr()
+
+
+def ptr_array(tensors):
+    arr = (C.c_void_p * len(tensors))()
+    for k, t in enumerate(tensors):
+        arr[k] = ptr(t)
+    return arr
+
+
+def int_array(vals):
+    arr = (C.c_int * len(vals))()
+    for k, v in enumerate(vals):
+        arr[k] = int(v)
+    return arr

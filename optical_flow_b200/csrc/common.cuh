@@ -1,0 +1,126 @@
+// Shared helpers for liboflow_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/oflow_b200.h"
+
+#define OF_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+// ---- error reporting -------------------------------------------------------
+void of_set_error(const char* fmt, ...);
+
+#define OF_REQUIRE(cond, code, ...)            \
+  do {                                         \
+    if (!(cond)) {                             \
+      of_set_error(__VA_ARGS__);               \
+      return (code);                           \
+    }                                          \
+  } while (0)
+
+#define OF_CUDA(expr)                                                          \
+  do {                                                                         \
+    cudaError_t _e = (expr);                                                   \
+    if (_e != cudaSuccess) {                                                   \
+      of_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),     \
+                   __FILE__, __LINE__);                                        \
+      return (int)_e;                                                          \
+    }                                                                          \
+  } while (0)
+
+void of_count_launch(void);
+
+static inline int of_launch_check(const char* what) {
+  of_count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    of_set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+// ---- storage-type helpers ---------------------------------------------------
+template <typename T> __device__ __forceinline__ float ld_f(const T* p);
+template <> __device__ __forceinline__ float ld_f<float>(const float* p) { return __ldg(p); }
+template <> __device__ __forceinline__ float ld_f<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return __bfloat162float(*p);
+}
+template <typename T> __device__ __forceinline__ void st_f(T* p, float v);
+template <> __device__ __forceinline__ void st_f<float>(float* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void st_f<__nv_bfloat16>(__nv_bfloat16* p, float v) {
+  *p = __float2bfloat16_rn(v);
+}
+
+// 4 consecutive channels
+template <typename T> __device__ __forceinline__ float4 ld4(const T* p);
+template <> __device__ __forceinline__ float4 ld4<float>(const float* p) {
+  return __ldg(reinterpret_cast<const float4*>(p));
+}
+template <> __device__ __forceinline__ float4 ld4<__nv_bfloat16>(const __nv_bfloat16* p) {
+  uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
+  __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&r.x);
+  __nv_bfloat162 b = *reinterpret_cast<__nv_bfloat162*>(&r.y);
+  float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+  return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+template <typename T> __device__ __forceinline__ void st4(T* p, float4 v);
+template <> __device__ __forceinline__ void st4<float>(float* p, float4 v) {
+  *reinterpret_cast<float4*>(p) = v;
+}
+template <> __device__ __forceinline__ void st4<__nv_bfloat16>(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y);
+  __nv_bfloat162 b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 r;
+  r.x = *reinterpret_cast<uint32_t*>(&a);
+  r.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
+// vectorised reduction to global memory: one instruction for 4 floats
+// (sm_90+: red.global.add.v4.f32).  p must be 16-byte aligned.
+__device__ __forceinline__ void red_add_v4(float* p, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void red_add(float* p, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Deterministic grid-wide sum of one double per CTA: each CTA stores its
+// partial, the last CTA to arrive (ticket counter) adds them in index order.
+// ws layout: [0] unsigned ticket, [8..] double partials[gridDim.x].
+// Returns true in thread 0 of the last CTA with *total set.
+__device__ __forceinline__ bool grid_sum_last(double cta_partial, void* ws, double* total) {
+  unsigned* ticket = reinterpret_cast<unsigned*>(ws);
+  double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + 16);
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = cta_partial;
+    __threadfence();
+    unsigned t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return false;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    double s = 0.0;
+    for (unsigned i = 0; i < gridDim.x; ++i) s += reinterpret_cast<volatile double*>(partials)[i];
+    *total = s;
+    *ticket = 0u;  // re-arm for the next launch
+    return true;
+  }
+  return false;
+}
+
+static inline int of_valid_dtype(int d) { return d == OF_F32 || d == OF_BF16; }

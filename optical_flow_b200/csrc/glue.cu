@@ -1,0 +1,151 @@
+// Small data-movement / parameter kernels that sit between the heavy ops:
+//   of_split_image_pair  model.py:122-123,131-132: (B,H,W,6) -> (2B,H,W,3) so the shared
+//                        encoder runs once on 2B images
+//   of_copy_channels     strided channel-slice copy / accumulate with dtype conversion
+//                        (tf.concat of model.py:100-102 and its gradient split)
+//   of_bn_fold_fwd/bwd   inference-mode BatchNormalization (model.py:14,
+//                        resnet/models.py:19,24) folded into the preceding conv:
+//                        w' = w * s, b' = (b - mean) * s + beta, s = gamma / sqrt(var + eps),
+//                        and the exact chain rule back to (w, b, gamma, beta).
+#include "common.cuh"
+
+static inline int g_grid(size_t work, int threads = 256) {
+  size_t blocks = (work + threads - 1) / threads;
+  size_t cap = (size_t)OF_NUM_SMS * 16;
+  if (blocks > cap) blocks = cap;
+  return (int)(blocks < 1 ? 1 : blocks);
+}
+
+template <typename TO>
+__global__ void __launch_bounds__(256) split_pair_kernel(const float* __restrict__ imgs, TO* __restrict__ out,
+                                                         size_t npix_b /* B*H*W */) {
+  // out[n = half*B + b] pixel p, channel c  <-  imgs[b, p, half*3 + c]
+  size_t total = npix_b * 6;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    size_t pix = e / 6;
+    int c6 = (int)(e - pix * 6);
+    int half = c6 / 3, c = c6 - half * 3;
+    st_f<TO>(out + ((size_t)half * npix_b + pix) * 3 + c, __ldg(imgs + e));
+  }
+}
+
+template <typename TS, typename TD, bool ACC>
+__global__ void __launch_bounds__(256) copy_channels_kernel(const TS* __restrict__ src, int src_stride,
+                                                            TD* __restrict__ dst, int dst_stride, int nch,
+                                                            size_t npix) {
+  size_t total = npix * nch;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    size_t pix = e / nch;
+    int c = (int)(e - pix * nch);
+    float v = ld_f<TS>(src + pix * src_stride + c);
+    TD* d = dst + pix * dst_stride + c;
+    if (ACC) v += ld_f<TD>(d);
+    st_f<TD>(d, v);
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_fold_fwd_kernel(const float* __restrict__ w, const float* __restrict__ b,
+                                                          const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta,
+                                                          const float* __restrict__ mean,
+                                                          const float* __restrict__ var, float eps,
+                                                          float* __restrict__ wf, float* __restrict__ bf, int K,
+                                                          int Cout) {
+  size_t total = (size_t)K * Cout;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int co = (int)(e % Cout);
+    float s = gamma[co] / sqrtf(var[co] + eps);
+    wf[e] = w[e] * s;
+    if (e < (size_t)Cout) bf[co] = ((b ? b[co] : 0.f) - mean[co]) * s + beta[co];
+  }
+}
+
+// one CTA per output channel: dgamma needs sum_k dwf[k,co] * w[k,co]
+__global__ void __launch_bounds__(256) bn_fold_bwd_kernel(const float* __restrict__ w, const float* __restrict__ b,
+                                                          const float* __restrict__ gamma,
+                                                          const float* __restrict__ mean,
+                                                          const float* __restrict__ var, float eps,
+                                                          const float* __restrict__ dwf,
+                                                          const float* __restrict__ dbf, float* __restrict__ dw,
+                                                          float* __restrict__ db, float* __restrict__ dgamma,
+                                                          float* __restrict__ dbeta, int K, int Cout) {
+  int co = blockIdx.x;
+  float inv_std = 1.0f / sqrtf(var[co] + eps);
+  float s = gamma[co] * inv_std;
+  float acc = 0.f;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    float g = dwf[(size_t)k * Cout + co];
+    acc += g * w[(size_t)k * Cout + co];
+    dw[(size_t)k * Cout + co] = g * s;
+  }
+  __shared__ float sm[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += sm[i];
+    float g_b = dbf[co];
+    dgamma[co] = (t + g_b * ((b ? b[co] : 0.f) - mean[co])) * inv_std;
+    dbeta[co] = g_b;
+    if (db) db[co] = g_b * s;
+  }
+}
+
+extern "C" {
+
+int of_split_image_pair(const float* imgs, void* out, int B, int H, int W, int out_dtype, void* stream) {
+  OF_REQUIRE(imgs && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(B > 0 && H > 0 && W > 0, OF_ERR_SHAPE, "bad dims");
+  OF_REQUIRE(of_valid_dtype(out_dtype), OF_ERR_ARG, "bad dtype");
+  size_t npix = (size_t)B * H * W;
+  if (out_dtype == OF_F32)
+    split_pair_kernel<float><<<g_grid(npix * 6), 256, 0, (cudaStream_t)stream>>>(imgs, (float*)out, npix);
+  else
+    split_pair_kernel<__nv_bfloat16><<<g_grid(npix * 6), 256, 0, (cudaStream_t)stream>>>(imgs, (__nv_bfloat16*)out, npix);
+  return of_launch_check("split_pair_kernel");
+}
+
+int of_copy_channels(const void* src, int src_stride, void* dst, int dst_stride, int nch, size_t npix,
+                     int src_dtype, int dst_dtype, int accumulate, void* stream) {
+  OF_REQUIRE(src && dst, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(nch > 0 && src_stride >= nch && dst_stride >= nch, OF_ERR_SHAPE, "bad channel strides");
+  OF_REQUIRE(of_valid_dtype(src_dtype) && of_valid_dtype(dst_dtype), OF_ERR_ARG, "bad dtype");
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = g_grid(npix * nch);
+#define GO(TS, TD)                                                                                          \
+  do {                                                                                                      \
+    if (accumulate)                                                                                         \
+      copy_channels_kernel<TS, TD, true><<<grid, 256, 0, st>>>((const TS*)src, src_stride, (TD*)dst, dst_stride, nch, npix); \
+    else                                                                                                    \
+      copy_channels_kernel<TS, TD, false><<<grid, 256, 0, st>>>((const TS*)src, src_stride, (TD*)dst, dst_stride, nch, npix); \
+  } while (0)
+  if (src_dtype == OF_F32 && dst_dtype == OF_F32) GO(float, float);
+  else if (src_dtype == OF_F32 && dst_dtype == OF_BF16) GO(float, __nv_bfloat16);
+  else if (src_dtype == OF_BF16 && dst_dtype == OF_F32) GO(__nv_bfloat16, float);
+  else GO(__nv_bfloat16, __nv_bfloat16);
+#undef GO
+  return of_launch_check("copy_channels_kernel");
+}
+
+int of_bn_fold_fwd(const float* w, const float* b, const float* gamma, const float* beta, const float* mean,
+                   const float* var, float eps, float* w_folded, float* b_folded, int K, int Cout, void* stream) {
+  OF_REQUIRE(w && gamma && beta && mean && var && w_folded && b_folded, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(K > 0 && Cout > 0, OF_ERR_SHAPE, "bad dims");
+  bn_fold_fwd_kernel<<<g_grid((size_t)K * Cout), 256, 0, (cudaStream_t)stream>>>(w, b, gamma, beta, mean, var, eps,
+                                                                                 w_folded, b_folded, K, Cout);
+  return of_launch_check("bn_fold_fwd_kernel");
+}
+
+int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const float* mean, const float* var,
+                   float eps, const float* dw_folded, const float* db_folded, float* dw, float* db, float* dgamma,
+                   float* dbeta, int K, int Cout, void* stream) {
+  OF_REQUIRE(w && gamma && mean && var && dw_folded && db_folded && dw && dgamma && dbeta, OF_ERR_ARG,
+             "null pointer argument");
+  OF_REQUIRE(K > 0 && Cout > 0, OF_ERR_SHAPE, "bad dims");
+  bn_fold_bwd_kernel<<<Cout, 256, 0, (cudaStream_t)stream>>>(w, b, gamma, mean, var, eps, dw_folded, db_folded, dw,
+                                                             db, dgamma, dbeta, K, Cout);
+  return of_launch_check("bn_fold_bwd_kernel");
+}
+
+}  // extern "C"

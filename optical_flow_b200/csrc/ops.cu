@@ -1,0 +1,274 @@
+// K5/K9/K11/K13 + elementwise: bilinear resize, flow upscale (fwd/bwd),
+// 2x2 max-pool (fwd/bwd), add+ReLU, activation backward, Adam.
+// All HBM-bound: coalesced NHWC access, float4 vectors where the shape allows,
+// grids sized in multiples of the SM count.
+#include "common.cuh"
+
+static inline int ew_grid(size_t work_items, int threads = 256) {
+  size_t blocks = (work_items + threads - 1) / threads;
+  size_t cap = (size_t)OF_NUM_SMS * 16;
+  if (blocks > cap) blocks = cap;
+  return (int)(blocks < 1 ? 1 : blocks);
+}
+
+// ---- tf.image.resize (bilinear, half-pixel centres, no antialias) -----------
+// loss.py:18, old/loss.py:15-22, model.py:77.  TF's
+// compute_interpolation_weights: in = (o + 0.5) * scale - 0.5,
+// lower = max(floor(in), 0), upper = min(ceil(in), size - 1), lerp = in - floor(in).
+struct Lerp { int lo, hi; float t; };
+__device__ __forceinline__ Lerp tf_lerp(int o, float scale, int in_size) {
+  float src = __fsub_rn(__fmul_rn(__fadd_rn((float)o, 0.5f), scale), 0.5f);
+  float fl = floorf(src);
+  Lerp l;
+  l.lo = max((int)fl, 0);
+  l.hi = min((int)ceilf(src), in_size - 1);
+  l.t = __fsub_rn(src, fl);
+  return l;
+}
+
+__global__ void __launch_bounds__(256) resize_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                     int B, int H, int W, int C, int oh, int ow, float mul) {
+  const float sy = (float)H / (float)oh, sx = (float)W / (float)ow;
+  size_t total = (size_t)B * oh * ow * C;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int c = (int)(e % C);
+    size_t r = e / C;
+    int x = (int)(r % ow); r /= ow;
+    int y = (int)(r % oh);
+    int b = (int)(r / oh);
+    Lerp ly = tf_lerp(y, sy, H), lx = tf_lerp(x, sx, W);
+    const float* base = in + (size_t)b * H * W * C + c;
+    float tl = __ldg(base + ((size_t)ly.lo * W + lx.lo) * C), tr = __ldg(base + ((size_t)ly.lo * W + lx.hi) * C);
+    float bl = __ldg(base + ((size_t)ly.hi * W + lx.lo) * C), br = __ldg(base + ((size_t)ly.hi * W + lx.hi) * C);
+    float top = tl + (tr - tl) * lx.t;
+    float bot = bl + (br - bl) * lx.t;
+    out[e] = (top + (bot - top) * ly.t) * mul;
+  }
+}
+
+// adjoint of the x2 upscale: every low-res pixel gathers from the <=5x5 high-res
+// pixels whose stencil can touch it (deterministic, no atomics).
+__global__ void __launch_bounds__(256) upscale2_bwd_kernel(const float* __restrict__ d_out, float* __restrict__ d_in,
+                                                           int B, int h, int w, int C, float mul) {
+  const int oh = 2 * h, ow = 2 * w;
+  size_t total = (size_t)B * h * w * C;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int c = (int)(e % C);
+    size_t r = e / C;
+    int x = (int)(r % w); r /= w;
+    int y = (int)(r % h);
+    int b = (int)(r / h);
+    float acc = 0.f;
+    for (int oy = max(2 * y - 2, 0); oy <= min(2 * y + 2, oh - 1); ++oy) {
+      Lerp ly = tf_lerp(oy, 0.5f, h);
+      float wy = (ly.lo == y ? 1.f - ly.t : 0.f) + (ly.hi == y ? ly.t : 0.f);
+      if (wy == 0.f) continue;
+      for (int ox = max(2 * x - 2, 0); ox <= min(2 * x + 2, ow - 1); ++ox) {
+        Lerp lx = tf_lerp(ox, 0.5f, w);
+        float wx = (lx.lo == x ? 1.f - lx.t : 0.f) + (lx.hi == x ? lx.t : 0.f);
+        if (wx == 0.f) continue;
+        acc += wy * wx * __ldg(d_out + (((size_t)b * oh + oy) * ow + ox) * C + c);
+      }
+    }
+    d_in[e] = acc * mul;
+  }
+}
+
+// ---- MaxPool2D() 2x2 / 2 / valid  (model.py:17) ------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const T* __restrict__ in, T* __restrict__ out,
+                                                           int B, int H, int W, int C) {
+  const int oh = H / 2, ow = W / 2, CV = C / 4;
+  size_t total = (size_t)B * oh * ow * CV;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int v = (int)(e % CV);
+    size_t r = e / CV;
+    int x = (int)(r % ow); r /= ow;
+    int y = (int)(r % oh);
+    int b = (int)(r / oh);
+    const T* p = in + (((size_t)b * H + 2 * y) * W + 2 * x) * C + v * 4;
+    float4 a = ld4<T>(p), bq = ld4<T>(p + C), c = ld4<T>(p + (size_t)W * C), d = ld4<T>(p + (size_t)W * C + C);
+    float4 m;
+    m.x = fmaxf(fmaxf(a.x, bq.x), fmaxf(c.x, d.x));
+    m.y = fmaxf(fmaxf(a.y, bq.y), fmaxf(c.y, d.y));
+    m.z = fmaxf(fmaxf(a.z, bq.z), fmaxf(c.z, d.z));
+    m.w = fmaxf(fmaxf(a.w, bq.w), fmaxf(c.w, d.w));
+    st4<T>(out + (((size_t)b * oh + y) * ow + x) * C + v * 4, m);
+  }
+}
+
+__device__ __forceinline__ void route4(float a, float b, float c, float d, float g, float& ga, float& gb,
+                                       float& gc, float& gd) {
+  // gradient to the first maximum in window scan order (row-major)
+  float m = fmaxf(fmaxf(a, b), fmaxf(c, d));
+  ga = gb = gc = gd = 0.f;
+  if (a == m) ga = g;
+  else if (b == m) gb = g;
+  else if (c == m) gc = g;
+  else gd = g;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2_bwd_kernel(const T* __restrict__ in, const T* __restrict__ d_out,
+                                                           T* __restrict__ d_in, int B, int H, int W, int C) {
+  const int oh = H / 2, ow = W / 2, CV = C / 4;
+  size_t total = (size_t)B * oh * ow * CV;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int v = (int)(e % CV);
+    size_t r = e / CV;
+    int x = (int)(r % ow); r /= ow;
+    int y = (int)(r % oh);
+    int b = (int)(r / oh);
+    size_t o = (((size_t)b * H + 2 * y) * W + 2 * x) * C + v * 4;
+    const T* p = in + o;
+    float4 a = ld4<T>(p), bq = ld4<T>(p + C), c = ld4<T>(p + (size_t)W * C), d = ld4<T>(p + (size_t)W * C + C);
+    float4 g = ld4<T>(d_out + (((size_t)b * oh + y) * ow + x) * C + v * 4);
+    float4 ga, gb, gc, gd;
+    route4(a.x, bq.x, c.x, d.x, g.x, ga.x, gb.x, gc.x, gd.x);
+    route4(a.y, bq.y, c.y, d.y, g.y, ga.y, gb.y, gc.y, gd.y);
+    route4(a.z, bq.z, c.z, d.z, g.z, ga.z, gb.z, gc.z, gd.z);
+    route4(a.w, bq.w, c.w, d.w, g.w, ga.w, gb.w, gc.w, gd.w);
+    st4<T>(d_in + o, ga);
+    st4<T>(d_in + o + C, gb);
+    st4<T>(d_in + o + (size_t)W * C, gc);
+    st4<T>(d_in + o + (size_t)W * C + C, gd);
+  }
+}
+
+// ---- elementwise -------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) add_relu_kernel(const T* __restrict__ a, const T* __restrict__ b,
+                                                       T* __restrict__ out, size_t n4) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n4; e += (size_t)gridDim.x * blockDim.x) {
+    float4 x = ld4<T>(a + e * 4), y = ld4<T>(b + e * 4);
+    st4<T>(out + e * 4, make_float4(fmaxf(x.x + y.x, 0.f), fmaxf(x.y + y.y, 0.f), fmaxf(x.z + y.z, 0.f),
+                                    fmaxf(x.w + y.w, 0.f)));
+  }
+}
+
+__device__ __forceinline__ float act_grad(float y, int act) {
+  // ReLU: tf grad = (y > 0); LeakyReLU(0.3): y > 0 ? 1 : 0.3 (sign(y) == sign(z))
+  if (act == OF_ACT_RELU) return y > 0.f ? 1.f : 0.f;
+  if (act == OF_ACT_LEAKY) return y > 0.f ? 1.f : 0.3f;
+  return 1.f;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) act_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy,
+                                                      T* __restrict__ dz, size_t n4, int act) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n4; e += (size_t)gridDim.x * blockDim.x) {
+    float4 a = ld4<T>(y + e * 4), g = ld4<T>(dy + e * 4);
+    st4<T>(dz + e * 4, make_float4(g.x * act_grad(a.x, act), g.y * act_grad(a.y, act), g.z * act_grad(a.z, act),
+                                   g.w * act_grad(a.w, act)));
+  }
+}
+
+// ---- Adam (train.py:34,56; Keras epsilon 1e-7, TF update form) ----------------
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, size_t n,
+                                                   float lr_t, float omb1, float omb2, float eps, float gscale) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    float gr = g[e] * gscale;
+    float mm = m[e], vv = v[e];
+    mm = mm + (gr - mm) * omb1;
+    vv = vv + (gr * gr - vv) * omb2;
+    m[e] = mm;
+    v[e] = vv;
+    p[e] = p[e] - lr_t * mm / (sqrtf(vv) + eps);
+  }
+}
+
+extern "C" {
+
+int of_resize_bilinear(const float* in, float* out, int B, int H, int W, int C, int out_h, int out_w,
+                       void* stream) {
+  OF_REQUIRE(in && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(B > 0 && H > 0 && W > 0 && C > 0 && out_h > 0 && out_w > 0, OF_ERR_SHAPE, "bad dims");
+  size_t total = (size_t)B * out_h * out_w * C;
+  resize_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(in, out, B, H, W, C, out_h, out_w, 1.0f);
+  return of_launch_check("resize_kernel");
+}
+
+int of_upscale_flow_fwd(const float* flow, float* out, int B, int h, int w, void* stream) {
+  OF_REQUIRE(flow && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(B > 0 && h > 0 && w > 0, OF_ERR_SHAPE, "bad dims");
+  size_t total = (size_t)B * 4 * h * w * 2;
+  resize_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(flow, out, B, h, w, 2, 2 * h, 2 * w, 2.0f);
+  return of_launch_check("upscale_flow_fwd");
+}
+
+int of_upscale_flow_bwd(const float* d_out, float* d_flow, int B, int h, int w, void* stream) {
+  OF_REQUIRE(d_out && d_flow, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(B > 0 && h > 0 && w > 0, OF_ERR_SHAPE, "bad dims");
+  size_t total = (size_t)B * h * w * 2;
+  upscale2_bwd_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(d_out, d_flow, B, h, w, 2, 2.0f);
+  return of_launch_check("upscale_flow_bwd");
+}
+
+int of_maxpool2_fwd(const void* in, void* out, int B, int H, int W, int C, int dtype, void* stream) {
+  OF_REQUIRE(in && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype), OF_ERR_ARG, "bad dtype");
+  OF_REQUIRE(B > 0 && H >= 2 && W >= 2 && C > 0 && C % 4 == 0, OF_ERR_SHAPE, "maxpool2 needs C %% 4 == 0, H,W >= 2");
+  size_t total = (size_t)B * (H / 2) * (W / 2) * (C / 4);
+  if (dtype == OF_F32)
+    maxpool2_fwd_kernel<float><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>((const float*)in, (float*)out, B, H, W, C);
+  else
+    maxpool2_fwd_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)in, (__nv_bfloat16*)out, B, H, W, C);
+  return of_launch_check("maxpool2_fwd");
+}
+
+int of_maxpool2_bwd(const void* in, const void* d_out, void* d_in, int B, int H, int W, int C, int dtype,
+                    void* stream) {
+  OF_REQUIRE(in && d_out && d_in, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype), OF_ERR_ARG, "bad dtype");
+  OF_REQUIRE(B > 0 && H >= 2 && W >= 2 && C > 0 && C % 4 == 0 && H % 2 == 0 && W % 2 == 0, OF_ERR_SHAPE,
+             "maxpool2_bwd needs even H,W and C %% 4 == 0");
+  size_t total = (size_t)B * (H / 2) * (W / 2) * (C / 4);
+  if (dtype == OF_F32)
+    maxpool2_bwd_kernel<float><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const float*)in, (const float*)d_out, (float*)d_in, B, H, W, C);
+  else
+    maxpool2_bwd_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)in, (const __nv_bfloat16*)d_out, (__nv_bfloat16*)d_in, B, H, W, C);
+  return of_launch_check("maxpool2_bwd");
+}
+
+int of_add_relu_fwd(const void* a, const void* b, void* out, size_t n, int dtype, void* stream) {
+  OF_REQUIRE(a && b && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype) && n % 4 == 0, OF_ERR_ARG, "bad dtype or n %% 4 != 0");
+  if (dtype == OF_F32)
+    add_relu_kernel<float><<<ew_grid(n / 4), 256, 0, (cudaStream_t)stream>>>((const float*)a, (const float*)b, (float*)out, n / 4);
+  else
+    add_relu_kernel<__nv_bfloat16><<<ew_grid(n / 4), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)out, n / 4);
+  return of_launch_check("add_relu");
+}
+
+int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int dtype, void* stream) {
+  OF_REQUIRE(y && dy && dz, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype) && n % 4 == 0, OF_ERR_ARG, "bad dtype or n %% 4 != 0");
+  OF_REQUIRE(act >= OF_ACT_NONE && act <= OF_ACT_LEAKY, OF_ERR_ARG, "bad activation %d", act);
+  if (dtype == OF_F32)
+    act_bwd_kernel<float><<<ew_grid(n / 4), 256, 0, (cudaStream_t)stream>>>((const float*)y, (const float*)dy, (float*)dz, n / 4, act);
+  else
+    act_bwd_kernel<__nv_bfloat16><<<ew_grid(n / 4), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dz, n / 4, act);
+  return of_launch_check("act_bwd");
+}
+
+int of_relu_bwd(const void* out, const void* d_out, void* d, size_t n, int dtype, void* stream) {
+  return of_act_bwd(out, d_out, d, n, OF_ACT_RELU, dtype, stream);
+}
+
+int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n, int step, float lr, float beta1,
+                 float beta2, float eps, float grad_scale, void* stream) {
+  OF_REQUIRE(param && grad && m && v, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(step >= 1, OF_ERR_ARG, "Adam step count is 1-based");
+  double lr_t = (double)lr * sqrt(1.0 - pow((double)beta2, step)) / (1.0 - pow((double)beta1, step));
+  adam_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, m, v, n, (float)lr_t, 1.0f - beta1,
+                                                            1.0f - beta2, eps, grad_scale);
+  return of_launch_check("adam_kernel");
+}
+
+}  // extern "C"

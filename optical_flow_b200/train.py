@@ -1,0 +1,132 @@
+"""Mirror of the reference's train.py: ``train_step(batch_imgs, step_count)`` ->
+``(loss_value, flows)`` (train.py:47-61) plus a thin epoch driver.
+
+The reference is a module-level script (constants at import time, train.py:15-27);
+here the same constants are defaults of ``Trainer`` / ``main()``.  Data-parallel
+replicas (one process per GPU) all-reduce the flat gradient with NCCL before Adam.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import time
+
+import torch
+
+from . import _lib as L
+from . import functional as F
+from .loss import LossLayer
+from .model import build_flow_net
+
+img_height = 192            # train.py:15
+img_width = 640             # train.py:16
+batch_size = 4              # train.py:22
+nepochs = 20                # train.py:25
+learning_rate = 1e-4        # train.py:34
+
+
+class Trainer:
+    def __init__(self, height=img_height, width=img_width, pretrained_weights_path=None, lr=learning_rate,
+                 conv_mode="bf16", warp_mode="ref_ij", comm=None, world_size=1, seed=42):
+        self.flow_net = build_flow_net(height, width, pretrained_weights_path, conv_mode=conv_mode,
+                                       warp_mode=warp_mode, seed=seed)
+        self.loss_layer = LossLayer(warp_mode=warp_mode)
+        self.lr = lr
+        self.step = 0
+        self.comm = comm
+        self.world_size = world_size
+
+    @property
+    def trainable_weights(self):
+        return self.flow_net.trainable_weights
+
+    def forward_backward(self, batch_imgs):
+        """tape.gradient(loss, trainable_weights) of train.py:50-55: loss + flat gradient."""
+        flows = self.flow_net(batch_imgs)
+        loss_value = self.loss_layer(batch_imgs, flows)            # also yields d loss / d flow_s
+        self.flow_net.backward(self.loss_layer.d_flows)
+        return loss_value, flows
+
+    def apply_gradients(self):
+        """optimizer.apply_gradients (train.py:56): Adam, Keras defaults (eps 1e-7)."""
+        st = self.flow_net.store
+        if self.comm is not None and self.world_size > 1:
+            L.check(L.load().of_comm_allreduce_sum_f32(self.comm, L.ptr(st.grad), st.grad.numel(), L.stream_ptr()),
+                    "of_comm_allreduce_sum_f32")
+        self.step += 1
+        F.adam_step(st.flat, st.grad, st.adam_m, st.adam_v, self.step, lr=self.lr,
+                    grad_scale=1.0 / self.world_size)
+
+    def train_step(self, batch_imgs, step_count=None):
+        """train.py:47-61.  Returns (loss_value [0-d device tensor], flows)."""
+        loss_value, flows = self.forward_backward(batch_imgs)
+        self.apply_gradients()
+        return loss_value, flows
+
+
+_default_trainer = None
+
+
+def train_step(batch_imgs, step_count=None):
+    """Module-level entry point with the reference's signature (train.py:48)."""
+    global _default_trainer
+    if _default_trainer is None:
+        _default_trainer = Trainer(batch_imgs.shape[1], batch_imgs.shape[2])
+    return _default_trainer.train_step(batch_imgs, step_count)
+
+
+def synthetic_batch(batch, height, width, seed, device):
+    """Seeded synthetic image pairs in the value range data_reader.py:53-63 produces
+    (pixels/255 minus the BGR mean); frame 2 is frame 1 shifted by a few pixels."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    yy = torch.arange(height, dtype=torch.float32).view(1, height, 1, 1)
+    xx = torch.arange(width, dtype=torch.float32).view(1, 1, width, 1)
+    im1 = torch.zeros(batch, height, width, 3)
+    im2 = torch.zeros(batch, height, width, 3)
+    shift = (torch.rand(batch, 2, generator=g) * 16 - 8).view(batch, 1, 1, 2)
+    for _ in range(8):
+        fx = 0.005 + 0.145 * torch.rand(batch, 1, 1, 3, generator=g)
+        fy = 0.005 + 0.145 * torch.rand(batch, 1, 1, 3, generator=g)
+        ph = 6.2831853 * torch.rand(batch, 1, 1, 3, generator=g)
+        amp = 0.03 + 0.09 * torch.rand(batch, 1, 1, 3, generator=g)
+        im1 += amp * torch.sin(6.2831853 * (fx * xx + fy * yy) + ph)
+        im2 += amp * torch.sin(6.2831853 * (fx * (xx + shift[..., :1]) + fy * (yy + shift[..., 1:])) + ph)
+    means = torch.tensor([104.0, 117.0, 123.0]).view(1, 1, 1, 3) / 255.0
+    im1 = (im1 + 0.5 + 0.02 * torch.randn(im1.shape, generator=g)).clamp(0, 1) - means
+    im2 = (im2 + 0.5 + 0.01 * torch.randn(im2.shape, generator=g)).clamp(0, 1) - means
+    return torch.cat([im1, im2], dim=-1).contiguous().to(device)
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description="optical-flow training (synthetic pairs; mirrors train.py:64-88)")
+    ap.add_argument("--height", type=int, default=img_height)
+    ap.add_argument("--width", type=int, default=img_width)
+    ap.add_argument("--batch-size", type=int, default=batch_size)
+    ap.add_argument("--epochs", type=int, default=nepochs)
+    ap.add_argument("--batches-per-epoch", type=int, default=50)
+    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--warp-mode", default="ref_ij", choices=["ref_ij", "xy"])
+    ap.add_argument("--save-dir", default="ckpts")
+    args = ap.parse_args(argv)
+    dev = torch.device("cuda", 0)
+    trainer = Trainer(args.height, args.width, None, conv_mode=args.conv_mode, warp_mode=args.warp_mode)
+    trainer.flow_net.summary()
+    step_count = 0
+    for epoch in range(args.epochs):
+        t0 = time.time()
+        if epoch == 15:                                   # train.py:69-71
+            trainer.lr = 1e-5
+        for batch_idx in range(args.batches_per_epoch):
+            batch = synthetic_batch(args.batch_size, args.height, args.width, 1234 + step_count, dev)
+            loss_value, _ = trainer.train_step(batch, step_count)
+            if (batch_idx + 1) % 10 == 0:                 # loss stays on device between reads
+                print("epoch %d batch %d/%d loss %.4e" % (epoch + 1, batch_idx + 1, args.batches_per_epoch,
+                                                          loss_value.item()))
+            step_count += 1
+        print("Epoch computed in %.1fs" % (time.time() - t0))
+        os.makedirs(args.save_dir, exist_ok=True)
+        trainer.flow_net.save_weights(os.path.join(args.save_dir, "flow_net_%d" % epoch))   # train.py:88
+
+
+if __name__ == "__main__":
+    main()

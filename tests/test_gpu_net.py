@@ -1,0 +1,129 @@
+"""GPU parity of the whole training step (network forward, loss, every gradient,
+Adam) against the torch-CPU oracle, through the reference-named Python surface.
+
+conv_mode='fp32' (SIMT convs): flows, loss and all 4 937 608 gradient entries within
+1e-4 of max-abs per tensor (fp32 accumulation-order noise through ~40 layers; the
+per-op 1e-5 bars are in test_gpu_ops.py).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_torch as T
+
+pytestmark = pytest.mark.gpu
+
+
+def maxrel(got, exp):
+    got = got.detach().float().cpu().numpy() if isinstance(got, torch.Tensor) else np.asarray(got)
+    exp = exp.detach().cpu().numpy() if isinstance(exp, torch.Tensor) else np.asarray(exp)
+    return float(np.abs(got - exp).max()) / max(float(np.abs(exp).max()), 1e-30)
+
+
+@pytest.fixture(scope="module")
+def small_case():
+    B, H, W = 2, 64, 96
+    params, stats = T.init_params(seed=42, randomize_bn=True)
+    imgs = T.synthetic_pairs(B, H, W, seed=11)
+    ref = T.FlowNetRef(params, stats)
+    loss, flows, grads = ref.loss_and_grads(torch.tensor(imgs))
+    return dict(B=B, H=H, W=W, params=params, stats=stats, imgs=imgs, loss=loss, flows=flows, grads=grads)
+
+
+def make_net(case, cuda, conv_mode):
+    from optical_flow_b200.model import build_flow_net
+    net = build_flow_net(case["H"], case["W"], None, conv_mode=conv_mode)
+    net.store.load_numpy(case["params"], case["stats"])
+    return net
+
+
+def test_param_inventory_matches_reference_count(cuda):
+    from optical_flow_b200.model import build_flow_net
+    net = build_flow_net(32, 64, None, conv_mode="fp32")
+    assert net.store.num_trainable() == 4937608
+    assert len(net.trainable_weights) == len(T.encoder_param_specs()) + len(T.decoder_param_specs())
+    assert list(net.store.specs.keys()) == list(T.encoder_param_specs().keys()) + list(T.decoder_param_specs().keys())
+
+
+def test_fp32_forward_loss_backward_parity(cuda, small_case):
+    from optical_flow_b200.loss import LossLayer
+    net = make_net(small_case, cuda, "fp32")
+    imgs = torch.tensor(small_case["imgs"], device=cuda)
+    flows = net(imgs)
+    assert [tuple(f.shape) for f in flows] == [tuple(f.shape) for f in small_case["flows"]]
+    for k, (f, e) in enumerate(zip(flows, small_case["flows"])):
+        assert maxrel(f, e) < 1e-4, "flow %d: %g" % (k, maxrel(f, e))
+    layer = LossLayer()
+    loss = layer(imgs, flows)
+    assert abs(loss.item() - small_case["loss"].item()) < 1e-4 * abs(small_case["loss"].item())
+    net.backward(layer.d_flows)
+    worst = ("", 0.0)
+    for name, g in net.store.g.items():
+        e = small_case["grads"][name]
+        r = maxrel(g, e)
+        if r > worst[1]:
+            worst = (name, r)
+    # warp indices flip when an fp32-noisy flow crosses an integer; allow that on isolated entries
+    assert worst[1] < 2e-3, "worst gradient tensor %s: %g" % worst
+    cos_all = []
+    for name, g in net.store.g.items():
+        e = small_case["grads"][name].numpy().ravel()
+        gg = g.detach().cpu().numpy().ravel()
+        if np.linalg.norm(e) > 0:
+            cos_all.append(float(np.dot(gg, e) / (np.linalg.norm(gg) * np.linalg.norm(e) + 1e-30)))
+    assert min(cos_all) > 0.9999
+
+
+def test_train_step_adam_parity(cuda, small_case):
+    from optical_flow_b200.train import Trainer
+    tr = Trainer(small_case["H"], small_case["W"], None, conv_mode="fp32")
+    tr.flow_net.store.load_numpy(small_case["params"], small_case["stats"])
+    imgs = torch.tensor(small_case["imgs"], device=cuda)
+    loss_value, flows = tr.train_step(imgs, 0)
+    assert abs(loss_value.item() - small_case["loss"].item()) < 1e-4 * abs(small_case["loss"].item())
+    # oracle Adam step on the oracle gradients
+    for name in ("flow3_conv6/kernel", "layer2_block_1_conv1/kernel", "layer1_bn/gamma", "conv1/bias"):
+        p0 = torch.tensor(small_case["params"][name])
+        g = small_case["grads"][name]
+        p1, _, _ = T.adam_step(p0, g, torch.zeros_like(p0), torch.zeros_like(p0), 1)
+        got = tr.flow_net.store.p[name].detach().cpu()
+        # first Adam step moves every weight by ~lr * sign(g): compare the update, not the weight
+        upd_ref = (p1 - p0).numpy()
+        upd_got = (got - p0).numpy()
+        big = np.abs(g.numpy()) > 1e-3 * np.abs(g.numpy()).max()
+        np.testing.assert_allclose(upd_got[big], upd_ref[big], rtol=2e-2, atol=1e-7)
+
+
+def test_dp_average_equals_concatenated_batch(cuda, small_case):
+    """the average of replica gradients over batch shards equals the
+    single-replica gradient on the concatenated batch (loss is a batch mean, BN is
+    inference-mode)."""
+    from optical_flow_b200.loss import LossLayer
+    net = make_net(small_case, cuda, "fp32")
+    imgs = torch.tensor(small_case["imgs"], device=cuda)
+    layer = LossLayer()
+    net.backward_from = None
+    flows = net(imgs)
+    layer(imgs, flows)
+    net.backward(layer.d_flows)
+    g_full = net.store.grad.clone()
+    acc = torch.zeros_like(g_full)
+    for b in range(small_case["B"]):
+        part = imgs[b:b + 1].contiguous()
+        flows = net(part)
+        layer(part, flows)
+        net.backward(layer.d_flows)
+        acc += net.store.grad
+    acc /= small_case["B"]
+    assert maxrel(acc, g_full) < 1e-4
+
+
+def test_save_load_weights_roundtrip(cuda, tmp_path):
+    from optical_flow_b200.model import build_flow_net
+    net = build_flow_net(32, 64, None, conv_mode="fp32", seed=1)
+    path = str(tmp_path / "w")
+    net.save_weights(path)
+    net2 = build_flow_net(32, 64, None, conv_mode="fp32", seed=2)
+    assert not torch.equal(net.store.flat, net2.store.flat)
+    net2.load_weights(path)
+    assert torch.equal(net.store.flat, net2.store.flat)
