@@ -146,6 +146,50 @@ int of_conv2d_dgrad(const void* dy, const float* w, void* dx,
 int of_conv2d_wgrad(const void* x, const void* dy, float* dw, float* db,
                     int N, int H, int W, int Cin, int KH, int KW, int Cout, int stride,
                     int x_dtype, int dy_dtype, void* stream);
+/* bf16 tensor-core path (tcgen05 / TMEM implicit GEMM, fp32 accumulate) - the fast path for
+ * every conv with >= 32 in/out channels.  One descriptor drives fprop and dgrad:
+ *   out[p, n] = epi( sum_{tap, k} src[p*stride + sign*(tap - pad), k] * wpacked[tap][n][k] )
+ *   epi(v) = act(v + bias[n] + add[p, n]) * act'(mask[p, n])
+ * fprop: sign=+1, wpacked = [tap][Cout][K over the (64-padded) sources];
+ * dgrad (stride 1): sign=-1, src = dz, wpacked = [tap][Cin segment][Cout], mask = the producing
+ * layer's stored activation output so the next dz is written directly.
+ * Sources are bf16 NHWC (channel counts and pixel strides multiples of 8); up to two sources
+ * replace tf.concat (model.py:100-102). */
+typedef struct {
+  const void* src[2]; int src_c[2]; int src_stride[2]; int num_src;
+  const void* wpacked; int n_rows; int k_pad;
+  int N, H, W;              /* source spatial dims */
+  int Ho, Wo;               /* output spatial dims */
+  int KH, KW, stride, pad_t, pad_l, sign;
+  int n_mma, n_valid;       /* MMA N (multiple of 16, <= 256) and real output channels */
+  void* out; int out_dtype; int out_stride;
+  const float* bias; int act;
+  const void* add; int add_dtype; int add_stride;
+  const void* mask; int mask_dtype; int mask_stride; int mask_act;
+} of_tc_conv;
+int of_conv_tc_run(const of_tc_conv* c, void* stream);
+/* fp32 HWIO weights -> bf16 packed [taps][rows][cols] (cols %% 64 == 0).  transpose=0: rows = co,
+ * cols = packed ci; transpose=1: rows = packed ci, cols = co.  Segment s maps original ci in
+ * [seg_off, seg_off+seg_cnt) to packed index seg_base + (ci - seg_off); everything else is 0. */
+int of_conv_tc_pack_weights(const float* w_hwio, void* packed, int taps, int Cin, int Cout, int rows, int cols,
+                            int transpose, int nseg, const int* seg_off, const int* seg_cnt, const int* seg_base,
+                            void* stream);
+/* dw[tap][ci][co] (f32 HWIO, overwritten) = sum_pix x[pix (+) tap][ci] * dy[pix][co]; x = up to two
+ * bf16 NHWC sources (x_valid real channels each, the first mapping to original ci = x_ci0). */
+typedef struct {
+  const void* x[2]; int x_c[2]; int x_stride[2]; int x_valid[2]; int x_ci0[2]; int num_src;
+  const void* dy; int dy_c; int dy_stride;
+  float* dw;
+  int N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, Cin, Cout;
+} of_tc_wgrad;
+int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream);
+/* out (N,H,W,C) = dy (N,Ho,Wo,C) with zeros inserted (out[2i,2j] = dy[i,j]): a stride-2 conv's
+ * dgrad is the stride-1 dgrad of this tensor. */
+int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,
+                      void* stream);
+/* db[c] = sum over pixels of dy[p, c] (dy has pixel stride dy_stride) */
+int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int dtype, void* stream);
+
 /* dz = dy * act'(y)  (y = stored activation output) */
 int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int dtype, void* stream);
 

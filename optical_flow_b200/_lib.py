@@ -22,8 +22,40 @@ _vp, _i, _sz, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_float
 _pp = C.POINTER(C.c_void_p)
 _ip = C.POINTER(C.c_int)
 
+class TcConv(C.Structure):
+    """of_tc_conv (include/oflow_b200.h)."""
+    _fields_ = [("src", C.c_void_p * 2), ("src_c", C.c_int * 2), ("src_stride", C.c_int * 2), ("num_src", C.c_int),
+                ("wpacked", C.c_void_p), ("n_rows", C.c_int), ("k_pad", C.c_int),
+                ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int),
+                ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_t", C.c_int), ("pad_l", C.c_int),
+                ("sign", C.c_int), ("n_mma", C.c_int), ("n_valid", C.c_int),
+                ("out", C.c_void_p), ("out_dtype", C.c_int), ("out_stride", C.c_int),
+                ("bias", C.c_void_p), ("act", C.c_int),
+                ("add", C.c_void_p), ("add_dtype", C.c_int), ("add_stride", C.c_int),
+                ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("mask_stride", C.c_int), ("mask_act", C.c_int)]
+
+
+class TcWgrad(C.Structure):
+    """of_tc_wgrad (include/oflow_b200.h)."""
+    _fields_ = [("x", C.c_void_p * 2), ("x_c", C.c_int * 2), ("x_stride", C.c_int * 2), ("x_valid", C.c_int * 2),
+                ("x_ci0", C.c_int * 2), ("num_src", C.c_int),
+                ("dy", C.c_void_p), ("dy_c", C.c_int), ("dy_stride", C.c_int),
+                ("dw", C.c_void_p),
+                ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int),
+                ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_t", C.c_int), ("pad_l", C.c_int),
+                ("Cin", C.c_int), ("Cout", C.c_int)]
+
+
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
 PROTOTYPES = {
+    "of_conv_tc_run": (C.c_int, [C.POINTER(TcConv), C.c_void_p]),
+    "of_conv_tc_pack_weights": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                          C.c_void_p]),
+    "of_conv_tc_wgrad": (C.c_int, [C.POINTER(TcWgrad), C.c_void_p]),
+    "of_zero_upsample2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_void_p]),
+    "of_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "of_version": (_i, []),
     "of_last_error": (C.c_char_p, []),
     "of_launch_count": (C.c_ulonglong, []),

@@ -1,0 +1,244 @@
+"""bf16 tensor-core convolution back-end (tcgen05 / TMEM implicit GEMM in conv_tc.cu and
+conv_tc_wgrad.cu) for FlowNet, plus thin functional wrappers used by the parity tests.
+
+Activations are bf16 NHWC; weights stay fp32 masters (BN folded per step) and are re-packed
+to bf16 GEMM layouts every step; accumulation is fp32 in TMEM.  Layers that are not
+tensor-core shaped (Cin = 3 stem, Cout = 2 flow heads' dgrad/wgrad) use the SIMT kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from . import functional as F
+
+
+def _ceil(a, b):
+    return (a + b - 1) // b * b
+
+
+class Source:
+    """One K-source of a conv: bf16 NHWC tensor, `valid` real channels that map to original
+    input channels [ci0, ci0 + valid)."""
+
+    def __init__(self, t, valid=None, ci0=0):
+        assert t.dtype == torch.bfloat16 and t.is_contiguous()
+        self.t, self.valid, self.ci0 = t, (t.shape[-1] if valid is None else valid), ci0
+
+
+class MultiSource:
+    """Stands for tf.concat([...], axis=-1) (model.py:100-102) without materialising it."""
+
+    def __init__(self, sources):
+        self.sources = sources
+        self.shape = tuple(sources[0].t.shape[:3]) + (sum(s.valid for s in sources),)
+        self.device = sources[0].t.device
+
+
+def _sources_of(x):
+    return x.sources if isinstance(x, MultiSource) else [Source(x)]
+
+
+def pack_weights(w_hwio, segs, rows, cols, transpose, out=None):
+    """fp32 HWIO -> bf16 [taps][rows][cols]; segs = [(orig_ci_off, count, packed_base), ...]."""
+    KH, KW, Cin, Cout = w_hwio.shape
+    taps = KH * KW
+    if out is None:
+        out = torch.empty((taps, rows, cols), dtype=torch.bfloat16, device=w_hwio.device)
+    n = len(segs)
+    L.check(L.load().of_conv_tc_pack_weights(L.ptr(w_hwio), L.ptr(out), taps, Cin, Cout, rows, cols,
+                                             1 if transpose else 0, n, L.int_array([s[0] for s in segs]),
+                                             L.int_array([s[1] for s in segs]), L.int_array([s[2] for s in segs]),
+                                             L.stream_ptr()), "of_conv_tc_pack_weights")
+    return out
+
+
+def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, sign, out,
+           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE):
+    d = L.TcConv()
+    for k, s in enumerate(sources):
+        d.src[k] = s.t.data_ptr()
+        d.src_c[k] = s.t.shape[-1]
+        d.src_stride[k] = s.t.shape[-1]
+    d.num_src = len(sources)
+    d.wpacked = wpacked.data_ptr()
+    d.n_rows, d.k_pad = wpacked.shape[1], wpacked.shape[2]
+    d.N, d.H, d.W, d.Ho, d.Wo = N, H, W, Ho, Wo
+    d.KH, d.KW, d.stride, d.pad_t, d.pad_l, d.sign = KH, KW, stride, pad_t, pad_l, sign
+    d.n_mma, d.n_valid = n_mma, n_valid
+    d.out, d.out_dtype, d.out_stride = out.data_ptr(), L.dtype_code(out), out.shape[-1]
+    d.bias = L.ptr(bias)
+    d.act = act
+    if add is not None:
+        d.add, d.add_dtype, d.add_stride = add.data_ptr(), L.dtype_code(add), add.shape[-1]
+    if mask is not None:
+        d.mask, d.mask_dtype, d.mask_stride, d.mask_act = mask.data_ptr(), L.dtype_code(mask), mask.shape[-1], mask_act
+    L.check(L.load().of_conv_tc_run(C.byref(d), L.stream_ptr()), "of_conv_tc_run")
+    return out
+
+
+# ------------------------------------------------------------------ functional --
+
+def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None):
+    """Keras Conv2D(padding='same') forward on tensor cores.  x: bf16 tensor or MultiSource."""
+    srcs = _sources_of(x)
+    N, H, W = srcs[0].t.shape[:3]
+    KH, KW, Cin, Cout = w_hwio.shape
+    Ho, pt, _ = F.same_pad(H, KH, stride)
+    Wo, pl, _ = F.same_pad(W, KW, stride)
+    segs, kb = [], 0
+    for s in srcs:
+        segs.append((s.ci0, s.valid, kb))
+        kb += _ceil(s.t.shape[-1], 64)
+    n_mma = _ceil(Cout, 16)
+    wp = pack_weights(w_hwio, segs, n_mma, kb, transpose=False)
+    out = torch.empty((N, Ho, Wo, Cout), dtype=out_dtype, device=w_hwio.device)
+    return tc_run(srcs, wp, n_mma, Cout, N, H, W, Ho, Wo, KH, KW, stride, pt, pl, +1, out, bias=bias, act=act, add=add)
+
+
+def zero_upsample2(dy, H, W):
+    N, Ho, Wo, Cc = dy.shape
+    out = torch.empty((N, H, W, Cc), dtype=dy.dtype, device=dy.device)
+    L.check(L.load().of_zero_upsample2(L.ptr(dy), L.ptr(out), N, Ho, Wo, H, W, Cc, L.dtype_code(dy), L.stream_ptr()),
+            "of_zero_upsample2")
+    return out
+
+
+def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloat16, mask=None,
+                    mask_act=L.OF_ACT_NONE, out_channels=None):
+    """dx for input channels [seg[0], seg[0]+seg[1]) (default: all).  dz: bf16 (N,Ho,Wo,Cout).
+    stride 2 is handled by zero-insertion of dz followed by the stride-1 kernel."""
+    KH, KW, Cin, Cout = w_hwio.shape
+    H, W = in_hw
+    N = dz.shape[0]
+    _, pt, _ = F.same_pad(H, KH, stride)
+    _, pl, _ = F.same_pad(W, KW, stride)
+    if stride == 2:
+        dz = zero_upsample2(dz, H, W)
+    ci0, cnt = seg if seg is not None else (0, Cin)
+    n_out = out_channels or cnt
+    n_mma = _ceil(n_out, 16)
+    kpad = _ceil(dz.shape[-1], 64)
+    wp = pack_weights(w_hwio, [(ci0, cnt, 0)], n_mma, kpad, transpose=True)
+    out = torch.empty((N, H, W, n_out), dtype=out_dtype, device=dz.device)
+    return tc_run([Source(dz)], wp, n_mma, n_out, N, H, W, H, W, KH, KW, 1, pt, pl, -1, out, mask=mask, mask_act=mask_act)
+
+
+def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=True):
+    srcs = _sources_of(x)
+    N, H, W = srcs[0].t.shape[:3]
+    KH, KW = ksize
+    Cout = dz.shape[-1]
+    Cin = sum(s.valid for s in srcs)
+    Ho, pt, _ = F.same_pad(H, KH, stride)
+    Wo, pl, _ = F.same_pad(W, KW, stride)
+    assert tuple(dz.shape[:3]) == (N, Ho, Wo) and dz.dtype == torch.bfloat16
+    if dw is None:
+        dw = torch.empty((KH, KW, Cin, Cout), dtype=torch.float32, device=dz.device)
+    d = L.TcWgrad()
+    for k, s in enumerate(srcs):
+        d.x[k] = s.t.data_ptr()
+        d.x_c[k] = s.t.shape[-1]
+        d.x_stride[k] = s.t.shape[-1]
+        d.x_valid[k] = s.valid
+        d.x_ci0[k] = s.ci0
+    d.num_src = len(srcs)
+    d.dy, d.dy_c, d.dy_stride = dz.data_ptr(), Cout, Cout
+    d.dw = dw.data_ptr()
+    d.N, d.H, d.W, d.Ho, d.Wo = N, H, W, Ho, Wo
+    d.KH, d.KW, d.stride, d.pad_t, d.pad_l, d.Cin, d.Cout = KH, KW, stride, pt, pl, Cin, Cout
+    L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad")
+    if need_bias_grad:
+        if db is None:
+            db = torch.empty((Cout,), dtype=torch.float32, device=dz.device)
+        L.check(L.load().of_colsum(L.ptr(dz), L.ptr(db), N * Ho * Wo, Cout, Cout, L.dtype_code(dz), L.stream_ptr()),
+                "of_colsum")
+    return dw, db
+
+
+# --------------------------------------------------------------------- backend --
+
+class Bf16Backend:
+    """FlowNet convolution back-end: bf16 activations, tcgen05 kernels."""
+    act_dtype = torch.bfloat16
+
+    def __init__(self, net):
+        self.net = net
+
+    @staticmethod
+    def _tc_ok(layer):
+        return layer.cin >= 32 and layer.cout >= 16
+
+    def fprop(self, layer, x, w, b):
+        if layer.cin < 32:          # conv1 (Cin = 3): fp32 image in, bf16 out, SIMT
+            return F.conv2d_fprop(x, w, b, stride=layer.stride, act=layer.act, out_dtype=torch.bfloat16)
+        out_dtype = torch.float32 if layer.cout < 16 else torch.bfloat16     # flow heads stay fp32
+        return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype)
+
+    def act_bwd(self, layer, y, dy):
+        if layer.act == L.OF_ACT_NONE:
+            return dy
+        return F.act_bwd(y, dy, layer.act)
+
+    def wgrad(self, layer, x, dz, dw, db):
+        if self._tc_ok(layer):
+            conv2d_wgrad_tc(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
+        else:
+            assert not isinstance(x, MultiSource)
+            F.conv2d_wgrad(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
+
+    def dgrad(self, layer, dz, w, in_hw, chain=None):
+        """Returns dx; with `chain` (the ConvLayer producing this layer's input, sole consumer)
+        the epilogue multiplies by act'(chain.y) and the result is already chain's dz."""
+        x = layer.x
+        if not self._tc_ok(layer):                       # flow heads: dz is the fp32 d_flow
+            return F.conv2d_dgrad(dz, w, in_hw, stride=layer.stride, out_dtype=torch.bfloat16)
+        mask = mask_act = None
+        if chain is not None and chain.act != L.OF_ACT_NONE:
+            mask, mask_act = chain.y, chain.act
+            chain.incoming_is_dz = True
+        if isinstance(x, MultiSource):
+            outs = []
+            for s in x.sources:
+                n_out = s.t.shape[-1]                    # padded channels of the cv/flow buffer get zeros
+                dt = torch.float32 if s.ci0 == 0 else torch.bfloat16
+                outs.append(conv2d_dgrad_tc(dz, w, in_hw, 1, seg=(s.ci0, s.valid), out_dtype=dt, out_channels=n_out))
+            return tuple(outs)
+        return conv2d_dgrad_tc(dz, w, in_hw, layer.stride, out_dtype=torch.bfloat16, mask=mask,
+                               mask_act=mask_act if mask is not None else L.OF_ACT_NONE)
+
+    # concat [features1, cost_volume, flow_up] (model.py:97-102) as two K-sources
+    def concat_fwd(self, fm, f1, f2w, flow_up):
+        net = self.net
+        B, h, w, Cc = f1.shape
+        cvflow = net.zero_buf("cvflow%d" % fm.level, (B, h, w, 64), torch.bfloat16)
+        L.check(L.load().of_cost_volume_fwd(L.ptr(f1), L.ptr(f2w), L.ptr(cvflow), B, h, w, Cc, net.max_disp, 64,
+                                            L.OF_BF16, L.stream_ptr()), "of_cost_volume_fwd")
+        valid = fm.ncv
+        if flow_up is not None:
+            L.check(L.load().of_copy_channels(L.ptr(flow_up), 2, cvflow.data_ptr() + fm.ncv * 2, 64, 2, B * h * w,
+                                              L.OF_F32, L.OF_BF16, 0, L.stream_ptr()), "of_copy_channels")
+            valid += 2
+        fm.cvflow = cvflow
+        return MultiSource([Source(f1, Cc, 0), Source(cvflow, valid, Cc)])
+
+    def concat_bwd(self, fm, d):
+        d_f1, d_cvflow = d                               # fp32 (B,h,w,C), bf16 (B,h,w,64)
+        B, h, w, Cc = d_f1.shape
+        net = self.net
+        d_f1_b = torch.empty_like(d_f1)
+        d_f2w = torch.empty_like(d_f1)
+        L.check(L.load().of_cost_volume_bwd(L.ptr(fm.f1), L.ptr(fm.f2w), L.ptr(d_cvflow), L.ptr(d_f1_b), L.ptr(d_f2w),
+                                            B, h, w, Cc, net.max_disp, 64, L.OF_BF16, L.stream_ptr()),
+                "of_cost_volume_bwd")
+        n = d_f1.numel()
+        L.check(L.load().of_copy_channels(L.ptr(d_f1_b), 4, L.ptr(d_f1), 4, 4, n // 4, L.OF_F32, L.OF_F32, 1,
+                                          L.stream_ptr()), "of_copy_channels(acc)")
+        d_flow_up = None
+        if fm.has_prev:
+            d_flow_up = torch.empty((B, h, w, 2), dtype=torch.float32, device=d_f1.device)
+            L.check(L.load().of_copy_channels(d_cvflow.data_ptr() + fm.ncv * 2, 64, L.ptr(d_flow_up), 2, 2, B * h * w,
+                                              L.OF_BF16, L.OF_F32, 0, L.stream_ptr()), "of_copy_channels")
+        return d_f1, d_f2w, d_flow_up

@@ -169,13 +169,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(FA fa, FB fb, EPI epi, i
 // gridDim.y CTAs share the pixel range)
 template <typename TY>
 __global__ void __launch_bounds__(256) colsum_kernel(const TY* __restrict__ dy, float* __restrict__ db,
-                                                     size_t P, int C) {
+                                                     size_t P, int C, int ld = 0) {
+  if (ld == 0) ld = C;
   __shared__ float s[8][33];
   int c = blockIdx.x * 32 + (threadIdx.x & 31);
   int row = threadIdx.x >> 5;
   float acc = 0.f;
   if (c < C)
-    for (size_t p = (size_t)blockIdx.y * 8 + row; p < P; p += (size_t)gridDim.y * 8) acc += ldg_as_f<TY>(dy + p * C + c);
+    for (size_t p = (size_t)blockIdx.y * 8 + row; p < P; p += (size_t)gridDim.y * 8) acc += ldg_as_f<TY>(dy + p * ld + c);
   s[row][threadIdx.x & 31] = acc;
   __syncthreads();
   if (row == 0 && c < C) {
@@ -285,6 +286,22 @@ int of_conv2d_wgrad(const void* x, const void* dy, float* dw, float* db, int N, 
     return of_launch_check("colsum_kernel");
   }
   return 0;
+}
+
+int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int dtype, void* stream) {
+  OF_REQUIRE(dy && db, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype) && C > 0 && dy_stride >= C && npix > 0, OF_ERR_ARG, "bad colsum arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  OF_CUDA(cudaMemsetAsync(db, 0, (size_t)C * sizeof(float), st));
+  int gx = (C + 31) / 32;
+  int gy = (OF_NUM_SMS * 4 + gx - 1) / gx;
+  if ((size_t)gy * 8 > npix) gy = (int)((npix + 7) / 8);
+  dim3 cg(gx, gy);
+  if (dtype == OF_F32)
+    colsum_kernel<float><<<cg, 256, 0, st>>>((const float*)dy, db, npix, C, dy_stride);
+  else
+    colsum_kernel<__nv_bfloat16><<<cg, 256, 0, st>>>((const __nv_bfloat16*)dy, db, npix, C, dy_stride);
+  return of_launch_check("colsum_kernel");
 }
 
 }  // extern "C"

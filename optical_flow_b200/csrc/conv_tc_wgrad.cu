@@ -1,0 +1,255 @@
+// K10 (wgrad): weight gradient of Conv2D as a tcgen05 / TMEM GEMM with the PIXELS as the
+// reduction dimension:  dW[tap][ci][co] = sum_pix x[pix (+) tap][ci] * dy[pix][co].
+//
+// Both operands are NHWC activations, i.e. "MN-major" for this GEMM (the contiguous run is
+// channels = M for x / N for dy; K = pixels runs over 128-byte rows).  A TMA box
+// {64 channels, TWk, THk, 1} (TWk*THk = 64 pixels) lands in shared memory as 64 K-rows x 128 B
+// with SWIZZLE_128B, exactly the canonical MN-major UMMA operand; the x box is shifted by the
+// filter tap (zero fill outside the image == SAME padding, elementStrides for stride 2).
+// One CTA owns 128 input channels (two 64-channel chunks, possibly from two tensors - the
+// decoder concat), all Cout columns, a group of taps (one TMEM accumulator per tap: the dy
+// tile is loaded once per K step and reused by every tap) and a slice of the pixel range
+// (split-K).  Partial results are reduced into dW with red.global.add.f32.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+#define WG_THREADS 192
+#define WG_CHUNK_BYTES 8192   // 64 pixels x 64 bf16
+#define WG_MAX_TAPS 9
+
+int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long stride_elems, int N, int H, int W,
+                       int box_w, int box_h, int estride);
+
+#define WG_MAX_CHUNKS 16
+#define WG_MAX_JOBS 48
+struct WgradParams {
+  // 64-channel chunks of the (concatenated) input; M tile m uses chunks 2m and 2m+1
+  int chunk_map[WG_MAX_CHUNKS];   // which x tensor map (0/1); -1 = none (zero)
+  int chunk_c0[WG_MAX_CHUNKS];    // channel coordinate inside that tensor
+  int chunk_ci[WG_MAX_CHUNKS];    // original ci of the chunk's first channel
+  int chunk_cnt[WG_MAX_CHUNKS];   // valid channels in the chunk
+  // job (blockIdx.y) = (M tile, tap group)
+  int job_mt[WG_MAX_JOBS], job_tap0[WG_MAX_JOBS], job_ntaps[WG_MAX_JOBS];
+  int KW, pad_t, pad_l, stride;
+  int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
+  int ktiles, ktiles_per_split;
+  int n_mma, n_valid, n_chunks;   // dy: MMA N, real Cout, 64-channel chunks
+  int Cin, Cout;
+  int stages, stage_bytes, tmem_cols;
+  float* dw;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                     const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ WgradParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + (size_t)P.stages * P.stage_bytes);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* acc_full = empty_bar + 8;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    tc::mbar_init(acc_full, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
+  if (warp == 5) { tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols); tc::tmem_relinquish(); }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  const int job = blockIdx.y;
+  const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
+  const int k_begin = blockIdx.x * P.ktiles_per_split;
+  const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
+  const int a_bytes = ntaps * 2 * WG_CHUNK_BYTES;
+  const int tx_bytes = a_bytes + P.n_chunks * WG_CHUNK_BYTES;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int kt = k_begin; kt < k_end; ++kt) {
+        int tw_i = kt % P.tiles_w; int r = kt / P.tiles_w;
+        int th_i = r % P.tiles_h; int n = r / P.tiles_h;
+        int w0 = tw_i * P.TW, h0 = th_i * P.TH;
+        tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
+        tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
+        for (int t = 0; t < ntaps; ++t) {
+          int tap = tap0 + t;
+          int kh = tap / P.KW, kw = tap - kh * P.KW;
+          int cw = w0 * P.stride + kw - P.pad_l, ch = h0 * P.stride + kh - P.pad_t;
+          for (int c = 0; c < 2; ++c) {
+            // a chunk with no source reads channel coordinate far outside the tensor -> TMA zero fill
+            const int cm = P.chunk_map[mt * 2 + c];
+            const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
+            int cc = cm < 0 ? (1 << 20) : P.chunk_c0[mt * 2 + c];
+            tc::tma_load_4d(base + (size_t)(t * 2 + c) * WG_CHUNK_BYTES, tm, &full_bar[stage], cc, cw, ch, n);
+          }
+        }
+        for (int c = 0; c < P.n_chunks; ++c)
+          tc::tma_load_4d(base + a_bytes + (size_t)c * WG_CHUNK_BYTES, &tmDY, &full_bar[stage], c * 64, w0, h0, n);
+        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 5) {
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 1, 1);
+      int stage = 0; uint32_t phase = 0;
+      for (int kt = k_begin; kt < k_end; ++kt) {
+        tc::mbar_wait(&full_bar[stage], phase);
+        tc::fence_after_sync();
+        uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
+        uint32_t b_addr = base + (uint32_t)a_bytes;
+        for (int t = 0; t < ntaps; ++t) {
+          uint32_t a_addr = base + (uint32_t)(t * 2 * WG_CHUNK_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            // 16 pixels (K) per MMA = 16 rows of 128 B = 2048 B
+            uint64_t adesc = tc::desc_sw128_mnmajor(a_addr + k * 2048, WG_CHUNK_BYTES);
+            uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
+            tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
+          }
+        }
+        tc::mma_commit(&empty_bar[stage]);
+        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+      }
+      tc::mma_commit(acc_full);
+    }
+  } else {
+    // epilogue: row = input channel (M), columns = output channels
+    const bool has_work = k_end > k_begin;
+    if (has_work) {
+      tc::mbar_wait(acc_full, 0);
+      tc::fence_after_sync();
+      int row = warp * 32 + lane;
+      int c = mt * 2 + (row >> 6), rc = row & 63;
+      bool valid = P.chunk_map[c] >= 0 && rc < P.chunk_cnt[c];
+      int ci = P.chunk_ci[c] + rc;
+      const bool vec4 = (P.Cout % 4) == 0;
+      for (int t = 0; t < ntaps; ++t) {
+        float* dst_row = P.dw + ((size_t)(tap0 + t) * P.Cin + (valid ? ci : 0)) * P.Cout;
+        uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * P.n_mma);
+        for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
+          __syncwarp();
+          uint32_t rr[16];
+          tc::tmem_ld16(taddr + (uint32_t)c0, rr);
+          tc::tmem_ld_wait();
+          if (valid && c0 < P.n_valid) {
+            int nv = min(16, P.n_valid - c0);
+            if (vec4 && nv == 16) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                red_add_v4(dst_row + c0 + 4 * j,
+                           make_float4(__uint_as_float(rr[4 * j]), __uint_as_float(rr[4 * j + 1]),
+                                       __uint_as_float(rr[4 * j + 2]), __uint_as_float(rr[4 * j + 3])));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < nv) red_add(dst_row + c0 + j, __uint_as_float(rr[j]));
+            }
+          }
+        }
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 5) tc::tmem_dealloc(tmem_base, (uint32_t)P.tmem_cols);
+}
+
+extern "C" {
+
+int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
+  OF_REQUIRE(c && c->x[0] && c->dy && c->dw, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");
+  OF_REQUIRE(c->stride == 1 || c->stride == 2, OF_ERR_UNSUPPORTED, "stride %d unsupported", c->stride);
+  OF_REQUIRE(c->Cout >= 1 && c->Cout <= 256 && c->dy_c >= c->Cout, OF_ERR_SHAPE, "Cout %d unsupported", c->Cout);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int taps = c->KH * c->KW;
+  OF_CUDA(cudaMemsetAsync(c->dw, 0, (size_t)taps * c->Cin * c->Cout * sizeof(float), st));
+
+  WgradParams P;
+  memset(&P, 0, sizeof(P));
+  P.KW = c->KW; P.pad_t = c->pad_t; P.pad_l = c->pad_l; P.stride = c->stride;
+  P.NB = c->N; P.Ho = c->Ho; P.Wo = c->Wo;
+  const int cands[4] = {16, 32, 8, 64};
+  P.TW = 16; P.TH = 4;
+  for (int k = 0; k < 4; ++k)
+    if (c->Wo % cands[k] == 0) { P.TW = cands[k]; P.TH = 64 / cands[k]; break; }
+  P.tiles_w = (c->Wo + P.TW - 1) / P.TW;
+  P.tiles_h = (c->Ho + P.TH - 1) / P.TH;
+  long long kt = (long long)c->N * P.tiles_w * P.tiles_h;
+  OF_REQUIRE(kt > 0 && kt < (1ll << 30), OF_ERR_SHAPE, "bad pixel tiling");
+  P.ktiles = (int)kt;
+  P.n_valid = c->Cout;
+  P.n_mma = (c->Cout + 15) / 16 * 16;
+  P.n_chunks = (P.n_mma + 63) / 64;
+  P.Cin = c->Cin; P.Cout = c->Cout;
+  P.dw = c->dw;
+  int tpp = 512 / P.n_mma;              // taps per pass: one TMEM accumulator (n_mma columns) per tap
+  if (tpp > taps) tpp = taps;
+  // keep >= 2 pipeline stages inside 200 KB of shared memory
+  while (tpp > 1 && 2 * (tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES) > 200 * 1024) --tpp;
+  int passes = (taps + tpp - 1) / tpp;
+  tpp = (taps + passes - 1) / passes;   // balance the groups
+
+  CUtensorMap tmX[2], tmDY;
+  memset(tmX, 0, sizeof(tmX));
+  for (int s = 0; s < c->num_src; ++s)
+    if (int r = of_tc_make_act_map(&tmX[s], c->x[s], c->x_c[s], c->x_stride[s], c->N, c->H, c->W, P.TW, P.TH, c->stride))
+      return r;
+  if (c->num_src == 1) tmX[1] = tmX[0];
+  if (int r = of_tc_make_act_map(&tmDY, c->dy, c->dy_c, c->dy_stride, c->N, c->Ho, c->Wo, P.TW, P.TH, 1)) return r;
+
+  // list of 64-channel chunks over the sources (original ci offsets follow the concat order)
+  int nch = 0;
+  for (int k = 0; k < WG_MAX_CHUNKS; ++k) P.chunk_map[k] = -1;
+  for (int s = 0; s < c->num_src; ++s)
+    for (int c0 = 0; c0 < c->x_c[s]; c0 += 64) {
+      int valid_c = c->x_valid[s] - c0;
+      if (valid_c <= 0) break;
+      OF_REQUIRE(nch < WG_MAX_CHUNKS, OF_ERR_SHAPE, "too many input channels");
+      P.chunk_map[nch] = s; P.chunk_c0[nch] = c0; P.chunk_ci[nch] = c->x_ci0[s] + c0;
+      P.chunk_cnt[nch] = valid_c < 64 ? valid_c : 64;
+      ++nch;
+    }
+  static bool attr_set = false;
+  if (!attr_set) {
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  int m_tiles = (nch + 1) / 2;
+  int jobs = 0;
+  for (int mt = 0; mt < m_tiles; ++mt)
+    for (int p = 0; p < passes; ++p) {
+      int t0 = p * tpp;
+      int nt = taps - t0 < tpp ? taps - t0 : tpp;
+      if (nt <= 0) break;
+      OF_REQUIRE(jobs < WG_MAX_JOBS, OF_ERR_SHAPE, "too many wgrad jobs");
+      P.job_mt[jobs] = mt; P.job_tap0[jobs] = t0; P.job_ntaps[jobs] = nt;
+      ++jobs;
+    }
+  int splits = (2 * OF_NUM_SMS + jobs - 1) / jobs;   // ~2 waves so uneven jobs balance
+  if (splits > P.ktiles) splits = P.ktiles;
+  if (splits < 1) splits = 1;
+  P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
+  splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
+  P.stage_bytes = tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES;
+  P.stages = (200 * 1024) / P.stage_bytes;
+  if (P.stages > 8) P.stages = 8;
+  OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
+  int cols = tpp * P.n_mma;
+  P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+  size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + 17 * sizeof(uint64_t) + 16;
+  dim3 grid(splits, jobs);
+  conv_tc_wgrad_kernel<<<grid, WG_THREADS, smem, st>>>(tmX[0], tmX[1], tmDY, P);
+  if (int r = of_launch_check("conv_tc_wgrad_kernel")) return r;
+  return 0;
+}
+
+}  // extern "C"

@@ -92,7 +92,39 @@ __global__ void __launch_bounds__(256) bn_fold_bwd_kernel(const float* __restric
   }
 }
 
+// zero-insertion x2 (stride-2 dgrad = stride-1 dgrad of the zero-upsampled dy)
+template <typename T>
+__global__ void __launch_bounds__(256) zero_upsample2_kernel(const T* __restrict__ dy, T* __restrict__ out, int N,
+                                                             int Ho, int Wo, int H, int W, int C4) {
+  size_t total = (size_t)N * H * W * C4;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int c = (int)(e % C4);
+    size_t r = e / C4;
+    int w = (int)(r % W); r /= W;
+    int h = (int)(r % H);
+    int n = (int)(r / H);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!(h & 1) && !(w & 1) && (h >> 1) < Ho && (w >> 1) < Wo)
+      v = ld4<T>(dy + ((((size_t)n * Ho + (h >> 1)) * Wo + (w >> 1)) * C4 + c) * 4);
+    st4<T>(out + e * 4, v);
+  }
+}
+
 extern "C" {
+
+int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,
+                      void* stream) {
+  OF_REQUIRE(dy && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(N > 0 && Ho > 0 && Wo > 0 && H > 0 && W > 0 && C > 0 && C % 4 == 0, OF_ERR_SHAPE, "bad dims");
+  OF_REQUIRE(of_valid_dtype(dtype), OF_ERR_ARG, "bad dtype");
+  size_t total = (size_t)N * H * W * (C / 4);
+  if (dtype == OF_F32)
+    zero_upsample2_kernel<float><<<g_grid(total), 256, 0, (cudaStream_t)stream>>>((const float*)dy, (float*)out, N, Ho, Wo, H, W, C / 4);
+  else
+    zero_upsample2_kernel<__nv_bfloat16><<<g_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (__nv_bfloat16*)out, N, Ho, Wo, H, W, C / 4);
+  return of_launch_check("zero_upsample2_kernel");
+}
 
 int of_split_image_pair(const float* imgs, void* out, int B, int H, int W, int out_dtype, void* stream) {
   OF_REQUIRE(imgs && out, OF_ERR_ARG, "null pointer argument");

@@ -74,6 +74,8 @@ class ConvLayer:
         self.k, self.cin, self.cout, self.stride, self.act, self.bn = ksize, cin, cout, stride, act, bn
         self.use_bias = use_bias
         self.x = self.y = None
+        self.prev_chain = None         # ConvLayer whose output is exactly this layer's input (sole consumer)
+        self.incoming_is_dz = False    # set by a fused dgrad epilogue: dy already multiplied by act'(y)
 
     # parameters (views into the flat buffers)
     def _p(self, suffix):
@@ -108,7 +110,10 @@ class ConvLayer:
     def backward(self, dy, need_dx=True):
         """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None."""
         net = self.net
-        dz = net.backend.act_bwd(self, self.y, dy)
+        if self.incoming_is_dz:
+            dz, self.incoming_is_dz = dy, False
+        else:
+            dz = net.backend.act_bwd(self, self.y, dy)
         if self.bn is None:
             dw = self._g("/kernel")
             db = self._g("/bias") if self.use_bias else None
@@ -128,7 +133,7 @@ class ConvLayer:
                 "of_bn_fold_bwd")
         if not need_dx:
             return None
-        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]))
+        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self.prev_chain)
 
 
 class Fp32Backend:
@@ -149,7 +154,7 @@ class Fp32Backend:
     def wgrad(self, layer, x, dz, dw, db):
         F.conv2d_wgrad(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
 
-    def dgrad(self, layer, dz, w, in_hw):
+    def dgrad(self, layer, dz, w, in_hw, chain=None):
         return F.conv2d_dgrad(dz, w, in_hw, stride=layer.stride, out_dtype=torch.float32)
 
 
@@ -164,6 +169,7 @@ class ResnetBlock:
         self.conv1 = ConvLayer(net, base + "_conv1", 3, cin, cout, s, L.OF_ACT_RELU, bn=base + "_bn1")
         self.conv2 = ConvLayer(net, base + "_conv2", 3, cout, cout, 1, L.OF_ACT_RELU, bn=base + "_bn2")
         self.shortcut = ConvLayer(net, base + "_shortcut", 1, cin, cout, 2, L.OF_ACT_NONE, use_bias=False) if downsample else None
+        self.conv2.prev_chain = self.conv1
 
     def forward(self, x):
         self.x = x
@@ -237,6 +243,8 @@ class FlowModule:
         for ci, cout in enumerate(DECODER_WIDTHS):
             act = L.OF_ACT_LEAKY if ci < 5 else L.OF_ACT_NONE      # LeakyReLU() alpha 0.3
             self.convs.append(ConvLayer(net, "flow%d_conv%d" % (level, ci + 1), 3, cin, cout, 1, act))
+            if ci > 0:
+                self.convs[ci].prev_chain = self.convs[ci - 1]
             cin = cout
 
     def forward(self, features1, features2, previous_flow):
@@ -264,7 +272,7 @@ class FlowModule:
         """d_flow: f32 gradient w.r.t. this level's flow.  Returns (d_f1, d_f2, d_prev_flow),
         d_f1/d_f2 float32."""
         net = self.net
-        d = net.to_act_dtype(d_flow)
+        d = d_flow                      # the flow head has no activation: its dz is the fp32 d_flow
         for conv in reversed(self.convs):
             d = conv.backward(d)
         d_f1, d_f2w, d_flow_up = net.backend_concat_bwd(self, d)
@@ -312,6 +320,14 @@ class FlowNet:
         t = self._bufs.get(key)
         if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
             t = torch.empty(tuple(shape), dtype=dtype, device=self.device)
+            self._bufs[key] = t
+        return t
+
+    def zero_buf(self, key, shape, dtype):
+        """Persistent buffer zero-filled once at allocation (padding channels stay zero)."""
+        t = self._bufs.get(key)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.zeros(tuple(shape), dtype=dtype, device=self.device)
             self._bufs[key] = t
         return t
 

@@ -1,0 +1,224 @@
+"""GPU parity of the tcgen05 / TMEM implicit-GEMM convolutions (conv_tc.cu, conv_tc_wgrad.cu)
+through the C ABI, against torch-CPU fp32 convolution on the SAME bf16-rounded operands.
+
+Stated bf16 tolerance for the conv path: operands are rounded to bf16 (2^-8 relative),
+products accumulate in fp32 (TMEM).  With identical bf16 inputs the only differences are
+accumulation order (fp32) and, for bf16 outputs, the final rounding:
+  fp32 outputs : max|err| <= 2e-4 * max|ref|
+  bf16 outputs : max|err| <= 2^-7 * max|ref|
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_torch as T
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_round(a):
+    return torch.tensor(a).bfloat16().float().numpy()
+
+
+def rel_err(got, exp):
+    got = got.detach().float().cpu().numpy() if isinstance(got, torch.Tensor) else got
+    return float(np.abs(got - exp).max()) / max(float(np.abs(exp).max()), 1e-30)
+
+
+def make(cfg, seed):
+    N, H, W, Cin, K, Cout, s = cfg
+    r = np.random.default_rng(seed)
+    x = bf16_round(r.standard_normal((N, H, W, Cin)).astype(np.float32))
+    w = bf16_round((r.standard_normal((K, K, Cin, Cout)) / np.sqrt(K * K * Cin)).astype(np.float32))
+    b = r.standard_normal((Cout,)).astype(np.float32)
+    return x, w, b
+
+
+FPROP_CASES = [
+    (2, 24, 32, 64, 3, 64, 1),
+    (1, 16, 48, 128, 3, 96, 1),
+    (1, 9, 13, 64, 3, 32, 1),        # partial tiles in both directions
+    (2, 24, 32, 64, 3, 128, 2),      # stride 2, TF SAME pad (0,1)
+    (1, 24, 32, 64, 1, 128, 2),      # 1x1 / 2 shortcut
+    (1, 12, 16, 32, 3, 2, 1),        # flow head: Cout = 2 (N padded to 16), fp32 out
+    (1, 8, 16, 256, 3, 256, 1),      # N = 256: both TMEM buffers full width
+    (4, 96, 128, 64, 3, 64, 1),      # 384 tiles > 148 CTAs: persistent loop + TMEM double buffering
+    (1, 16, 16, 96, 3, 64, 1),       # K tail chunk: 96 = 64 + 32 (TMA zero-fills channels 96..127)
+]
+
+
+@pytest.mark.parametrize("cfg", FPROP_CASES)
+def test_tc_fprop(cuda, cfg):
+    from optical_flow_b200 import conv_tc, _lib as L
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 1)
+    ref = torch.nn.functional.leaky_relu(T.conv2d_same(torch.tensor(x), torch.tensor(w), torch.tensor(b), s), 0.3).numpy()
+    xd = torch.tensor(x, device=cuda).bfloat16()
+    out_dtype = torch.float32 if Cout < 16 else torch.bfloat16
+    y = conv_tc.conv2d_fprop_tc(xd, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), stride=s,
+                                act=L.OF_ACT_LEAKY, out_dtype=out_dtype)
+    assert tuple(y.shape) == ref.shape
+    tol = 2e-4 if out_dtype == torch.float32 else 2 ** -7
+    assert rel_err(y, ref) <= tol, rel_err(y, ref)
+
+
+def test_tc_fprop_fp32_out_is_tight(cuda):
+    """fp32 output isolates the MMA path: only accumulation order differs from the reference."""
+    from optical_flow_b200 import conv_tc, _lib as L
+    cfg = (2, 24, 32, 128, 3, 128, 1)
+    x, w, b = make(cfg, 2)
+    ref = T.conv2d_same(torch.tensor(x), torch.tensor(w), torch.tensor(b), 1).numpy()
+    y = conv_tc.conv2d_fprop_tc(torch.tensor(x, device=cuda).bfloat16(), torch.tensor(w, device=cuda),
+                                torch.tensor(b, device=cuda), out_dtype=torch.float32)
+    assert rel_err(y, ref) <= 2e-5, rel_err(y, ref)
+
+
+def test_tc_fprop_two_sources_concat(cuda):
+    """model.py:100-102 concat([f1, cost_volume, flow_up]) as two K-sources (never materialised)."""
+    from optical_flow_b200 import conv_tc, _lib as L
+    r = np.random.default_rng(3)
+    N, H, W, C = 1, 12, 16, 64
+    f1 = bf16_round(r.standard_normal((N, H, W, C)).astype(np.float32))
+    cvf = np.zeros((N, H, W, 64), np.float32)
+    cvf[..., :51] = bf16_round(r.standard_normal((N, H, W, 51)).astype(np.float32))
+    w = bf16_round((r.standard_normal((3, 3, C + 51, 128)) / 30).astype(np.float32))
+    b = r.standard_normal((128,)).astype(np.float32)
+    xcat = np.concatenate([f1, cvf[..., :51]], axis=-1)
+    ref = T.conv2d_same(torch.tensor(xcat), torch.tensor(w), torch.tensor(b), 1).numpy()
+    ms = conv_tc.MultiSource([conv_tc.Source(torch.tensor(f1, device=cuda).bfloat16(), C, 0),
+                              conv_tc.Source(torch.tensor(cvf, device=cuda).bfloat16(), 51, C)])
+    y = conv_tc.conv2d_fprop_tc(ms, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), out_dtype=torch.float32)
+    assert rel_err(y, ref) <= 2e-5, rel_err(y, ref)
+
+
+DGRAD_CASES = [
+    (2, 24, 32, 64, 3, 64, 1),
+    (1, 16, 48, 128, 3, 96, 1),
+    (1, 9, 13, 64, 3, 32, 1),
+    (2, 24, 32, 64, 3, 128, 2),
+    (1, 24, 32, 64, 1, 128, 2),
+    (1, 8, 16, 256, 3, 256, 1),
+]
+
+
+@pytest.mark.parametrize("cfg", DGRAD_CASES)
+def test_tc_dgrad(cuda, cfg):
+    from optical_flow_b200 import conv_tc, _lib as L
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 4)
+    xt, wt = torch.tensor(x, requires_grad=True), torch.tensor(w)
+    yt = T.conv2d_same(xt, wt, None, s)
+    r = np.random.default_rng(5)
+    g = bf16_round(r.standard_normal(tuple(yt.shape)).astype(np.float32))
+    yt.backward(torch.tensor(g))
+    ref = xt.grad.numpy()
+    dx = conv_tc.conv2d_dgrad_tc(torch.tensor(g, device=cuda).bfloat16(), torch.tensor(w, device=cuda), (H, W), s,
+                                 out_dtype=torch.float32)
+    assert rel_err(dx, ref) <= 2e-5, rel_err(dx, ref)
+    # fused activation-backward epilogue: dz_prev = dx * leaky'(y_prev), bf16 out
+    yprev = r.standard_normal((N, H, W, Cin)).astype(np.float32)
+    dz = conv_tc.conv2d_dgrad_tc(torch.tensor(g, device=cuda).bfloat16(), torch.tensor(w, device=cuda), (H, W), s,
+                                 out_dtype=torch.bfloat16, mask=torch.tensor(yprev, device=cuda).bfloat16(),
+                                 mask_act=L.OF_ACT_LEAKY)
+    ref2 = ref * np.where(bf16_round(yprev) > 0, 1.0, 0.3)
+    assert rel_err(dz, ref2) <= 2 ** -7
+
+
+def test_tc_dgrad_segments(cuda):
+    """dgrad of the first decoder conv: one launch per concat segment (features | cv+flow)."""
+    from optical_flow_b200 import conv_tc
+    r = np.random.default_rng(6)
+    N, H, W, C, Cout = 1, 12, 16, 64, 128
+    w = bf16_round((r.standard_normal((3, 3, C + 51, Cout)) / 30).astype(np.float32))
+    xt = torch.zeros((N, H, W, C + 51), requires_grad=True)
+    yt = T.conv2d_same(xt, torch.tensor(w), None, 1)
+    g = bf16_round(r.standard_normal(tuple(yt.shape)).astype(np.float32))
+    yt.backward(torch.tensor(g))
+    ref = xt.grad.numpy()
+    gd, wd = torch.tensor(g, device=cuda).bfloat16(), torch.tensor(w, device=cuda)
+    d_f1 = conv_tc.conv2d_dgrad_tc(gd, wd, (H, W), 1, seg=(0, C), out_dtype=torch.float32)
+    d_cv = conv_tc.conv2d_dgrad_tc(gd, wd, (H, W), 1, seg=(C, 51), out_dtype=torch.float32, out_channels=64)
+    assert rel_err(d_f1, ref[..., :C]) <= 2e-5
+    assert rel_err(d_cv[..., :51], ref[..., C:]) <= 2e-5
+    assert float(d_cv[..., 51:].abs().max()) == 0.0
+
+
+WGRAD_CASES = [
+    (2, 24, 32, 64, 3, 64, 1),
+    (1, 16, 48, 128, 3, 96, 1),
+    (1, 9, 13, 64, 3, 32, 1),
+    (2, 24, 32, 64, 3, 128, 2),
+    (1, 24, 32, 64, 1, 128, 2),
+    (1, 8, 16, 256, 3, 256, 1),
+    (1, 16, 16, 96, 3, 64, 1),
+    (2, 96, 128, 128, 3, 128, 1),    # long pixel reduction, several split-K slices
+]
+
+
+@pytest.mark.parametrize("cfg", WGRAD_CASES)
+def test_tc_wgrad(cuda, cfg):
+    from optical_flow_b200 import conv_tc
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 7)
+    xt, wt, bt = torch.tensor(x), torch.tensor(w, requires_grad=True), torch.tensor(b, requires_grad=True)
+    yt = T.conv2d_same(xt, wt, bt, s)
+    r = np.random.default_rng(8)
+    g = bf16_round(r.standard_normal(tuple(yt.shape)).astype(np.float32))
+    yt.backward(torch.tensor(g))
+    dw, db = conv_tc.conv2d_wgrad_tc(torch.tensor(x, device=cuda).bfloat16(), torch.tensor(g, device=cuda).bfloat16(),
+                                     (K, K), stride=s)
+    assert rel_err(dw, wt.grad.numpy()) <= 5e-5, rel_err(dw, wt.grad.numpy())
+    assert rel_err(db, bt.grad.numpy()) <= 5e-5
+
+
+def test_tc_wgrad_two_sources(cuda):
+    from optical_flow_b200 import conv_tc
+    r = np.random.default_rng(9)
+    N, H, W, C, Cout = 1, 12, 16, 128, 128
+    f1 = bf16_round(r.standard_normal((N, H, W, C)).astype(np.float32))
+    cvf = np.zeros((N, H, W, 64), np.float32)
+    cvf[..., :51] = bf16_round(r.standard_normal((N, H, W, 51)).astype(np.float32))
+    xcat = torch.tensor(np.concatenate([f1, cvf[..., :51]], axis=-1))
+    wt = torch.zeros((3, 3, C + 51, Cout), requires_grad=True)
+    yt = T.conv2d_same(xcat, wt, None, 1)
+    g = bf16_round(r.standard_normal(tuple(yt.shape)).astype(np.float32))
+    yt.backward(torch.tensor(g))
+    ms = conv_tc.MultiSource([conv_tc.Source(torch.tensor(f1, device=cuda).bfloat16(), C, 0),
+                              conv_tc.Source(torch.tensor(cvf, device=cuda).bfloat16(), 51, C)])
+    dw, _ = conv_tc.conv2d_wgrad_tc(ms, torch.tensor(g, device=cuda).bfloat16(), (3, 3), need_bias_grad=False)
+    assert rel_err(dw, wt.grad.numpy()) <= 5e-5
+
+
+# ------------------------------------------------------------------ whole network, bf16 mode --
+def test_bf16_train_step_vs_oracle(cuda):
+    """Full step with tensor-core convs vs the fp32 oracle.  Stated tolerance: loss within 2 %,
+    flows within 5 % of max-abs, gradient cosine similarity > 0.98 per large tensor (bf16 operand
+    rounding through ~20 stacked convs; warp indices can flip on isolated pixels)."""
+    from optical_flow_b200.loss import LossLayer
+    from optical_flow_b200.model import build_flow_net
+    B, H, W = 2, 64, 96
+    params, stats = T.init_params(seed=42, randomize_bn=True)
+    imgs = T.synthetic_pairs(B, H, W, seed=11)
+    ref = T.FlowNetRef(params, stats)
+    r_loss, r_flows, r_grads = ref.loss_and_grads(torch.tensor(imgs))
+    net = build_flow_net(H, W, None, conv_mode="bf16")
+    net.store.load_numpy(params, stats)
+    x = torch.tensor(imgs, device=cuda)
+    flows = net(x)
+    for f, e in zip(flows, r_flows):
+        assert f.dtype == torch.float32
+        assert rel_err(f, e.numpy()) < 5e-2, rel_err(f, e.numpy())
+    layer = LossLayer()
+    loss = layer(x, flows)
+    assert abs(loss.item() - r_loss.item()) < 2e-2 * abs(r_loss.item())
+    net.backward(layer.d_flows)
+    bad = []
+    for name, g in net.store.g.items():
+        e = r_grads[name].numpy().ravel()
+        gg = g.detach().cpu().numpy().ravel()
+        if e.size < 512 or np.linalg.norm(e) == 0:
+            continue
+        cos = float(np.dot(gg, e) / (np.linalg.norm(gg) * np.linalg.norm(e) + 1e-30))
+        if cos < 0.98:
+            bad.append((name, cos))
+    assert not bad, bad

@@ -116,10 +116,17 @@ def test_warp_bwd_smooth_flow_collisions(cuda):
     B, H, W, C = 2, 32, 48, 3
     r = rng(5)
     im = r.standard_normal((B, H, W, C)).astype(np.float32)
-    flow = np.full((B, H, W, 2), 0.3, np.float32) + (r.standard_normal((B, 1, 1, 2)) * 0.1).astype(np.float32)
-    flow[:, :, : W // 2] = 40.0      # everything clamps onto the border column/row: heavy collisions
+    base = np.full((B, H, W, 2), 0.3, np.float32) + (r.standard_normal((B, 1, 1, 2)) * 0.1).astype(np.float32)
     g = r.standard_normal((B, H, W, C)).astype(np.float32)
+    ii, jj = np.meshgrid(np.arange(H, dtype=np.float32), np.arange(W, dtype=np.float32), indexing="ij")
     for mode, bw in (("ref_ij", R.warp_features_bwd), ("xy", R.warp_xy_bwd)):
+        flow = base.copy()
+        # a 16x16 block whose pixels all sample the same in-range point: 256-way collisions
+        # (in range, so the reference's clipped-tap weights stay in [0,1]: no fp32 cancellation)
+        c0 = (ii if mode == "ref_ij" else jj)[8:24, 8:24]
+        c1 = (jj if mode == "ref_ij" else ii)[8:24, 8:24]
+        flow[:, 8:24, 8:24, 0] = 5.25 - c0
+        flow[:, 8:24, 8:24, 1] = 7.25 - c1
         e_im, e_flow = bw(flow, im, g)
         d_im, d_flow = F.warp_features_bwd(dev(flow, cuda), dev(im, cuda), dev(g, cuda), mode=mode)
         assert_close_maxrel(d_im, e_im, what="d_im " + mode)
