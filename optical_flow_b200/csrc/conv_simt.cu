@@ -187,6 +187,105 @@ __global__ void __launch_bounds__(256) colsum_kernel(const TY* __restrict__ dy, 
   }
 }
 
+// coalesced variant for C % 4 == 0, C <= 1024: each thread owns 4 channels of every ppp-th pixel
+// (a warp reads whole pixel rows, 8/16 bytes per lane), CTA-level reduction, one atomic per channel
+template <typename TY>
+__global__ void __launch_bounds__(256) colsum4_kernel(const TY* __restrict__ dy, float* __restrict__ db, size_t P,
+                                                      int C, int ld) {
+  const int cg = C >> 2, ppp = 256 / cg;
+  const int g = threadIdx.x % cg, pr = threadIdx.x / cg;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (pr < ppp) {
+    for (size_t p = (size_t)blockIdx.x * ppp + pr; p < P; p += (size_t)gridDim.x * ppp) {
+      float4 v = ld4<TY>(dy + p * ld + g * 4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  __shared__ float4 s[256];
+  s[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x < cg) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < ppp; ++r) {
+      float4 v = s[r * cg + threadIdx.x];
+      t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+    }
+    red_add(db + threadIdx.x * 4 + 0, t.x);
+    red_add(db + threadIdx.x * 4 + 1, t.y);
+    red_add(db + threadIdx.x * 4 + 2, t.z);
+    red_add(db + threadIdx.x * 4 + 3, t.w);
+  }
+}
+
+// wgrad for tiny Cout (the flow heads, Cout = 2): dw is only KH*KW*Cin x Cout, so a GEMM tile is
+// wasted.  One thread per weight row (tap, ci) (+1 thread for the bias), the CTA stages an input halo
+// tile and the dy tile in shared memory and every thread walks the tile's pixels; lanes = consecutive
+// ci -> conflict-free, dy is a broadcast.  Stride 1 only.
+#define SC_TH 8
+#define SC_TW 32
+template <typename TX, int COUT>
+__global__ void __launch_bounds__(1024) smallcout_wgrad_kernel(const TX* __restrict__ x, const float* __restrict__ dy,
+                                                               float* __restrict__ dw, float* __restrict__ db,
+                                                               ConvGeom g) {
+  extern __shared__ float sm[];
+  const int HH = SC_TH + g.KH - 1, HW = SC_TW + g.KW - 1;
+  float* xs = sm;                                   // [HH][HW][Cin]
+  float* dys = sm + (size_t)HH * HW * g.Cin;        // [SC_TH*SC_TW][COUT]
+  const int R = g.KH * g.KW * g.Cin;
+  const int r = threadIdx.x;
+  const int ci = r % g.Cin, tap = r / g.Cin;
+  const int kh = tap / g.KW, kw = tap % g.KW;
+  const int tiles_x = (g.W + SC_TW - 1) / SC_TW, tiles_y = (g.H + SC_TH - 1) / SC_TH;
+  const long long ntiles = (long long)g.N * tiles_x * tiles_y;
+  float acc[COUT];
+#pragma unroll
+  for (int c = 0; c < COUT; ++c) acc[c] = 0.f;
+  for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    int tx = (int)(t % tiles_x); long long q = t / tiles_x;
+    int ty = (int)(q % tiles_y); int n = (int)(q / tiles_y);
+    int y0 = ty * SC_TH, x0 = tx * SC_TW;
+    __syncthreads();
+    for (int e = threadIdx.x; e < HH * HW * g.Cin; e += blockDim.x) {
+      int c = e % g.Cin; int p = e / g.Cin;
+      int hx = p % HW, hy = p / HW;
+      int yy = y0 + hy - g.pt, xx = x0 + hx - g.pl;
+      float v = 0.f;
+      if (yy >= 0 && yy < g.H && xx >= 0 && xx < g.W)
+        v = ldg_as_f<TX>(x + (((size_t)n * g.H + yy) * g.W + xx) * g.Cin + c);
+      xs[e] = v;
+    }
+    for (int e = threadIdx.x; e < SC_TH * SC_TW * COUT; e += blockDim.x) {
+      int c = e % COUT; int p = e / COUT;
+      int yy = y0 + p / SC_TW, xx = x0 + p % SC_TW;
+      dys[e] = (yy < g.H && xx < g.W) ? __ldg(dy + (((size_t)n * g.H + yy) * g.W + xx) * COUT + c) : 0.f;
+    }
+    __syncthreads();
+    if (r < R) {
+      for (int py = 0; py < SC_TH; ++py) {
+        const float* xrow = xs + ((size_t)(py + kh) * HW + kw) * g.Cin + ci;
+        const float* drow = dys + (size_t)py * SC_TW * COUT;
+#pragma unroll 8
+        for (int px = 0; px < SC_TW; ++px) {
+          float xv = xrow[(size_t)px * g.Cin];
+#pragma unroll
+          for (int c = 0; c < COUT; ++c) acc[c] = fmaf(xv, drow[px * COUT + c], acc[c]);
+        }
+      }
+    } else if (r == R && db != nullptr) {
+      for (int p = 0; p < SC_TH * SC_TW; ++p)
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) acc[c] += dys[p * COUT + c];
+    }
+  }
+  if (r < R) {
+#pragma unroll
+    for (int c = 0; c < COUT; ++c) red_add(dw + (size_t)r * COUT + c, acc[c]);
+  } else if (r == R && db != nullptr) {
+#pragma unroll
+    for (int c = 0; c < COUT; ++c) red_add(db + c, acc[c]);
+  }
+}
+
 static int make_geom(ConvGeom* g, int N, int H, int W, int Cin, int KH, int KW, int Cout, int stride) {
   OF_REQUIRE(N > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && KH > 0 && KW > 0, OF_ERR_SHAPE, "bad conv dims");
   OF_REQUIRE(stride == 1 || stride == 2, OF_ERR_UNSUPPORTED, "stride %d unsupported", stride);
@@ -257,6 +356,24 @@ int of_conv2d_wgrad(const void* x, const void* dy, float* dw, float* db, int N, 
   int M = KH * KW * Cin, K = N * g.Ho * g.Wo;
   cudaStream_t st = (cudaStream_t)stream;
   OF_CUDA(cudaMemsetAsync(dw, 0, (size_t)M * Cout * sizeof(float), st));
+  if (Cout == 2 && stride == 1 && dy_dtype == OF_F32 && M + 1 <= 1024) {
+    // flow heads: dedicated small-Cout kernel (also produces db)
+    if (db) OF_CUDA(cudaMemsetAsync(db, 0, (size_t)Cout * sizeof(float), st));
+    int threads = (M + 1 + 31) / 32 * 32;
+    size_t smem = ((size_t)(SC_TH + KH - 1) * (SC_TW + KW - 1) * Cin + (size_t)SC_TH * SC_TW * 2) * sizeof(float);
+    if (smem <= 200 * 1024) {
+      long long ntiles = (long long)N * ((W + SC_TW - 1) / SC_TW) * ((H + SC_TH - 1) / SC_TH);
+      int grid = (int)(ntiles < 2 * OF_NUM_SMS ? ntiles : 2 * OF_NUM_SMS);
+      if (x_dtype == OF_F32) {
+        OF_CUDA(cudaFuncSetAttribute(smallcout_wgrad_kernel<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smallcout_wgrad_kernel<float, 2><<<grid, threads, smem, st>>>((const float*)x, (const float*)dy, dw, db, g);
+      } else {
+        OF_CUDA(cudaFuncSetAttribute(smallcout_wgrad_kernel<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smallcout_wgrad_kernel<__nv_bfloat16, 2><<<grid, threads, smem, st>>>((const __nv_bfloat16*)x, (const float*)dy, dw, db, g);
+      }
+      return of_launch_check("smallcout_wgrad_kernel");
+    }
+  }
   // split the pixel reduction so the grid covers the machine (~4 CTAs per SM)
   int tiles = ((M + BM - 1) / BM) * ((Cout + BN - 1) / BN);
   int splits = (OF_NUM_SMS * 4 + tiles - 1) / tiles;
@@ -273,18 +390,7 @@ int of_conv2d_wgrad(const void* x, const void* dy, float* dw, float* db, int N, 
   else { GO(__nv_bfloat16, __nv_bfloat16); }
 #undef GO
   if (rc) return rc;
-  if (db != nullptr) {
-    OF_CUDA(cudaMemsetAsync(db, 0, (size_t)Cout * sizeof(float), st));
-    int gx = (Cout + 31) / 32;
-    int gy = (OF_NUM_SMS * 4 + gx - 1) / gx;
-    if ((size_t)gy * 8 > (size_t)K) gy = (K + 7) / 8;
-    dim3 cg(gx, gy);
-    if (dy_dtype == OF_F32)
-      colsum_kernel<float><<<cg, 256, 0, st>>>((const float*)dy, db, (size_t)K, Cout);
-    else
-      colsum_kernel<__nv_bfloat16><<<cg, 256, 0, st>>>((const __nv_bfloat16*)dy, db, (size_t)K, Cout);
-    return of_launch_check("colsum_kernel");
-  }
+  if (db != nullptr) return of_colsum(dy, db, (size_t)K, Cout, Cout, dy_dtype, stream);
   return 0;
 }
 
@@ -293,6 +399,16 @@ int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int 
   OF_REQUIRE(of_valid_dtype(dtype) && C > 0 && dy_stride >= C && npix > 0, OF_ERR_ARG, "bad colsum arguments");
   cudaStream_t st = (cudaStream_t)stream;
   OF_CUDA(cudaMemsetAsync(db, 0, (size_t)C * sizeof(float), st));
+  if (C % 4 == 0 && C <= 1024 && dy_stride % 4 == 0) {
+    int ppp = 256 / (C / 4);
+    size_t blocks = (npix + ppp - 1) / ppp;
+    if (blocks > (size_t)OF_NUM_SMS * 8) blocks = (size_t)OF_NUM_SMS * 8;
+    if (dtype == OF_F32)
+      colsum4_kernel<float><<<(int)blocks, 256, 0, st>>>((const float*)dy, db, npix, C, dy_stride);
+    else
+      colsum4_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, db, npix, C, dy_stride);
+    return of_launch_check("colsum4_kernel");
+  }
   int gx = (C + 31) / 32;
   int gy = (OF_NUM_SMS * 4 + gx - 1) / gx;
   if ((size_t)gy * 8 > npix) gy = (int)((npix + 7) / 8);

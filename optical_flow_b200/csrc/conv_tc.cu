@@ -54,6 +54,40 @@ __device__ __forceinline__ float act_slope(float y, int act) {
   return 1.f;
 }
 
+// 16 consecutive channels as floats: two 16-byte (bf16) / four 16-byte (f32) vector loads when the
+// run is complete and aligned, scalar (zero-filled) otherwise
+__device__ __forceinline__ void load16(const void* base, int dtype, size_t idx, int nv, float (&o)[16]) {
+  if (dtype == OF_BF16) {
+    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(base) + idx;
+    if (nv == 16 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+      uint4 q[2];
+      q[0] = __ldg(reinterpret_cast<const uint4*>(p));
+      q[1] = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(q);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        o[2 * j] = __uint_as_float(w[j] << 16);
+        o[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) o[j] = j < nv ? __bfloat162float(p[j]) : 0.f;
+    }
+  } else {
+    const float* p = reinterpret_cast<const float*>(base) + idx;
+    if (nv == 16 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 t = __ldg(reinterpret_cast<const float4*>(p) + j);
+        o[4 * j] = t.x; o[4 * j + 1] = t.y; o[4 * j + 2] = t.z; o[4 * j + 3] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) o[j] = j < nv ? __ldg(p + j) : 0.f;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvTcParams P) {
@@ -172,19 +206,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[j]);
         int nv = min(16, P.n_valid - c0);
         if (P.bias) {
+          float t[16];
+          load16(P.bias, OF_F32, (size_t)c0, nv, t);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) if (j < nv) v[j] += __ldg(P.bias + c0 + j);
+          for (int j = 0; j < 16; ++j) v[j] += t[j];
         }
         if (P.add) {
+          float t[16];
+          load16(P.add, P.add_dtype, pix * P.add_stride + c0, nv, t);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) if (j < nv) v[j] += load_any(P.add, P.add_dtype, pix * P.add_stride + c0 + j);
+          for (int j = 0; j < 16; ++j) v[j] += t[j];
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], P.act);
         if (P.mask) {
+          float t[16];
+          load16(P.mask, P.mask_dtype, pix * P.mask_stride + c0, nv, t);
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nv) v[j] *= act_slope(load_any(P.mask, P.mask_dtype, pix * P.mask_stride + c0 + j), P.mask_act);
+          for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], P.mask_act);
         }
         if (P.out_dtype == OF_BF16) {
           __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(P.out) + pix * P.out_stride + c0;

@@ -97,10 +97,19 @@ __global__ void __launch_bounds__(256) costvol_bwd_kernel(const T* __restrict__ 
   }
 }
 
+// tuned max_disp = 3 path (costvol7.cu)
+template <typename T>
+int cv7_fwd(const void* f1, const void* f2, void* cv, int B, int H, int W, int C, int cv_stride, cudaStream_t st);
+template <typename T>
+int cv7_bwd(const void* f1, const void* f2, const void* d_cv, float* d_f1, float* d_f2, int B, int H, int W, int C,
+            int cv_stride, cudaStream_t st);
+template <typename T> static bool cv7_ok(int C, int D) { return D == 7 && (C * (int)sizeof(T)) % 16 == 0; }
+
 template <typename T>
 static int cv_fwd(const void* f1, const void* f2, void* cv, int B, int H, int W, int C, int m, int cv_stride,
                   cudaStream_t st) {
   int D = 2 * m + 1;
+  if (cv7_ok<T>(C, D)) return cv7_fwd<T>(f1, f2, cv, B, H, W, C, cv_stride, st);
   long long ntiles = (long long)B * ((W + 31) / 32) * ((H + 7) / 8) * D;
   int grid = (int)(ntiles < OF_NUM_SMS * 8 ? ntiles : OF_NUM_SMS * 8);
 #define L(DD) costvol_fwd_kernel<T, DD><<<grid, 256, 0, st>>>((const T*)f1, (const T*)f2, (T*)cv, B, H, W, C, cv_stride)
@@ -119,6 +128,7 @@ template <typename T>
 static int cv_bwd(const void* f1, const void* f2, const void* d_cv, float* d_f1, float* d_f2, int B, int H, int W,
                   int C, int m, int cv_stride, cudaStream_t st) {
   int D = 2 * m + 1;
+  if (cv7_ok<T>(C, D)) return cv7_bwd<T>(f1, f2, d_cv, d_f1, d_f2, B, H, W, C, cv_stride, st);
   size_t total = (size_t)B * H * W * (C / 4);
   size_t blocks = (total + 255) / 256;
   int grid = (int)(blocks < (size_t)OF_NUM_SMS * 16 ? blocks : (size_t)OF_NUM_SMS * 16);
