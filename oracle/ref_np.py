@@ -83,8 +83,13 @@ def bilinear_interpolation(input_tensor, sampling_points, return_indices=False):
     return out
 
 
-def bilinear_interpolation_bwd(input_tensor, sampling_points, d_out):
+def bilinear_interpolation_bwd(input_tensor, sampling_points, d_out, return_abs=False):
     """Reverse mode of transformations.py:85-129 as TF autodiff derives it.
+
+    return_abs=True additionally returns sum |w_k| * |d_out| scattered the same way: the
+    magnitude an fp32 scatter-add (TF's scatter_nd or CUDA atomics, any order) rounds
+    against.  Clipped taps have weights far outside [0,1] that cancel, so
+    this - not max|d_input| - is the scale of the legitimate fp32 reordering error.
 
     * d_input: scatter-add (gather_nd gradient) of w_k * d_out at the 4 taps.
     * d_points: only through a = x1c - x and b = y1c - y (floor/cast/clip carry
@@ -116,6 +121,13 @@ def bilinear_interpolation_bwd(input_tensor, sampling_points, d_out):
                       (x1, y0, (1 - a) * b), (x1, y1, (1 - a) * (1 - b))):
         flat = (bidx + yy.astype(np.int64) * W + xx).reshape(-1)
         np.add.at(d_inp, flat, (w[..., None] * g).reshape(-1, C))
+    if return_abs:
+        d_abs = np.zeros((B * H * W, C), dtype=np.float64)
+        for xx, yy, w in ((x0, y0, a * b), (x0, y1, a * (1 - b)),
+                          (x1, y0, (1 - a) * b), (x1, y1, (1 - a) * (1 - b))):
+            flat = (bidx + yy.astype(np.int64) * W + xx).reshape(-1)
+            np.add.at(d_abs, flat, (np.abs(w)[..., None] * np.abs(g)).reshape(-1, C))
+        return d_inp.reshape(B, H, W, C).astype(F32), d_pts.astype(F32), d_abs.reshape(B, H, W, C)
     return d_inp.reshape(B, H, W, C).astype(F32), d_pts.astype(F32)
 
 
@@ -140,13 +152,12 @@ def warp_features(flow_1_to_2, features2, return_indices=False):
     return bilinear_interpolation(feats, pts, return_indices=return_indices)
 
 
-def warp_features_bwd(flow_1_to_2, features2, d_out):
+def warp_features_bwd(flow_1_to_2, features2, d_out, return_abs=False):
     flow = _f32(flow_1_to_2)
     feats = _f32(features2)
     _, height, width, _ = feats.shape
     pts = (warp_grid(height, width) + flow).astype(F32)
-    d_feats, d_pts = bilinear_interpolation_bwd(feats, pts, d_out)
-    return d_feats, d_pts  # d_flow == d_pts (grid is a constant)
+    return bilinear_interpolation_bwd(feats, pts, d_out, return_abs=return_abs)  # d_flow == d_pts
 
 
 def warp_xy(flow_xy, features2, return_indices=False):
@@ -160,13 +171,13 @@ def warp_xy(flow_xy, features2, return_indices=False):
     return bilinear_interpolation(feats, pts, return_indices=return_indices)
 
 
-def warp_xy_bwd(flow_xy, features2, d_out):
+def warp_xy_bwd(flow_xy, features2, d_out, return_abs=False):
     flow = _f32(flow_xy)
     feats = _f32(features2)
     _, height, width, _ = feats.shape
     g = np.ascontiguousarray(warp_grid(height, width)[..., ::-1])
     pts = (g + flow).astype(F32)
-    return bilinear_interpolation_bwd(feats, pts, d_out)
+    return bilinear_interpolation_bwd(feats, pts, d_out, return_abs=return_abs)
 
 
 # ---------------------------------------------------------------------------

@@ -217,8 +217,9 @@ def adam_step(param, grad, m, v, step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-7
     m = np.asarray(m, dtype=F32).copy()
     v = np.asarray(v, dtype=F32).copy()
     lr_t = F32(lr * np.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step))
-    m += (g - m) * F32(1.0 - beta1)
-    v += (np.square(g) - v) * F32(1.0 - beta2)
+    # TF's ApplyAdam kernel forms (1 - beta) in the variable dtype: T(1) - T(beta) in fp32
+    m += (g - m) * (F32(1.0) - F32(beta1))
+    v += (np.square(g) - v) * (F32(1.0) - F32(beta2))
     p -= lr_t * m / (np.sqrt(v) + F32(eps))
     return p, m, v
 

@@ -103,9 +103,14 @@ def test_warp_features_bwd(cuda, mode, shape):
     flow = (r.standard_normal((B, H, W, 2)) * 3.0).astype(np.float32)
     g = r.standard_normal(shape).astype(np.float32)
     bw = R.warp_features_bwd if mode == "ref_ij" else R.warp_xy_bwd
-    e_feats, e_flow = bw(flow, feats, g)
+    e_feats, e_flow, e_abs = bw(flow, feats, g, return_abs=True)
     d_feats, d_flow = F.warp_features_bwd(dev(flow, cuda), dev(feats, cuda), dev(g, cuda), mode=mode)
-    assert_close_maxrel(d_feats, e_feats, what="d_feats")
+    # fp32 scatter-add: 1e-5 of max|ref|, or (where clipped taps with |w| >> 1 cancel: ref_ij with
+    # W > H folds every column j >= H onto row H-1) 4 fp32 ulps of the summed |contributions| - the
+    # rounding bound of ANY fp32 summation order, the reference's own scatter_nd included.
+    err = np.abs(d_feats.cpu().numpy() - e_feats)
+    bound = np.maximum(REL * np.abs(e_feats).max(), 4 * np.finfo(np.float32).eps * e_abs)
+    assert (err <= bound).all(), "d_feats: max excess %.3e" % float((err - bound).max())
     assert_close_maxrel(d_flow, e_flow, what="d_flow")
 
 
@@ -357,5 +362,6 @@ def test_adam_steps(cuda):
         p, m, v = O.adam_step(p, g, m, v, step)
         F.adam_step(pd, dev(g, cuda), md, vd, step)
     np.testing.assert_allclose(pd.cpu().numpy(), p, rtol=1e-6, atol=1e-9)
-    np.testing.assert_allclose(md.cpu().numpy(), m, rtol=1e-6, atol=1e-12)
-    np.testing.assert_allclose(vd.cpu().numpy(), v, rtol=1e-6, atol=1e-15)
+    # m, v: one fp32 rounding of O(1e-3) values (FMA contraction order) -> absolute floor 1e-9
+    np.testing.assert_allclose(md.cpu().numpy(), m, rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(vd.cpu().numpy(), v, rtol=1e-6, atol=1e-13)
