@@ -346,8 +346,11 @@ class FlowNetRef:
 
 def adam_step(param, grad, m, v, step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-7):
     lr_t = lr * math.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step)
-    m = m + (grad - m) * (1.0 - beta1)
-    v = v + (grad * grad - v) * (1.0 - beta2)
+    # TF's ApplyAdam forms (1 - beta) in the variable dtype (fp32): T(1) - T(beta)
+    omb1 = float(np.float32(1.0) - np.float32(beta1))
+    omb2 = float(np.float32(1.0) - np.float32(beta2))
+    m = m + (grad - m) * omb1
+    v = v + (grad * grad - v) * omb2
     param = param - lr_t * m / (torch.sqrt(v) + eps)
     return param, m, v
 
