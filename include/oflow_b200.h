@@ -102,8 +102,10 @@ int of_cost_volume_bwd(const void* f1, const void* f2, const void* d_cv,
  * != NULL) d loss / d flow_s for every scale.
  *   imgs (B,H,W,6) f32; flows/d_flows: HOST arrays of num_scales device
  *   pointers, flow s is (B,hs[s],ws[s],2) f32; loss: device float[1];
- *   workspace: of_loss_workspace_bytes() bytes (device). */
-size_t of_loss_workspace_bytes(void);
+ *   workspace: of_loss_workspace_bytes(B, H, W, num_scales) device bytes, 16-byte aligned,
+ *   zeroed ONCE by the caller after allocation and then reusable by every call of that size
+ *   or smaller (header + an L2-resident float4 pyramid of the resized pair). */
+size_t of_loss_workspace_bytes(int B, int H, int W, int num_scales);
 int of_loss_l1_pyramid_fwdbwd(const float* imgs, const float* const* flows, float* const* d_flows,
                               const int* hs, const int* ws, int num_scales,
                               float* loss, int B, int H, int W, int mode,

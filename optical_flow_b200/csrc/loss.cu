@@ -11,6 +11,7 @@
 // centres, no antialias), so HBM sees the image pair once (the coarser scales
 // hit L2), the flows once and the flow gradients once.  The scalar is reduced
 // deterministically (per-CTA double partials, last CTA sums in index order).
+#include <stdlib.h>
 #include "common.cuh"
 
 #define LOSS_MAX_SCALES 8
@@ -228,6 +229,12 @@ __global__ void __launch_bounds__(256) fused_loss_kernel(const __grid_constant__
 
 #define LOSS_MAX_GRID (OF_NUM_SMS * 8)
 
+// fast path (loss_fused.cu): H, W multiples of 16, power-of-two pyramid
+size_t of_lf_workspace_bytes(int B, int H, int W, int num_scales);
+bool of_lf_supported(int B, int H, int W, int num_scales, const int* hs, const int* ws);
+int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flows, const int* hs, const int* ws,
+              int num_scales, float* loss, int B, int H, int W, int mode, void* workspace, void* stream);
+
 static int run_loss(int kind, const float* imgs, const float* const* flows, float* const* d_flows, const int* hs,
                     const int* ws, int num_scales, float* loss, int B, int H, int W, int mode, void* workspace,
                     void* stream) {
@@ -269,7 +276,7 @@ static int run_loss(int kind, const float* imgs, const float* const* flows, floa
   P.total_tiles = tiles;
   P.imgs = imgs;
   P.loss = loss;
-  P.ws = workspace;
+  P.ws = reinterpret_cast<char*>(workspace) + 16384;   // [0,16K) belongs to the fast path's counters
   P.B = B; P.H = H; P.W = W;
   P.mode = mode;
   long long g = tiles < LOSS_MAX_GRID ? tiles : LOSS_MAX_GRID;
@@ -282,14 +289,24 @@ static int run_loss(int kind, const float* imgs, const float* const* flows, floa
 
 extern "C" {
 
-// workspace: 16-byte header (ticket) + one double per CTA.  Must be zeroed once
-// by the caller after allocation (the kernel re-arms the ticket itself).
-size_t of_loss_workspace_bytes(void) { return 16 + sizeof(double) * LOSS_MAX_GRID; }
+// workspace: header (ticket, per-image counters, one double per CTA) + the L2-resident float4
+// pyramid of the fast path.  Must be zeroed once by the caller after allocation (the kernels
+// re-arm their counters themselves).  Sized for (B, H, W, num_scales); 16-byte aligned.
+size_t of_loss_workspace_bytes(int B, int H, int W, int num_scales) {
+  size_t generic = 32768;   // two 16 KB headers (fast path, generic path: ticket + one double per CTA)
+  size_t fast = (B > 0 && H > 0 && W > 0 && num_scales > 0) ? of_lf_workspace_bytes(B, H, W, num_scales) : 0;
+  return generic > fast ? generic : fast;
+}
 
 int of_loss_l1_pyramid_fwdbwd(const float* imgs, const float* const* flows, float* const* d_flows, const int* hs,
                               const int* ws, int num_scales, float* loss, int B, int H, int W, int mode,
                               void* workspace, void* stream) {
   OF_REQUIRE(mode == OF_WARP_REF_IJ || mode == OF_WARP_XY, OF_ERR_ARG, "bad warp mode %d", mode);
+  OF_REQUIRE(imgs && flows && hs && ws && loss && workspace, OF_ERR_ARG, "null pointer argument");
+  if (of_lf_supported(B, H, W, num_scales, hs, ws) && !getenv("OF_LOSS_GENERIC")) {
+    for (int s = 0; s < num_scales; ++s) OF_REQUIRE(flows[s] != nullptr, OF_ERR_ARG, "flow %d is null", s);
+    return of_lf_run(imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
+  }
   return run_loss(0, imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
 }
 

@@ -159,11 +159,13 @@ def cost_volume_bwd(f1, f2, d_cv, max_disp):
 _loss_ws = {}
 
 
-def _workspace(device):
+def _workspace(device, B, H, W, num_scales):
+    """Zero-initialised once, grown when a larger problem arrives (the kernels re-arm it)."""
     key = (device.type, device.index)
+    need = L.load().of_loss_workspace_bytes(B, H, W, num_scales)
     ws = _loss_ws.get(key)
-    if ws is None:
-        ws = torch.zeros(L.load().of_loss_workspace_bytes(), dtype=torch.uint8, device=device)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, dtype=torch.uint8, device=device)
         _loss_ws[key] = ws
     return ws
 
@@ -178,7 +180,7 @@ def loss_l1_pyramid(batch_imgs, flows, need_grads=True, mode="ref_ij", loss_out=
         loss_out = torch.empty(1, dtype=torch.float32, device=batch_imgs.device)
     if need_grads and d_flows is None:
         d_flows = [torch.empty_like(f) for f in flows]
-    ws = _workspace(batch_imgs.device)
+    ws = _workspace(batch_imgs.device, B, H, W, len(flows))
     L.check(L.load().of_loss_l1_pyramid_fwdbwd(
         L.ptr(batch_imgs), L.ptr_array(flows), L.ptr_array(d_flows) if need_grads else None,
         L.int_array([f.shape[1] for f in flows]), L.int_array([f.shape[2] for f in flows]), len(flows),
@@ -195,7 +197,7 @@ def loss_charbonnier_smooth(y_true, flows_coarse_to_fine, need_grads=True, loss_
         loss_out = torch.empty(1, dtype=torch.float32, device=y_true.device)
     if need_grads and d_flows is None:
         d_flows = [torch.empty_like(f) for f in flows]
-    ws = _workspace(y_true.device)
+    ws = _workspace(y_true.device, B, H, W, len(flows))
     L.check(L.load().of_loss_charbonnier_smooth_fwdbwd(
         L.ptr(y_true), L.ptr_array(flows), L.ptr_array(d_flows) if need_grads else None,
         L.int_array([f.shape[1] for f in flows]), L.int_array([f.shape[2] for f in flows]), len(flows),

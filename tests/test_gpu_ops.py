@@ -254,6 +254,26 @@ def test_loss_layer_fused(cuda, B, H, W):
         assert_close_maxrel(layer.d_flows[s], e_d[s], what="d_flow scale %d" % s)
 
 
+@pytest.mark.parametrize("mode", ["ref_ij", "xy"])
+@pytest.mark.parametrize("B,H,W", [(1, 16, 16), (3, 48, 80), (2, 64, 208), (8, 384, 1280)])
+def test_loss_fast_path_equals_generic(cuda, monkeypatch, B, H, W, mode):
+    """The L2-pyramid fast path (loss_fused.cu; H, W multiples of 16) against the direct-gather
+    kernel (loss.cu) on the same inputs, up to BASELINE's full 8 x 384 x 1280, twice in a row
+    (the kernel re-arms its own counters)."""
+    from optical_flow_b200 import functional as F
+    g = torch.Generator(device="cpu").manual_seed(B * 1000 + H)
+    imgs = (torch.rand((B, H, W, 6), generator=g) - 0.5).to(cuda)
+    flows = [(torch.randn((B, H >> (s + 1), W >> (s + 1), 2), generator=g) * (4.0 / 2 ** s)).to(cuda) for s in range(4)]
+    monkeypatch.setenv("OF_LOSS_GENERIC", "1")
+    l_ref, d_ref = F.loss_l1_pyramid(imgs, flows, mode=mode)
+    monkeypatch.delenv("OF_LOSS_GENERIC")
+    for _ in range(2):
+        l_fast, d_fast = F.loss_l1_pyramid(imgs, flows, mode=mode)
+        assert abs(l_fast.item() - l_ref.item()) <= 1e-6 * abs(l_ref.item())
+        for a, b in zip(d_fast, d_ref):
+            assert_close_maxrel(a, b.cpu().numpy(), rel=1e-6, what="d_flow")
+
+
 def test_loss_layer_shape_assert(cuda):
     from optical_flow_b200.loss import LossLayer
     imgs = torch.zeros((1, 32, 64, 6), device=cuda)
