@@ -17,17 +17,18 @@
 //   build(0), build(1), gather(0), build(2), gather(1), ... so the HBM stream of image b+1
 //   overlaps the L2-bound gather of image b and nobody spins in steady state.
 // HBM traffic = image pair once + flows + d_flows (the algorithmic bytes of SURVEY 8d).
+#include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
 
 #define LF_MAX_SCALES 4
-#define LF_ROWS 16           // full-resolution rows per build unit
-#define LF_COLS 64           // full-resolution columns per build unit
+#define LF_ROWS 32           // full-resolution rows per build unit
+#define LF_COLS 32           // full-resolution columns per build unit
 #define LF_ROW_BYTES (LF_COLS * 24)
-#define LF_STAGE_BYTES (LF_ROWS * LF_ROW_BYTES)   // 24576
-#define LF_STAGES 3
+#define LF_STAGE_BYTES (LF_ROWS * LF_ROW_BYTES)   // 24576: one TMA box {192 floats, 32 rows}
+#define LF_STAGES 4
 #define LF_CONSUMERS 256
-#define LF_THREADS (LF_CONSUMERS + 32)
+#define LF_THREADS (LF_CONSUMERS + 64)   // 8 consumer warps + TMA producer warp + publisher warp
 #define LF_GT_I 32           // gather tile: 32 x 32 output pixels, 4 per thread
 #define LF_GT_J 32
 #define LF_FLOW_ROW_BYTES 272   // 32 float2 + 16 B pad (bank spread; keeps 16-byte TMA alignment)
@@ -46,6 +47,11 @@ struct LfScale {
   float inv_n;     // 1 / (B*h*w*3*num_scales)
 };
 
+struct LfMaps {
+  CUtensorMap img;                    // (B, H, W/16, 96) f32 (16-pixel segments), box {96, 2, 32, 1}: a 32 x 32 pixel patch
+  CUtensorMap flow[LF_MAX_SCALES];    // (B, h, w*2) f32, box {68, 32, 1}: 32 x 32 flow vectors (+ pad)
+};
+
 struct LfParams {
   LfScale sc[LF_MAX_SCALES];
   int ns;
@@ -57,6 +63,9 @@ struct LfParams {
   int B, H, W, mode;
   int bands, chunks;     // H/16, ceil(W/64)
   int nb, ng;            // build / gather units per image
+  int lead;              // images built ahead of the first gather
+  int prows, pcols;      // patch shape (32 x 32; other shapes only for the dbg streaming experiment)
+  int dbg;               // profiling only: 1 skip build math, 2 skip gather math, 4 skip flag polling
   int total_units;
 };
 
@@ -77,6 +86,24 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint
       ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)), "l"(policy)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d_hint(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                                 int c2, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      ::"r"(tc::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1),
+      "r"(c2), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_hint(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                                 int c2, int c3, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
+      ::"r"(tc::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1),
+      "r"(c2), "r"(c3), "l"(policy)
+      : "memory");
+}
 __device__ __forceinline__ void st_f4_policy(float4* p, float4 v, uint64_t policy) {
   asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
                "f"(v.w), "l"(policy)
@@ -95,18 +122,34 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(tc::smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(LF_CONSUMERS) : "memory"); }
 
-// unit index -> (is_build, image, local index); order: build(0), [build(k), gather(k-1)]..., gather(B-1)
+// unit index -> (is_build, image, local index).  Order: build(0..L-1), then pairs
+// [build(L+k), gather(k)] for k < B-L, then gather(B-L..B-1): the pyramid of an image is complete
+// L = lead images' worth of work before anybody gathers from it.
 __device__ __forceinline__ void decode_unit(const LfParams& P, int u, bool* build, int* b, int* local) {
-  if (u < P.nb) { *build = true; *b = 0; *local = u; return; }
-  int v = u - P.nb;
-  int per = P.nb + P.ng;
-  int k = v / per + 1, r = v - (k - 1) * per;
-  if (k <= P.B - 1 && r < P.nb) { *build = true; *b = k; *local = r; return; }
-  *build = false;
-  *b = k - 1;
-  *local = (k <= P.B - 1) ? r - P.nb : r;
+  const int head = P.lead * P.nb;
+  if (u < head) { *build = true; *b = u / P.nb; *local = u - *b * P.nb; return; }
+  int v = u - head;
+  const int per = P.nb + P.ng, pairs = P.B - P.lead;
+  if (v < pairs * per) {
+    int k = v / per, r = v - k * per;
+    if (r < P.nb) { *build = true; *b = P.lead + k; *local = r; }
+    else { *build = false; *b = k; *local = r - P.nb; }
+    return;
+  }
+  v -= pairs * per;
+  int k = v / P.ng;
+  *build = false; *b = pairs + k; *local = v - k * P.ng;
 }
 
 __device__ __forceinline__ int lf_clamp(int v, int lo, int hi) { return min(max(v, lo), hi); }
@@ -146,22 +189,31 @@ __device__ __forceinline__ void lf_build_pixel(const bool VEC, const float* T, i
                     lf_mean4(ra[5], ra[11], rc[5], rc[11]), 0.f);
 }
 
-__global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(const __grid_constant__ LfParams P) {
+__global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(const __grid_constant__ LfParams P, const __grid_constant__ LfMaps M) {
   extern __shared__ __align__(128) uint8_t lf_smem[];
   uint8_t* tiles = lf_smem;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(lf_smem + LF_STAGES * LF_STAGE_BYTES);
   uint64_t* empty_bar = full_bar + LF_STAGES;
+  uint64_t* pub_bar = empty_bar + LF_STAGES;     // consumers -> publisher warp
   __shared__ double s_part[LF_CONSUMERS / 32];
   __shared__ bool s_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    for (int s = 0; s < LF_STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < LF_STAGES; ++s) {
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], LF_CONSUMERS / 32 + 1);   // 8 consumer warps + the publisher
+      tc::mbar_init(&pub_bar[s], LF_CONSUMERS / 32);
+    }
     tc::fence_barrier_init();
   }
   __syncthreads();
 
   float acc = 0.f;
+  if (warp == LF_CONSUMERS / 32 && lane == 0) {
+    tc::prefetch_tmap(&M.img);
+    for (int k = 0; k < P.ns; ++k) tc::prefetch_tmap(&M.flow[k]);
+  }
   if (warp == LF_CONSUMERS / 32) {
     // ============ producer warp: TMA bulk loads (image patches for build units, flow tiles for
     // gather units) into the shared-memory ring; one stage per unit ============
@@ -173,33 +225,50 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
       uint8_t* dst = tiles + (size_t)stage * LF_STAGE_BYTES;
       if (lane == 0) tc::mbar_wait(&empty_bar[stage], phase ^ 1);
       __syncwarp();
-      if (build) {
-        int band = local / P.chunks, cx = local - band * P.chunks;
-        int wc = min(LF_COLS, P.W - cx * LF_COLS);
-        if (lane == 0) tc::mbar_expect_tx(&full_bar[stage], (uint32_t)(LF_ROWS * wc * 24));
-        __syncwarp();
-        if (lane < LF_ROWS) {
-          const float* src = P.imgs + (((size_t)b * P.H + band * LF_ROWS + lane) * P.W + (size_t)cx * LF_COLS) * 6;
-          bulk_load(dst + lane * LF_ROW_BYTES, src, (uint32_t)(wc * 24), &full_bar[stage], pol);
-        }
-      } else {
-        int s = 0;
+      if (lane == 0) {
+        if (build) {
+          int band = local / P.chunks, cx = local - band * P.chunks;
+          tc::mbar_expect_tx(&full_bar[stage], (uint32_t)(P.prows * P.pcols * 24));   // OOB is zero-filled
+          tma_load_4d_hint(dst, &M.img, &full_bar[stage], 0, cx * (P.pcols / 16), band * P.prows, b, pol);
+        } else {
+          int s = 0;
 #pragma unroll
-        for (int k = 1; k < LF_MAX_SCALES; ++k)
-          if (k < P.ns && local >= P.sc[k].g_begin) s = k;
-        const LfScale& S = P.sc[s];
-        int lt = local - S.g_begin;
-        int ti = lt / S.gt_j, tj = lt - ti * S.gt_j;
-        int rows = min(LF_GT_I, S.h - ti * LF_GT_I), cols = min(LF_GT_J, S.w - tj * LF_GT_J);
-        bool staged = (S.w & 1) == 0;
-        if (lane == 0) tc::mbar_expect_tx(&full_bar[stage], staged ? (uint32_t)(rows * cols * 8) : 0u);
-        __syncwarp();
-        if (staged && lane < rows) {
-          const float* src = S.flow + (((size_t)b * S.h + ti * LF_GT_I + lane) * S.w + tj * LF_GT_J) * 2;
-          bulk_load(dst + lane * LF_FLOW_ROW_BYTES, src, (uint32_t)(cols * 8), &full_bar[stage], pol);
+          for (int k = 1; k < LF_MAX_SCALES; ++k)
+            if (k < P.ns && local >= P.sc[k].g_begin) s = k;
+          const LfScale& S = P.sc[s];
+          int lt = local - S.g_begin;
+          int ti = lt / S.gt_j, tj = lt - ti * S.gt_j;
+          bool staged = (S.w & 1) == 0;
+          tc::mbar_expect_tx(&full_bar[stage], staged ? (uint32_t)(LF_GT_I * LF_FLOW_ROW_BYTES) : 0u);
+          if (staged) tma_load_3d_hint(dst, &M.flow[s], &full_bar[stage], tj * LF_GT_J * 2, ti * LF_GT_I, b, pol);
         }
       }
       if (++stage == LF_STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == LF_CONSUMERS / 32 + 1) {
+    // ============ publisher warp: one thread turns "all 8 consumer warps finished build unit n"
+    // (mbarrier, CTA-scope release/acquire) into a gpu-scope release of done[image]: the ~1 us
+    // membar stalls nobody who computes.  Units that completed meanwhile share one fence. ============
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      int u = blockIdx.x;
+      while (u < P.total_units) {
+        tc::mbar_wait(&pub_bar[stage], phase);
+        int imgs_done[LF_STAGES]; int k = 0;
+        do {
+          bool build; int b, local;
+          decode_unit(P, u, &build, &b, &local);
+          if (build) imgs_done[k++] = b;
+          tc::mbar_arrive(&empty_bar[stage]);
+          if (++stage == LF_STAGES) { stage = 0; phase ^= 1; }
+          u += gridDim.x;
+        } while (u < P.total_units && k < LF_STAGES && mbar_test(&pub_bar[stage], phase));
+        if (k) {
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          for (int i = 0; i < k; ++i)
+            asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(P.done + imgs_done[i]) : "memory");
+        }
+      }
     }
   } else {
     // ===================== consumers =====================
@@ -212,22 +281,23 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
       const uint8_t* Tb = tiles + (size_t)stage * LF_STAGE_BYTES;
       if (build) {
         int band = local / P.chunks, cx = local - band * P.chunks;
-        int wc = min(LF_COLS, P.W - cx * LF_COLS);
-        tc::mbar_wait(&full_bar[stage], phase);
+        const int wc = min(LF_COLS, P.W - cx * LF_COLS), hr = min(LF_ROWS, P.H - band * LF_ROWS);
+        if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);   // one poller per warp
+        __syncwarp();
         const float* T = reinterpret_cast<const float*>(Tb);
-        // items enumerated on the full 16 x 64 patch grid (shifts, no divisions); columns beyond a
-        // narrow last chunk are skipped.  scale s: (16 >> (s+1)) rows x (64 >> (s+1)) columns.
-        int t = tid;
+        // items enumerated on the full 32 x 32 patch grid (shifts, no divisions); rows / columns beyond
+        // the image (last band / chunk) are skipped.  scale s: (32 >> (s+1))^2 resized pixels.
+        int t = (P.dbg & 1) ? 1 << 20 : tid;
 #pragma unroll
         for (int s = 0; s < LF_MAX_SCALES; ++s) {
-          const int lc = 5 - s;                         // log2(columns at scale s)
+          const int lc = 4 - s;                         // log2(columns at scale s)
           const int n_s = (LF_ROWS >> (s + 1)) << lc;
           if (s < P.ns) {
             const LfScale& S = P.sc[s];
             const int bs = 2 << s;
             for (; t < n_s; t += LF_CONSUMERS) {
               int orow = t >> lc, ocol = t & ((1 << lc) - 1);
-              if (ocol * bs < wc) {
+              if (ocol * bs < wc && orow * bs < hr) {
                 float4 o1, o2;
                 lf_build_pixel(s == 0, T, bs * orow + (bs >> 1) - 1, bs * ocol + (bs >> 1) - 1, &o1, &o2);
                 unsigned pix = ((unsigned)b * S.h + band * (LF_ROWS / bs) + orow) * S.w + cx * (LF_COLS / bs) + ocol;
@@ -238,18 +308,16 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
           }
           t -= n_s;
         }
-        consumer_sync();               // all pyramid stores of this unit issued, patch no longer read
-        if (tid == 0) {
-          tc::mbar_arrive(&empty_bar[stage]);
-          __threadfence();             // cumulative: publishes the CTA's stores ordered by the barrier
-          atomicAdd(&P.done[b], 1u);
-        }
+        // warps are decoupled (no CTA barrier): each warp hands the unit to the publisher warp (which
+        // makes the pyramid stores visible gpu-wide off the critical path) and frees the ring slot
+        __syncwarp();
+        if (lane == 0) { tc::mbar_arrive(&pub_bar[stage]); tc::mbar_arrive(&empty_bar[stage]); }
       } else {
         // ---- gather unit: 32 x 32 output pixels of one scale, 4 per thread (2 in flight) ----
-        if (b > confirmed) {           // first gather unit of image b in this CTA: wait for its pyramid
-          if (tid == 0)
-            while (ld_acquire(&P.done[b]) < (unsigned)P.nb) __nanosleep(32);
-          consumer_sync();
+        if (b > confirmed && !(P.dbg & 4)) {           // first gather unit of image b in this CTA: wait for its pyramid
+          if (lane == 0)
+            while (ld_acquire(&P.done[b]) < (unsigned)P.nb) __nanosleep(64);
+          __syncwarp();
           confirmed = b;
         }
         int s = 0;
@@ -269,9 +337,10 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
         const float4* q1 = S.p1 + img_px;
         const float2* gflow = reinterpret_cast<const float2*>(S.flow) + img_px;
         float2* gdflow = S.d_flow ? reinterpret_cast<float2*>(S.d_flow) + img_px : nullptr;
-        tc::mbar_wait(&full_bar[stage], phase);
+        if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);   // one poller per warp
+        __syncwarp();
 #pragma unroll 1
-        for (int q = 0; q < 2; ++q) {
+        for (int q = (P.dbg & 2) ? 2 : 0; q < 2; ++q) {
           const int lj = dj + 16 * q, j = tj * LF_GT_J + lj;
           int ii[2]; bool ok[2]; float2 fl[2];
 #pragma unroll
@@ -329,8 +398,8 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
             }
           }
         }
-        consumer_sync();               // flow tile no longer read
-        if (tid == 0) tc::mbar_arrive(&empty_bar[stage]);
+        __syncwarp();                  // flow tile no longer read by this warp
+        if (lane == 0) { tc::mbar_arrive(&pub_bar[stage]); tc::mbar_arrive(&empty_bar[stage]); }
       }
       if (++stage == LF_STAGES) { stage = 0; phase ^= 1; }
     }
@@ -353,19 +422,54 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
   }
   __syncthreads();
   if (s_last) {
-    // every CTA has finished all of its units: re-arm the per-image counters and the ticket
+    // every CTA has finished all of its units: re-arm the per-image counters and the ticket, and add
+    // the per-CTA partials in a fixed (deterministic) order - in parallel: a one-thread loop over
+    // ~300 L2 round trips costs more than the rest of the kernel
     for (int b = tid; b < P.B; b += LF_THREADS) P.done[b] = 0u;
-    if (tid == 0) {
+    __shared__ double s_red[LF_CONSUMERS];
+    if (tid < LF_CONSUMERS) {
       __threadfence();
-      double s = 0.0;
-      for (unsigned i = 0; i < gridDim.x; ++i) s += reinterpret_cast<volatile double*>(P.partials)[i];
-      *P.loss = (float)s;
+      double v = 0.0;
+      for (unsigned i = tid; i < gridDim.x; i += LF_CONSUMERS) v += reinterpret_cast<volatile double*>(P.partials)[i];
+      s_red[tid] = v;
+    }
+    __syncthreads();
+    for (int o = LF_CONSUMERS / 2; o > 0; o >>= 1) {
+      if (tid < o) s_red[tid] += s_red[tid + o];
+      __syncthreads();
+    }
+    if (tid == 0) {
+      *P.loss = (float)s_red[0];
       *P.ticket = 0u;
     }
   }
 }
 
 // ---- host side ------------------------------------------------------------------------------
+int of_tc_get_encode(void** fn);   // conv_tc.cu: cuTensorMapEncodeTiled through the runtime's driver entry point
+
+typedef CUresult (*LfEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// (B, rows, row_floats) f32 tensor, box {box_floats, box_rows, 1}, no swizzle, zero fill outside
+static int lf_make_map(CUtensorMap* m, const void* base, int B, int rows, long long row_floats, int box_floats,
+                       int box_rows) {
+  void* fn;
+  if (int r = of_tc_get_encode(&fn)) return r;
+  OF_REQUIRE(((uintptr_t)base & 15) == 0 && (row_floats * 4) % 16 == 0, OF_ERR_ARG,
+             "TMA needs 16-byte aligned base and row pitch");
+  cuuint64_t dims[3] = {(cuuint64_t)row_floats, (cuuint64_t)rows, (cuuint64_t)B};
+  cuuint64_t strides[2] = {(cuuint64_t)row_floats * 4, (cuuint64_t)rows * row_floats * 4};
+  cuuint32_t box[3] = {(cuuint32_t)box_floats, (cuuint32_t)box_rows, 1};
+  cuuint32_t es[3] = {1, 1, 1};
+  CUresult r = ((LfEncodeTiled)fn)(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box,
+                                   es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  OF_REQUIRE(r == CUDA_SUCCESS, OF_ERR_STATE, "cuTensorMapEncodeTiled(loss) failed: %d", (int)r);
+  return 0;
+}
+
 size_t of_lf_workspace_bytes(int B, int H, int W, int num_scales) {
   size_t px = 0;
   for (int s = 0; s < num_scales && s < LF_MAX_SCALES; ++s) px += (size_t)B * (H >> (s + 1)) * (W >> (s + 1));
@@ -407,15 +511,47 @@ int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flow
   P.ns = num_scales;
   P.imgs = imgs; P.loss = loss;
   P.B = B; P.H = H; P.W = W; P.mode = mode;
-  P.bands = H / LF_ROWS;
-  P.chunks = (W + LF_COLS - 1) / LF_COLS;
+  P.prows = LF_ROWS; P.pcols = LF_COLS;
+  if (const char* e = getenv("OF_LF_SHAPE")) {            // streaming experiment (use with OF_LF_DBG=7)
+    int r_ = 0, c_ = 0;
+    if (sscanf(e, "%d,%d", &r_, &c_) == 2 && r_ > 0 && c_ > 0 && c_ % 16 == 0 && r_ * c_ * 24 <= LF_STAGE_BYTES) {
+      P.prows = r_; P.pcols = c_;
+    }
+  }
+  P.bands = (H + P.prows - 1) / P.prows;
+  P.chunks = (W + P.pcols - 1) / P.pcols;
   P.nb = P.bands * P.chunks;
   P.ng = ng;
+  P.lead = B < 4 ? B : 4;   // measured on B200 at C2: lead 1 / 2 / 3 / 4 -> 84 / 64 / 55 / 53 us
+  if (const char* e = getenv("OF_LF_DBG")) P.dbg = atoi(e);
+  if (const char* e = getenv("OF_LF_LEAD")) { int v = atoi(e); if (v >= 1 && v <= B) P.lead = v; }
   long long total = (long long)B * (P.nb + P.ng);
   OF_REQUIRE(total < (1ll << 30), OF_ERR_SHAPE, "too many loss work units");
   P.total_units = (int)total;
 
-  const size_t smem = (size_t)LF_STAGES * LF_STAGE_BYTES + 2 * LF_STAGES * sizeof(uint64_t);
+  LfMaps M;
+  memset(&M, 0, sizeof(M));
+  {
+    void* fn;
+    if (int r = of_tc_get_encode(&fn)) return r;
+    cuuint64_t dims[4] = {96, (cuuint64_t)(W / 16), (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t strides[3] = {384, (cuuint64_t)W * 24, (cuuint64_t)H * W * 24};
+    cuuint32_t box[4] = {96, (cuuint32_t)(P.pcols / 16), (cuuint32_t)P.prows, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    CUresult r = ((LfEncodeTiled)fn)(&M.img, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(imgs), dims, strides,
+                                     box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    OF_REQUIRE(r == CUDA_SUCCESS, OF_ERR_STATE, "cuTensorMapEncodeTiled(images) failed: %d", (int)r);
+  }
+  for (int s = 0; s < num_scales; ++s) {
+    M.flow[s] = M.img;                                    // unstaged scales never touch their map
+    if ((ws[s] & 1) == 0)
+      if (int r = lf_make_map(&M.flow[s], flows[s], B, hs[s], (long long)ws[s] * 2, LF_FLOW_ROW_BYTES / 4, LF_GT_I))
+        return r;
+  }
+  for (int s = num_scales; s < LF_MAX_SCALES; ++s) M.flow[s] = M.img;
+
+  const size_t smem = (size_t)LF_STAGES * LF_STAGE_BYTES + 3 * LF_STAGES * sizeof(uint64_t);
   static int max_ctas = 0;
   if (max_ctas == 0) {
     OF_CUDA(cudaFuncSetAttribute(loss_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -428,9 +564,10 @@ int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flow
     if (max_ctas > LF_MAX_GRID) max_ctas = LF_MAX_GRID;
   }
   int grid = P.total_units < max_ctas ? P.total_units : max_ctas;
+  if (const char* e = getenv("OF_LF_GRID")) { int v = atoi(e); if (v >= 1 && v < grid) grid = v; }
   // co-residency is required (gather units wait on build units of other CTAs): cooperative launch
   // makes the runtime enforce it
-  void* args[1] = {(void*)&P};
+  void* args[2] = {(void*)&P, (void*)&M};
   OF_CUDA(cudaLaunchCooperativeKernel((const void*)loss_fused_kernel, dim3(grid), dim3(LF_THREADS), args, smem,
                                       (cudaStream_t)stream));
   return of_launch_check("loss_fused_kernel");
