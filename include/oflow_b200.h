@@ -163,6 +163,10 @@ typedef struct {
   int N, H, W;              /* source spatial dims */
   int Ho, Wo;               /* output spatial dims */
   int KH, KW, stride, pad_t, pad_l, sign;
+  /* optional strided VIEW of source 0 (0 = dense NHWC): element strides between consecutive W / H / N
+   * coordinates, and separate W / H convolution strides.  Lets the Cin = 3 stem run as a 7x1 conv over
+   * overlapping 8-pixel windows of the packed image (of_pack_image_pair8): W pitch 2 pixels = 16 elements. */
+  long long view_w_stride, view_h_stride, view_n_stride; int stride_w, stride_h;
   int n_mma, n_valid;       /* MMA N (multiple of 16, <= 256) and real output channels */
   void* out; int out_dtype; int out_stride;
   const float* bias; int act;
@@ -183,8 +187,17 @@ typedef struct {
   const void* dy; int dy_c; int dy_stride;
   float* dw;
   int N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, Cin, Cout;
+  long long view_w_stride, view_h_stride, view_n_stride; int stride_w, stride_h;   /* as in of_tc_conv */
 } of_tc_wgrad;
 int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream);
+/* Stem (model.py:12, Cin = 3, 7x7 / 2) on tensor cores.  of_pack_image_pair8: imgs (B,H,W,6) f32 -> bf16
+ * (2B, H+5, W+6, 8): frame 1s then frame 2s, TF-SAME zero border (2 top/left, 3 bottom / 4 right), channels
+ * 3..7 zero.  A window of 8 consecutive pixels is then one 64-element K chunk (kw*8 + c) and the 7x7/2 conv is
+ * a 7-tap (kh) conv over the view {W pitch 16 elements, H pitch (W+6)*8}.  of_conv1_pack_weights: folded f32
+ * (7,7,3,Cout) -> bf16 [7][Cout][64]; of_conv1_unpack_wgrad: dw_view f32 [7][64][Cout] -> (7,7,3,Cout). */
+int of_pack_image_pair8(const float* imgs, void* out, int B, int H, int W, void* stream);
+int of_conv1_pack_weights(const float* w_hwio, void* packed, int Cout, void* stream);
+int of_conv1_unpack_wgrad(const float* dw_view, float* dw_hwio, int Cout, void* stream);
 /* out (N,H,W,C) = dy (N,Ho,Wo,C) with zeros inserted (out[2i,2j] = dy[i,j]): a stride-2 conv's
  * dgrad is the stride-1 dgrad of this tensor. */
 int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,

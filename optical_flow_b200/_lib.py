@@ -28,7 +28,10 @@ class TcConv(C.Structure):
                 ("wpacked", C.c_void_p), ("n_rows", C.c_int), ("k_pad", C.c_int),
                 ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int),
                 ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_t", C.c_int), ("pad_l", C.c_int),
-                ("sign", C.c_int), ("n_mma", C.c_int), ("n_valid", C.c_int),
+                ("sign", C.c_int),
+                ("view_w_stride", C.c_longlong), ("view_h_stride", C.c_longlong), ("view_n_stride", C.c_longlong),
+                ("stride_w", C.c_int), ("stride_h", C.c_int),
+                ("n_mma", C.c_int), ("n_valid", C.c_int),
                 ("out", C.c_void_p), ("out_dtype", C.c_int), ("out_stride", C.c_int),
                 ("bias", C.c_void_p), ("act", C.c_int),
                 ("add", C.c_void_p), ("add_dtype", C.c_int), ("add_stride", C.c_int),
@@ -43,7 +46,9 @@ class TcWgrad(C.Structure):
                 ("dw", C.c_void_p),
                 ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int),
                 ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_t", C.c_int), ("pad_l", C.c_int),
-                ("Cin", C.c_int), ("Cout", C.c_int)]
+                ("Cin", C.c_int), ("Cout", C.c_int),
+                ("view_w_stride", C.c_longlong), ("view_h_stride", C.c_longlong), ("view_n_stride", C.c_longlong),
+                ("stride_w", C.c_int), ("stride_h", C.c_int)]
 
 
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
@@ -53,6 +58,9 @@ PROTOTYPES = {
                                           C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                           C.c_void_p]),
     "of_conv_tc_wgrad": (C.c_int, [C.POINTER(TcWgrad), C.c_void_p]),
+    "of_pack_image_pair8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "of_conv1_pack_weights": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "of_conv1_unpack_wgrad": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "of_zero_upsample2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, C.c_void_p]),
     "of_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]),

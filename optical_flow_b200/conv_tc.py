@@ -158,6 +158,62 @@ def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=Tru
     return dw, db
 
 
+# ------------------------------------------------------- stem (Cin = 3) on tensor cores --
+
+def pack_image_pair8(batch_imgs):
+    """(B,H,W,6) f32 -> bf16 (2B, H+5, W+6, 8): frame 1s then frame 2s (model.py:122-123,131-132), TF-SAME
+    zero border of the 7x7/2 stem, channels 3..7 zero.  8 consecutive pixels = one 64-wide K chunk."""
+    B, H, W, _ = batch_imgs.shape
+    out = torch.empty((2 * B, H + 5, W + 6, 8), dtype=torch.bfloat16, device=batch_imgs.device)
+    L.check(L.load().of_pack_image_pair8(L.ptr(batch_imgs), L.ptr(out), B, H, W, L.stream_ptr()), "of_pack_image_pair8")
+    return out
+
+
+def _stem_view(d, xp, H, W):
+    """Describe the packed image as the strided view the stem convolves: windows of 8 pixels every 2."""
+    Hp, Wp = H + 5, W + 6
+    d.N, d.H, d.W, d.Ho, d.Wo = xp.shape[0], Hp, W // 2, H // 2, W // 2
+    d.KH, d.KW, d.stride, d.pad_t, d.pad_l = 7, 1, 2, 0, 0
+    d.stride_w, d.stride_h = 1, 2
+    d.view_w_stride, d.view_h_stride, d.view_n_stride = 16, Wp * 8, Hp * Wp * 8
+
+
+def conv1_fprop_tc(xp, H, W, w_hwio, bias, act=L.OF_ACT_RELU, out_dtype=torch.bfloat16):
+    """model.py:12-15 stem: Conv2D(64, 7, strides=2, 'same') (+ folded BN + ReLU) as a 7-tap conv over the view."""
+    Cout = w_hwio.shape[3]
+    assert tuple(w_hwio.shape[:3]) == (7, 7, 3) and Cout % 16 == 0
+    wp = torch.empty((7, Cout, 64), dtype=torch.bfloat16, device=xp.device)
+    L.check(L.load().of_conv1_pack_weights(L.ptr(w_hwio), L.ptr(wp), Cout, L.stream_ptr()), "of_conv1_pack_weights")
+    out = torch.empty((xp.shape[0], H // 2, W // 2, Cout), dtype=out_dtype, device=xp.device)
+    d = L.TcConv()
+    d.src[0], d.src_c[0], d.src_stride[0], d.num_src = xp.data_ptr(), 64, 16, 1
+    d.wpacked, d.n_rows, d.k_pad = wp.data_ptr(), Cout, 64
+    _stem_view(d, xp, H, W)
+    d.sign, d.n_mma, d.n_valid = 1, Cout, Cout
+    d.out, d.out_dtype, d.out_stride = out.data_ptr(), L.dtype_code(out), Cout
+    d.bias, d.act = L.ptr(bias), act
+    L.check(L.load().of_conv_tc_run(C.byref(d), L.stream_ptr()), "of_conv_tc_run(stem)")
+    return out
+
+
+def conv1_wgrad_tc(xp, H, W, dz, dw, db):
+    """dw (7,7,3,Cout) f32, db (Cout) f32 of the stem from the packed image and bf16 dz."""
+    Cout = dz.shape[-1]
+    dwv = torch.empty((7, 64, Cout), dtype=torch.float32, device=dz.device)
+    d = L.TcWgrad()
+    d.x[0], d.x_c[0], d.x_stride[0], d.x_valid[0], d.x_ci0[0], d.num_src = xp.data_ptr(), 64, 16, 64, 0, 1
+    d.dy, d.dy_c, d.dy_stride = dz.data_ptr(), Cout, Cout
+    d.dw = dwv.data_ptr()
+    _stem_view(d, xp, H, W)
+    d.Cin, d.Cout = 64, Cout
+    L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad(stem)")
+    L.check(L.load().of_conv1_unpack_wgrad(L.ptr(dwv), L.ptr(dw), Cout, L.stream_ptr()), "of_conv1_unpack_wgrad")
+    if db is not None:
+        npix = dz.shape[0] * dz.shape[1] * dz.shape[2]
+        L.check(L.load().of_colsum(L.ptr(dz), L.ptr(db), npix, Cout, Cout, L.dtype_code(dz), L.stream_ptr()), "of_colsum")
+    return dw, db
+
+
 # --------------------------------------------------------------------- backend --
 
 class Bf16Backend:
@@ -171,9 +227,14 @@ class Bf16Backend:
     def _tc_ok(layer):
         return layer.cin >= 32 and layer.cout >= 16
 
+    def split(self, batch_imgs):
+        """model.py:122-123,131-132 + the stem's input layout: the packed bf16 pair (see pack_image_pair8)."""
+        self.img_hw = (batch_imgs.shape[1], batch_imgs.shape[2])
+        return pack_image_pair8(batch_imgs)
+
     def fprop(self, layer, x, w, b):
-        if layer.cin < 32:          # conv1 (Cin = 3): fp32 image in, bf16 out, SIMT
-            return F.conv2d_fprop(x, w, b, stride=layer.stride, act=layer.act, out_dtype=torch.bfloat16)
+        if layer.cin < 32:          # conv1 (Cin = 3, 7x7/2): 7-tap tensor-core conv over the packed image
+            return conv1_fprop_tc(x, self.img_hw[0], self.img_hw[1], w, b, act=layer.act)
         out_dtype = torch.float32 if layer.cout < 16 else torch.bfloat16     # flow heads stay fp32
         return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype)
 
@@ -183,7 +244,9 @@ class Bf16Backend:
         return F.act_bwd(y, dy, layer.act)
 
     def wgrad(self, layer, x, dz, dw, db):
-        if self._tc_ok(layer):
+        if layer.cin < 32:
+            conv1_wgrad_tc(x, self.img_hw[0], self.img_hw[1], dz, dw, db)
+        elif self._tc_ok(layer):
             conv2d_wgrad_tc(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
         else:
             assert not isinstance(x, MultiSource)

@@ -26,7 +26,7 @@ struct ConvTcParams {
   int num_src;
   int kchunks[2];     // 64-channel chunks per source
   int kbase[2];       // first K column of each source in the packed weights
-  int taps, KW, pad_t, pad_l, stride, sign;
+  int taps, KW, pad_t, pad_l, stride_w, stride_h, sign;
   int NB, Ho, Wo;     // output (GEMM M) space
   int TW, TH, tiles_w, tiles_h, m_tiles;
   int n_mma, n_valid; // MMA N (multiple of 16) and real output channels
@@ -131,7 +131,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x) {
         int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
         int th_i = r % P.tiles_h; int n = r / P.tiles_h;
-        int w0 = tw_i * P.TW * P.stride, h0 = th_i * P.TH * P.stride;
+        int w0 = tw_i * P.TW * P.stride_w, h0 = th_i * P.TH * P.stride_h;
         for (int s = 0; s < P.num_src; ++s) {
           const CUtensorMap* tmA = s == 0 ? &tmA0 : &tmA1;
           for (int tap = 0; tap < P.taps; ++tap) {
@@ -313,24 +313,32 @@ int of_tc_get_encode(void** fn) {
   return 0;
 }
 
-// NHWC bf16 activation tensor (channels c_used of pixel stride `stride_elems`) as a 4-D map
-// {C, W, H, N}, box {64, TW*s, TH*s, 1}, elementStrides {1, s, s, 1}, SWIZZLE_128B.
-int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long stride_elems, int N, int H, int W,
-                       int box_w, int box_h, int estride) {
+// bf16 activation tensor as a 4-D map {C, W, H, N} with explicit element strides between consecutive
+// W / H / N coordinates (dense NHWC: stride_elems, W*stride_elems, H*W*stride_elems; an overlapping
+// window view is legal: strides only have to be multiples of 16 bytes), box {64, box_w*sw, box_h*sh, 1},
+// elementStrides {1, sw, sh, 1}, SWIZZLE_128B.
+int of_tc_make_view_map(CUtensorMap* m, const void* base, int c_used, long long w_stride, long long h_stride,
+                        long long n_stride, int N, int H, int W, int box_w, int box_h, int sw, int sh) {
   void* fn;
   if (int r = of_tc_get_encode(&fn)) return r;
-  OF_REQUIRE(((uintptr_t)base & 15) == 0 && (stride_elems * 2) % 16 == 0, OF_ERR_ARG,
-             "TMA needs 16-byte aligned base/strides (channels %% 8 == 0)");
+  OF_REQUIRE(((uintptr_t)base & 15) == 0 && (w_stride * 2) % 16 == 0 && (h_stride * 2) % 16 == 0 &&
+                 (n_stride * 2) % 16 == 0,
+             OF_ERR_ARG, "TMA needs 16-byte aligned base/strides (channels %% 8 == 0)");
   cuuint64_t dims[4] = {(cuuint64_t)c_used, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)stride_elems * 2, (cuuint64_t)W * stride_elems * 2,
-                           (cuuint64_t)H * W * stride_elems * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)(box_w * estride), (cuuint32_t)(box_h * estride), 1};
-  cuuint32_t es[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
+  cuuint64_t strides[3] = {(cuuint64_t)w_stride * 2, (cuuint64_t)h_stride * 2, (cuuint64_t)n_stride * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)(box_w * sw), (cuuint32_t)(box_h * sh), 1};
+  cuuint32_t es[4] = {1, (cuuint32_t)sw, (cuuint32_t)sh, 1};
   CUresult r = ((PFN_encodeTiled)fn)(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides,
                                      box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   OF_REQUIRE(r == CUDA_SUCCESS, OF_ERR_STATE, "cuTensorMapEncodeTiled(activation) failed: %d", (int)r);
   return 0;
+}
+
+int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long stride_elems, int N, int H, int W,
+                       int box_w, int box_h, int estride) {
+  return of_tc_make_view_map(m, base, c_used, stride_elems, (long long)W * stride_elems,
+                             (long long)H * W * stride_elems, N, H, W, box_w, box_h, estride, estride);
 }
 
 // packed weights bf16 [taps][rows][cols] as a 3-D map {cols, rows, taps}, box {64, box_rows, 1}
@@ -399,7 +407,13 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
     kb += P.kchunks[s] * 64;
   }
   OF_REQUIRE(kb <= c->k_pad, OF_ERR_SHAPE, "packed K %d smaller than the sources' %d", c->k_pad, kb);
-  P.taps = c->KH * c->KW; P.KW = c->KW; P.pad_t = c->pad_t; P.pad_l = c->pad_l; P.stride = c->stride;
+  P.taps = c->KH * c->KW; P.KW = c->KW; P.pad_t = c->pad_t; P.pad_l = c->pad_l;
+  P.stride_w = c->stride_w > 0 ? c->stride_w : c->stride;
+  P.stride_h = c->stride_h > 0 ? c->stride_h : c->stride;
+  OF_REQUIRE(P.stride_w >= 1 && P.stride_w <= 2 && P.stride_h >= 1 && P.stride_h <= 2, OF_ERR_UNSUPPORTED,
+             "conv strides %d x %d unsupported", P.stride_h, P.stride_w);
+  const bool view = c->view_w_stride > 0;
+  OF_REQUIRE(!view || c->num_src == 1, OF_ERR_ARG, "a strided view takes one source");
   P.sign = c->sign >= 0 ? 1 : -1;
   P.NB = c->N; P.Ho = c->Ho; P.Wo = c->Wo;
   pick_tile(c->Wo, &P.TW, &P.TH);
@@ -422,10 +436,14 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
 
   CUtensorMap tmA[2], tmB;
   memset(tmA, 0, sizeof(tmA));
-  for (int s = 0; s < c->num_src; ++s)
-    if (int r = of_tc_make_act_map(&tmA[s], c->src[s], c->src_c[s], c->src_stride[s], c->N, c->H, c->W, P.TW, P.TH,
-                                   c->stride))
+  for (int s = 0; s < c->num_src; ++s) {
+    long long ws_ = view ? c->view_w_stride : c->src_stride[s];
+    long long hs_ = view ? c->view_h_stride : (long long)c->W * c->src_stride[s];
+    long long ns_ = view ? c->view_n_stride : (long long)c->H * c->W * c->src_stride[s];
+    if (int r = of_tc_make_view_map(&tmA[s], c->src[s], c->src_c[s], ws_, hs_, ns_, c->N, c->H, c->W, P.TW, P.TH,
+                                    P.stride_w, P.stride_h))
       return r;
+  }
   if (c->num_src == 1) tmA[1] = tmA[0];
   if (int r = make_weight_map(&tmB, c->wpacked, P.taps, c->n_rows, c->k_pad, c->n_mma)) return r;
 

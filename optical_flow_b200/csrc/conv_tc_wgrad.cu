@@ -19,6 +19,8 @@
 
 int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long stride_elems, int N, int H, int W,
                        int box_w, int box_h, int estride);
+int of_tc_make_view_map(CUtensorMap* m, const void* base, int c_used, long long w_stride, long long h_stride,
+                        long long n_stride, int N, int H, int W, int box_w, int box_h, int sw, int sh);
 
 #define WG_MAX_CHUNKS 16
 #define WG_MAX_JOBS 48
@@ -30,7 +32,7 @@ struct WgradParams {
   int chunk_cnt[WG_MAX_CHUNKS];   // valid channels in the chunk
   // job (blockIdx.y) = (M tile, tap group)
   int job_mt[WG_MAX_JOBS], job_tap0[WG_MAX_JOBS], job_ntaps[WG_MAX_JOBS];
-  int KW, pad_t, pad_l, stride;
+  int KW, pad_t, pad_l, stride_w, stride_h;
   int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
   int ktiles, ktiles_per_split;
   int n_mma, n_valid, n_chunks;   // dy: MMA N, real Cout, 64-channel chunks
@@ -82,7 +84,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         for (int t = 0; t < ntaps; ++t) {
           int tap = tap0 + t;
           int kh = tap / P.KW, kw = tap - kh * P.KW;
-          int cw = w0 * P.stride + kw - P.pad_l, ch = h0 * P.stride + kh - P.pad_t;
+          int cw = w0 * P.stride_w + kw - P.pad_l, ch = h0 * P.stride_h + kh - P.pad_t;
           for (int c = 0; c < 2; ++c) {
             // a chunk with no source reads channel coordinate far outside the tensor -> TMA zero fill
             const int cm = P.chunk_map[mt * 2 + c];
@@ -175,7 +177,11 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
 
   WgradParams P;
   memset(&P, 0, sizeof(P));
-  P.KW = c->KW; P.pad_t = c->pad_t; P.pad_l = c->pad_l; P.stride = c->stride;
+  P.KW = c->KW; P.pad_t = c->pad_t; P.pad_l = c->pad_l;
+  P.stride_w = c->stride_w > 0 ? c->stride_w : c->stride;
+  P.stride_h = c->stride_h > 0 ? c->stride_h : c->stride;
+  const bool view = c->view_w_stride > 0;
+  OF_REQUIRE(!view || c->num_src == 1, OF_ERR_ARG, "a strided view takes one source");
   P.NB = c->N; P.Ho = c->Ho; P.Wo = c->Wo;
   const int cands[4] = {16, 32, 8, 64};
   P.TW = 16; P.TH = 4;
@@ -200,9 +206,14 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
 
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
-  for (int s = 0; s < c->num_src; ++s)
-    if (int r = of_tc_make_act_map(&tmX[s], c->x[s], c->x_c[s], c->x_stride[s], c->N, c->H, c->W, P.TW, P.TH, c->stride))
+  for (int s = 0; s < c->num_src; ++s) {
+    long long ws_ = view ? c->view_w_stride : c->x_stride[s];
+    long long hs_ = view ? c->view_h_stride : (long long)c->W * c->x_stride[s];
+    long long ns_ = view ? c->view_n_stride : (long long)c->H * c->W * c->x_stride[s];
+    if (int r = of_tc_make_view_map(&tmX[s], c->x[s], c->x_c[s], ws_, hs_, ns_, c->N, c->H, c->W, P.TW, P.TH,
+                                    P.stride_w, P.stride_h))
       return r;
+  }
   if (c->num_src == 1) tmX[1] = tmX[0];
   if (int r = of_tc_make_act_map(&tmDY, c->dy, c->dy_c, c->dy_stride, c->N, c->Ho, c->Wo, P.TW, P.TH, 1)) return r;
 

@@ -117,9 +117,11 @@ __device__ __forceinline__ float4 ld_f4_policy(const float4* p, uint64_t policy)
                : "memory");
   return v;
 }
-__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
+// poll with relaxed loads (an acquire load invalidates the SM's L1 on every iteration); the caller
+// issues ONE acquire fence after the value has been seen
+__device__ __forceinline__ unsigned ld_relaxed(const unsigned* p) {
   unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
@@ -316,7 +318,10 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
         // ---- gather unit: 32 x 32 output pixels of one scale, 4 per thread (2 in flight) ----
         if (b > confirmed && !(P.dbg & 4)) {           // first gather unit of image b in this CTA: wait for its pyramid
           if (lane == 0)
-            while (ld_acquire(&P.done[b]) < (unsigned)P.nb) __nanosleep(64);
+          {
+            while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(200);
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          }
           __syncwarp();
           confirmed = b;
         }
