@@ -17,6 +17,7 @@
 //   its epilogue multiplies by act'(y_prev) so the next layer's dz comes out directly.
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "conv_epi.cuh"
 
 #define TC_THREADS 192
 #define A_TILE_BYTES 16384   // 128 pixels x 64 bf16
@@ -38,55 +39,6 @@ struct ConvTcParams {
   const void* add; int add_dtype; long long add_stride;
   const void* mask; int mask_dtype; long long mask_stride; int mask_act;
 };
-
-__device__ __forceinline__ float load_any(const void* p, int dtype, size_t idx) {
-  return dtype == OF_F32 ? __ldg(reinterpret_cast<const float*>(p) + idx)
-                         : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[idx]);
-}
-__device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == OF_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == OF_ACT_LEAKY) return v > 0.f ? v : 0.3f * v;
-  return v;
-}
-__device__ __forceinline__ float act_slope(float y, int act) {
-  if (act == OF_ACT_RELU) return y > 0.f ? 1.f : 0.f;
-  if (act == OF_ACT_LEAKY) return y > 0.f ? 1.f : 0.3f;
-  return 1.f;
-}
-
-// 16 consecutive channels as floats: two 16-byte (bf16) / four 16-byte (f32) vector loads when the
-// run is complete and aligned, scalar (zero-filled) otherwise
-__device__ __forceinline__ void load16(const void* base, int dtype, size_t idx, int nv, float (&o)[16]) {
-  if (dtype == OF_BF16) {
-    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(base) + idx;
-    if (nv == 16 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
-      uint4 q[2];
-      q[0] = __ldg(reinterpret_cast<const uint4*>(p));
-      q[1] = __ldg(reinterpret_cast<const uint4*>(p) + 1);
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(q);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        o[2 * j] = __uint_as_float(w[j] << 16);
-        o[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 16; ++j) o[j] = j < nv ? __bfloat162float(p[j]) : 0.f;
-    }
-  } else {
-    const float* p = reinterpret_cast<const float*>(base) + idx;
-    if (nv == 16 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float4 t = __ldg(reinterpret_cast<const float4*>(p) + j);
-        o[4 * j] = t.x; o[4 * j + 1] = t.y; o[4 * j + 2] = t.z; o[4 * j + 3] = t.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 16; ++j) o[j] = j < nv ? __ldg(p + j) : 0.f;
-    }
-  }
-}
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -342,7 +294,7 @@ int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long s
 }
 
 // packed weights bf16 [taps][rows][cols] as a 3-D map {cols, rows, taps}, box {64, box_rows, 1}
-static int make_weight_map(CUtensorMap* m, const void* base, int taps, int rows, int cols, int box_rows) {
+int of_tc_make_weight_map(CUtensorMap* m, const void* base, int taps, int rows, int cols, int box_rows) {
   void* fn;
   if (int r = of_tc_get_encode(&fn)) return r;
   OF_REQUIRE(((uintptr_t)base & 15) == 0 && cols % 8 == 0, OF_ERR_ARG, "packed weights must be 16-byte aligned");
@@ -364,6 +316,8 @@ static void pick_tile(int Wo, int* TW, int* TH) {
     if (Wo % cands[k] == 0) { *TW = cands[k]; *TH = 128 / cands[k]; return; }
   *TW = 16; *TH = 8;
 }
+
+int of_conv_tc3_try(const of_tc_conv* c, void* stream);   // conv_tc3.cu
 
 extern "C" {
 
@@ -390,6 +344,13 @@ int of_conv_tc_pack_weights(const float* w_hwio, void* packed, int taps, int Cin
 
 int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   OF_REQUIRE(c && c->src[0] && c->wpacked && c->out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");
+  OF_REQUIRE(c->n_mma >= 16 && c->n_mma <= 256 && c->n_mma % 16 == 0 && c->n_valid <= c->n_mma && c->n_valid > 0,
+             OF_ERR_SHAPE, "n_mma %d / n_valid %d unsupported", c->n_mma, c->n_valid);
+  OF_REQUIRE(c->n_rows >= c->n_valid && c->k_pad % 64 == 0 && of_valid_dtype(c->out_dtype), OF_ERR_SHAPE,
+             "bad packed weight dims / out dtype");
+  for (int s = 0; s < c->num_src; ++s) OF_REQUIRE(c->src[s] && c->src_c[s] > 0, OF_ERR_ARG, "bad source %d", s);
+  if (int r = of_conv_tc3_try(c, stream)) return r < 0 || r > 1 ? r : 0;    // 3x3 / stride-1 fast path
   OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");
   OF_REQUIRE(c->stride == 1 || c->stride == 2, OF_ERR_UNSUPPORTED, "stride %d unsupported", c->stride);
   OF_REQUIRE(c->n_mma >= 16 && c->n_mma <= 256 && c->n_mma % 16 == 0 && c->n_valid <= c->n_mma && c->n_valid > 0,
@@ -445,7 +406,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
       return r;
   }
   if (c->num_src == 1) tmA[1] = tmA[0];
-  if (int r = make_weight_map(&tmB, c->wpacked, P.taps, c->n_rows, c->k_pad, c->n_mma)) return r;
+  if (int r = of_tc_make_weight_map(&tmB, c->wpacked, P.taps, c->n_rows, c->k_pad, c->n_mma)) return r;
 
   size_t smem = 1024 + (size_t)P.stages * stage_bytes + (2 * MAX_STAGES + 4) * sizeof(uint64_t) + 16;
   static bool attr_set = false;

@@ -1,0 +1,312 @@
+// K10 fast path: 3x3 / stride-1 convolution (fprop and dgrad) as a tcgen05 / TMEM implicit GEMM with
+// operand REUSE in shared memory - the layers that hold > 90 % of the conv FLOPs of the step
+// (model.py:104-114 decoder chains, resnet/models.py:17-24 residual blocks).
+//
+// conv_tc.cu reloads a 128-pixel x 64-channel A tile and a weight tile for each of the 9 taps:
+// 288 KB of L2 -> SM traffic per 128 pixels per 64 channels at Cout = 128, which bounds the kernel by
+// L2 bandwidth (~650 TFLOP/s measured).  Here
+//   * one CTA step covers a SUPER-TILE of 256 output pixels (TW x 2*TH, two 128-row accumulators),
+//   * per (source, 64-channel chunk, kw) ONE TMA box {64, TW, 2*TH + 2} - the "slab" - lands in
+//     shared memory; the three kh taps of both halves are UMMA descriptors into the same slab at row
+//     offsets that are multiples of 8 rows (1024 B), so the 128-byte swizzle phase is preserved,
+//   * every weight tile (tap, chunk) is loaded once per super-tile and used by both halves.
+// L2 -> SM traffic per 128 pixels per chunk: (3 * 36 KB + 9 * 16 KB) / 2 = 126 KB (2.3x less).
+// Two rings (A slabs, B weight tiles) with mbarrier full/empty pairs; D = 2 halves x 2 buffers x
+// n_mma TMEM columns (<= 512), so the epilogue of super-tile i overlaps the MMAs of i+1.
+// Warp roles as conv_tc.cu: warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer.
+#include <stdlib.h>
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "conv_epi.cuh"
+
+#define T3_THREADS 192
+#define T3_MAX_A 3
+#define T3_MAX_B 12
+
+int of_tc_make_view_map(CUtensorMap* m, const void* base, int c_used, long long w_stride, long long h_stride,
+                        long long n_stride, int N, int H, int W, int box_w, int box_h, int sw, int sh);
+int of_tc_make_weight_map(CUtensorMap* m, const void* base, int taps, int rows, int cols, int box_rows);
+
+struct Conv3Params {
+  int num_src;
+  int kchunks[2], kbase[2];
+  int pad_t, pad_l, sign;
+  int NB, Ho, Wo;
+  int TW, TH, tiles_w, tiles_h, m_tiles;   // super-tile = TW x 2*TH output pixels
+  int n_mma;
+  int na, nb;                              // ring depths
+  int slab_bytes, btile_bytes;
+  int tmem_cols;
+  ConvEpi E;
+};
+
+__global__ void __launch_bounds__(T3_THREADS, 1)
+conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ Conv3Params P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* a_ring = base;
+  uint8_t* b_ring = base + (size_t)P.na * P.slab_bytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(b_ring + (size_t)P.nb * P.btile_bytes);
+  uint64_t* a_empty = a_full + T3_MAX_A;
+  uint64_t* b_full = a_empty + T3_MAX_A;
+  uint64_t* b_empty = b_full + T3_MAX_B;
+  uint64_t* tmem_full = b_empty + T3_MAX_B;    // [2]
+  uint64_t* tmem_empty = tmem_full + 2;        // [2]
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  __shared__ float s_bias[128];                     // n_mma <= 128: bias read once, not per chunk per pixel
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < 128) s_bias[threadIdx.x] = (P.E.bias && (int)threadIdx.x < P.E.n_valid) ? P.E.bias[threadIdx.x] : 0.f;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P.na; ++s) { tc::mbar_init(&a_full[s], 1); tc::mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < P.nb; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
+    for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full[b], 1); tc::mbar_init(&tmem_empty[b], 4); }
+    tc::fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) {
+    tc::prefetch_tmap(&tmA0);
+    if (P.num_src > 1) tc::prefetch_tmap(&tmA1);
+    tc::prefetch_tmap(&tmB);
+  }
+  if (warp == 5) {
+    tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols);
+    tc::tmem_relinquish();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_base_slot;
+  const int SH = 2 * P.TH;                                        // super-tile height
+  // slab start row relative to the super-tile's first output row, and the slab row of tap kh
+  const int slab_dh = P.sign > 0 ? -P.pad_t : -(2 - P.pad_t);
+
+  if (warp == 4) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
+      for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x) {
+        int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
+        int th_i = r % P.tiles_h; int n = r / P.tiles_h;
+        int w0 = tw_i * P.TW, h0 = th_i * SH;
+        for (int s = 0; s < P.num_src; ++s) {
+          const CUtensorMap* tmA = s == 0 ? &tmA0 : &tmA1;
+          for (int kc = 0; kc < P.kchunks[s]; ++kc) {
+            for (int kw = 0; kw < 3; ++kw) {
+              tc::mbar_wait(&a_empty[as], aph ^ 1);
+              tc::mbar_expect_tx(&a_full[as], (uint32_t)P.slab_bytes);
+              tc::tma_load_4d(a_ring + (size_t)as * P.slab_bytes, tmA, &a_full[as], kc * 64,
+                              w0 + P.sign * (kw - P.pad_l), h0 + slab_dh, n);
+              if (++as == P.na) { as = 0; aph ^= 1; }
+              for (int kh = 0; kh < 3; ++kh) {
+                tc::mbar_wait(&b_empty[bs], bph ^ 1);
+                tc::mbar_expect_tx(&b_full[bs], (uint32_t)(P.n_mma * 128));
+                tc::tma_load_3d(b_ring + (size_t)bs * P.btile_bytes, &tmB, &b_full[bs], P.kbase[s] + kc * 64, 0,
+                                kh * 3 + kw);
+                if (++bs == P.nb) { bs = 0; bph ^= 1; }
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 0, 0);
+      const int slabs_per_tile = 3 * (P.kchunks[0] + (P.num_src > 1 ? P.kchunks[1] : 0));
+      int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x, ++it) {
+        int buf = it & 1;
+        uint32_t use = (uint32_t)(it >> 1);
+        tc::mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+        tc::fence_after_sync();
+        const uint32_t d0 = tmem_base + (uint32_t)(buf * 2 * P.n_mma);
+        for (int sl = 0; sl < slabs_per_tile; ++sl) {
+          tc::mbar_wait(&a_full[as], aph);
+          tc::fence_after_sync();
+          const uint32_t slab = tc::smem_u32(a_ring + (size_t)as * P.slab_bytes);
+          for (int kh = 0; kh < 3; ++kh) {
+            tc::mbar_wait(&b_full[bs], bph);
+            tc::fence_after_sync();
+            const uint64_t bdesc = tc::desc_sw128_kmajor(tc::smem_u32(b_ring + (size_t)bs * P.btile_bytes));
+            const int tap_row = P.sign > 0 ? kh : 2 - kh;
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                             (sl | kh | k) ? 1u : 0u);
+            }
+            tc::mma_commit(&b_empty[bs]);
+            if (++bs == P.nb) { bs = 0; bph ^= 1; }
+          }
+          tc::mma_commit(&a_empty[as]);
+          if (sl == slabs_per_tile - 1) tc::mma_commit(&tmem_full[buf]);
+          if (++as == P.na) { as = 0; aph ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..3 =====================
+    int it = 0;
+    for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x, ++it) {
+      int buf = it & 1;
+      uint32_t use = (uint32_t)(it >> 1);
+      int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
+      int th_i = r % P.tiles_h; int n = r / P.tiles_h;
+      int row = warp * 32 + lane;                       // accumulator row == TMEM lane == pixel in the half
+      tc::mbar_wait(&tmem_full[buf], use & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int hh = 0; hh < 2; ++hh) {
+        int ph = th_i * SH + hh * P.TH + row / P.TW, pw = tw_i * P.TW + row % P.TW;
+        bool valid = ph < P.Ho && pw < P.Wo;
+        size_t pix = ((size_t)n * P.Ho + ph) * P.Wo + pw;
+        uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)((buf * 2 + hh) * P.n_mma);
+        // software pipeline over 16-column chunks: the TMEM load of chunk c+1 and the global loads of
+        // its add / mask operands are in flight while chunk c is finished and stored
+        uint32_t rr[2][16];
+        uint4 araw[2][4], mraw[2][4];                    // raw add / mask operands of one chunk (bf16: 2 x uint4, f32: 4)
+        const int nchunks = P.n_mma >> 4;
+        auto issue = [&](int c, int slot) {
+          __syncwarp();                                  // tcgen05.ld is .sync.aligned: reconverge first
+          tc::tmem_ld16(taddr + (uint32_t)(c * 16), rr[slot]);
+          if (valid && c * 16 + 16 <= P.E.n_valid) {
+            if (P.E.add) {
+              const int nq = P.E.add_dtype == OF_BF16 ? 2 : 4;
+              const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.add) +
+                                                              (pix * P.E.add_stride + c * 16) * (P.E.add_dtype == OF_BF16 ? 2 : 4));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) if (k < nq) araw[slot][k] = __ldg(q + k);
+            }
+            if (P.E.mask) {
+              const int nq = P.E.mask_dtype == OF_BF16 ? 2 : 4;
+              const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.mask) +
+                                                              (pix * P.E.mask_stride + c * 16) * (P.E.mask_dtype == OF_BF16 ? 2 : 4));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) if (k < nq) mraw[slot][k] = __ldg(q + k);
+            }
+          }
+        };
+        auto finish = [&](int c, int slot) {             // slot is a compile-time constant at both call sites
+          __syncwarp();
+          tc::tmem_ld_wait();                            // chunk c has landed (only one tcgen05.ld is ever pending here)
+          if (c + 1 < nchunks) issue(c + 1, slot ^ 1);
+          const int c0 = c * 16;
+          if (!(valid && c0 < P.E.n_valid)) return;
+          if (c0 + 16 <= P.E.n_valid && (P.E.out_stride & 7) == 0 && (P.E.add == nullptr || (P.E.add_stride & 7) == 0) &&
+              (P.E.mask == nullptr || (P.E.mask_stride & 7) == 0)) {
+            float v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c0 + j];
+            if (P.E.add) {
+              float t[16];
+              unpack16(araw[slot], P.E.add_dtype, t);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += t[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], P.E.act);
+            if (P.E.mask) {
+              float t[16];
+              unpack16(mraw[slot], P.E.mask_dtype, t);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], P.E.mask_act);
+            }
+            store16(P.E, pix, c0, v);
+          } else {
+            epilogue_store16(P.E, pix, c0, rr[slot]);    // ragged channel tail / unaligned strides: generic path
+          }
+        };
+        issue(0, 0);
+#pragma unroll 1
+        for (int c = 0; c < nchunks; c += 2) {
+          finish(c, 0);
+          if (c + 1 < nchunks) finish(c + 1, 1);
+        }
+      }
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tmem_empty[buf]);
+    }
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 5) tc::tmem_dealloc(tmem_base, (uint32_t)P.tmem_cols);
+}
+
+// Returns 1 if handled, 0 if the shape is not this kernel's (caller falls back to conv_tc_kernel), < 0 / > 0 on error.
+int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
+  const bool view = c->view_w_stride > 0;
+  if (view || c->KH != 3 || c->KW != 3 || c->stride != 1 || (c->stride_w > 1) || (c->stride_h > 1)) return 0;
+  if (c->n_mma > 128) return 0;                         // 2 halves x 2 buffers x n_mma TMEM columns <= 512
+  if (getenv("OF_CONV_NO_SLAB")) return 0;
+  Conv3Params P;
+  memset(&P, 0, sizeof(P));
+  P.num_src = c->num_src;
+  int kb = 0;
+  for (int s = 0; s < c->num_src; ++s) {
+    P.kchunks[s] = (c->src_c[s] + 63) / 64;
+    P.kbase[s] = kb;
+    kb += P.kchunks[s] * 64;
+  }
+  OF_REQUIRE(kb <= c->k_pad, OF_ERR_SHAPE, "packed K %d smaller than the sources' %d", c->k_pad, kb);
+  P.pad_t = c->pad_t; P.pad_l = c->pad_l; P.sign = c->sign >= 0 ? 1 : -1;
+  P.NB = c->N; P.Ho = c->Ho; P.Wo = c->Wo;
+  // narrow tiles keep the halo overhead (2*TH + 2) / (2*TH) small; TW must be a multiple of 8 rows
+  P.TW = (c->Wo % 16 == 0 || c->Wo % 8 != 0) ? 16 : 8;
+  P.TH = 128 / P.TW;
+  P.tiles_w = (c->Wo + P.TW - 1) / P.TW;
+  P.tiles_h = (c->Ho + 2 * P.TH - 1) / (2 * P.TH);
+  long long mt = (long long)c->N * P.tiles_w * P.tiles_h;
+  OF_REQUIRE(mt > 0 && mt < (1ll << 30), OF_ERR_SHAPE, "bad output tiling");
+  P.m_tiles = (int)mt;
+  P.n_mma = c->n_mma;
+  P.slab_bytes = (2 * P.TH + 2) * P.TW * 128;
+  P.btile_bytes = ((c->n_mma * 128) + 1023) / 1024 * 1024;
+  // ring depths: TMA latency (~2k cycles loaded) must be covered by the MMAs of the slots in flight.
+  // One slab feeds 24 MMAs (~1.6k cycles at Cout = 128), one weight tile 8 (~0.5k): 3 slabs + >= 5 tiles.
+  const int budget = 204 * 1024;
+  P.na = 3;
+  P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes;
+  if (P.nb < 5) { P.na = 2; P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes; }
+  if (P.nb > T3_MAX_B) P.nb = T3_MAX_B;
+  if (const char* e = getenv("OF_T3_RINGS")) {            // tuning hook: "na,nb"
+    int a_ = 0, b_ = 0;
+    if (sscanf(e, "%d,%d", &a_, &b_) == 2 && a_ >= 1 && a_ <= T3_MAX_A && b_ >= 3 && b_ <= T3_MAX_B &&
+        a_ * P.slab_bytes + b_ * P.btile_bytes <= 220 * 1024) { P.na = a_; P.nb = b_; }
+  }
+  if (P.nb < 3) return 0;
+  int cols = 4 * c->n_mma;
+  P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+  P.E.out = c->out; P.E.out_dtype = c->out_dtype; P.E.out_stride = c->out_stride;
+  P.E.bias = c->bias; P.E.act = c->act;
+  P.E.add = c->add; P.E.add_dtype = c->add_dtype; P.E.add_stride = c->add_stride;
+  P.E.mask = c->mask; P.E.mask_dtype = c->mask_dtype; P.E.mask_stride = c->mask_stride; P.E.mask_act = c->mask_act;
+  P.E.n_valid = c->n_valid;
+
+  CUtensorMap tmA[2], tmB;
+  memset(tmA, 0, sizeof(tmA));
+  for (int s = 0; s < c->num_src; ++s)
+    if (int r = of_tc_make_view_map(&tmA[s], c->src[s], c->src_c[s], c->src_stride[s], (long long)c->W * c->src_stride[s],
+                                    (long long)c->H * c->W * c->src_stride[s], c->N, c->H, c->W, P.TW, 2 * P.TH + 2, 1, 1))
+      return r;
+  if (c->num_src == 1) tmA[1] = tmA[0];
+  if (int r = of_tc_make_weight_map(&tmB, c->wpacked, 9, c->n_rows, c->k_pad, c->n_mma)) return r;
+
+  size_t smem = 1024 + (size_t)P.na * P.slab_bytes + (size_t)P.nb * P.btile_bytes +
+                (2 * T3_MAX_A + 2 * T3_MAX_B + 4) * sizeof(uint64_t) + 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    attr_set = true;
+  }
+  int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
+  conv_tc3_kernel<<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
+  if (int r = of_launch_check("conv_tc3_kernel")) return r;
+  return 1;
+}

@@ -1,2 +1,2 @@
-timeout 300 python bench.py --workload loss --no-cpu-baseline --steps 8 --no-graph > gpurun_out/plain_loss.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:loss_fused -s 4 -c 1 -o gpurun_out/prof_loss -f python bench.py --workload loss --no-cpu-baseline --steps 8 --no-graph > gpurun_out/ncu_loss.log 2>&1
-tail -2 gpurun_out/ncu_loss.log
+timeout 300 python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv_tc3 -s 214 -c 2 -o gpurun_out/prof_tc3 -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_tc3.log 2>&1
+tail -2 gpurun_out/ncu_tc3.log
