@@ -13,13 +13,21 @@
 // L2 -> SM traffic per 128 pixels per chunk: (3 * 36 KB + 9 * 16 KB) / 2 = 126 KB (2.3x less).
 // Two rings (A slabs, B weight tiles) with mbarrier full/empty pairs; D = 2 halves x 2 buffers x
 // n_mma TMEM columns (<= 512), so the epilogue of super-tile i overlaps the MMAs of i+1.
-// Warp roles as conv_tc.cu: warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer.
+// Warp roles: warps 0-7 epilogue (warp & 3 = TMEM lane quarter, warp >> 2 = half of the super-tile),
+// warp 8 TMA producer, warp 9 MMA issuer.
+// Epilogue: with 4 epilogue warps the kernel was epilogue-bound (mainloop alone 1350 TFLOP/s at
+// Cout = 128, 880 with the epilogue); 8 warps, one half each, bring it to ~1200.  An optional variant
+// (COAL) sends bf16 outputs through a per-warp swizzled staging tile (32 pixels x 64 channels, 4 KB) so
+// 8 lanes cover one 128-byte pixel row per st.global.v4, and brings the dgrad activation mask in the
+// same way; it measured slightly slower than the direct row-per-thread stores and is off by default.
 #include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "conv_epi.cuh"
 
-#define T3_THREADS 192
+#define T3_THREADS 320
+#define T3_EPI_WARPS 8
+#define T3_WSTG_BYTES 4096
 #define T3_MAX_A 3
 #define T3_MAX_B 12
 
@@ -37,9 +45,13 @@ struct Conv3Params {
   int na, nb;                              // ring depths
   int slab_bytes, btile_bytes;
   int tmem_cols;
+  int tw_shift;                            // log2(TW)
+  int coal;                                // bf16 output through the per-warp staging tile (coalesced stores)
+  int dbg;                                 // profiling only: 1 = no epilogue memory traffic, 2 = no epilogue at all
   ConvEpi E;
 };
 
+template <bool COAL>
 __global__ void __launch_bounds__(T3_THREADS, 1)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ Conv3Params P) {
@@ -47,7 +59,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* a_ring = base;
   uint8_t* b_ring = base + (size_t)P.na * P.slab_bytes;
-  uint64_t* a_full = reinterpret_cast<uint64_t*>(b_ring + (size_t)P.nb * P.btile_bytes);
+  uint8_t* staging = b_ring + (size_t)P.nb * P.btile_bytes;           // one 4 KB tile per epilogue warp
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(staging + (COAL ? T3_EPI_WARPS * T3_WSTG_BYTES : 0));
   uint64_t* a_empty = a_full + T3_MAX_A;
   uint64_t* b_full = a_empty + T3_MAX_A;
   uint64_t* b_empty = b_full + T3_MAX_B;
@@ -61,15 +74,15 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   if (threadIdx.x == 0) {
     for (int s = 0; s < P.na; ++s) { tc::mbar_init(&a_full[s], 1); tc::mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < P.nb; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
-    for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full[b], 1); tc::mbar_init(&tmem_empty[b], 4); }
+    for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full[b], 1); tc::mbar_init(&tmem_empty[b], T3_EPI_WARPS); }
     tc::fence_barrier_init();
   }
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tc::prefetch_tmap(&tmA0);
     if (P.num_src > 1) tc::prefetch_tmap(&tmA1);
     tc::prefetch_tmap(&tmB);
   }
-  if (warp == 5) {
+  if (warp == 9) {
     tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols);
     tc::tmem_relinquish();
   }
@@ -81,7 +94,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   // slab start row relative to the super-tile's first output row, and the slab row of tap kh
   const int slab_dh = P.sign > 0 ? -P.pad_t : -(2 - P.pad_t);
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
@@ -110,7 +123,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 0, 0);
@@ -150,44 +163,72 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       }
     }
   } else {
-    // ===================== epilogue warps 0..3 =====================
+    // ===================== epilogue warps 0..7 =====================
+    const int q = warp & 3, hh = warp >> 2;             // TMEM lane quarter, half of the super-tile
+    uint8_t* wstg = staging + (size_t)warp * T3_WSTG_BYTES;
+    const int r_sub = lane >> 3, u = lane & 7;          // copy phase: 8 lanes x 16 B cover one 128-byte pixel row
+    const int row = q * 32 + lane;                      // accumulator row == TMEM lane == pixel in the half
+    const int nch = (P.E.n_valid + 15) >> 4;            // 16-column chunks that hold real channels
+    const bool mask_coal = COAL && P.E.mask != nullptr;   // host: COAL implies a bf16, 16-byte-aligned mask
     int it = 0;
     for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x, ++it) {
       int buf = it & 1;
       uint32_t use = (uint32_t)(it >> 1);
       int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
       int th_i = r % P.tiles_h; int n = r / P.tiles_h;
-      int row = warp * 32 + lane;                       // accumulator row == TMEM lane == pixel in the half
+      const int h_base = th_i * SH + hh * P.TH, w_base = tw_i * P.TW;
+      const int ph = h_base + (row >> P.tw_shift), pw = w_base + (row & (P.TW - 1));
+      const bool valid = ph < P.Ho && pw < P.Wo && !(P.dbg & 1);
+      const size_t pix = ((size_t)n * P.Ho + ph) * P.Wo + pw;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((buf * 2 + hh) * P.n_mma);
+
+      // copy-phase pixel of (i, lane): staging row i*4 + r_sub
+      auto copy_pix = [&](int i, size_t& cpix) -> bool {
+        int rr_ = q * 32 + i * 4 + r_sub;
+        int ch_ = h_base + (rr_ >> P.tw_shift), cw_ = w_base + (rr_ & (P.TW - 1));
+        cpix = ((size_t)n * P.Ho + ch_) * P.Wo + cw_;
+        return ch_ < P.Ho && cw_ < P.Wo && !(P.dbg & 1);
+      };
+      uint4 mreg[8];
+      auto load_mask = [&](int g) {                     // coalesced: 4 pixel rows x 128 B per instruction
+        const int ch = g * 64 + u * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          size_t cpix;
+          bool ok = copy_pix(i, cpix) && ch + 8 <= P.E.n_valid;
+          mreg[i] = ok ? __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(P.E.mask) +
+                                                              cpix * P.E.mask_stride + ch))
+                       : make_uint4(0, 0, 0, 0);
+        }
+      };
+      if (mask_coal && !(P.dbg & 2)) load_mask(0);       // in flight while the accumulator is still being produced
+
       tc::mbar_wait(&tmem_full[buf], use & 1);
       tc::fence_after_sync();
-#pragma unroll 1
-      for (int hh = 0; hh < 2; ++hh) {
-        int ph = th_i * SH + hh * P.TH + row / P.TW, pw = tw_i * P.TW + row % P.TW;
-        bool valid = ph < P.Ho && pw < P.Wo;
-        size_t pix = ((size_t)n * P.Ho + ph) * P.Wo + pw;
-        uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)((buf * 2 + hh) * P.n_mma);
+      if (!(P.dbg & 2)) {
         // software pipeline over 16-column chunks: the TMEM load of chunk c+1 and the global loads of
-        // its add / mask operands are in flight while chunk c is finished and stored
+        // its add (and row-wise mask) operands are in flight while chunk c is finished
         uint32_t rr[2][16];
-        uint4 araw[2][4], mraw[2][4];                    // raw add / mask operands of one chunk (bf16: 2 x uint4, f32: 4)
-        const int nchunks = P.n_mma >> 4;
+        // raw add / mask operands of one chunk (bf16: 2 x uint4, f32: 4); COAL: add is bf16, mask comes via staging
+        uint4 araw[2][COAL ? 2 : 4], mraw[2][COAL ? 1 : 4];
+        const int nchunks = COAL ? nch : (P.n_mma >> 4);
         auto issue = [&](int c, int slot) {
           __syncwarp();                                  // tcgen05.ld is .sync.aligned: reconverge first
           tc::tmem_ld16(taddr + (uint32_t)(c * 16), rr[slot]);
           if (valid && c * 16 + 16 <= P.E.n_valid) {
             if (P.E.add) {
-              const int nq = P.E.add_dtype == OF_BF16 ? 2 : 4;
-              const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.add) +
-                                                              (pix * P.E.add_stride + c * 16) * (P.E.add_dtype == OF_BF16 ? 2 : 4));
+              const int nq = (COAL || P.E.add_dtype == OF_BF16) ? 2 : 4;
+              const uint4* qd = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.add) +
+                                                               (pix * P.E.add_stride + c * 16) * (nq == 2 ? 2 : 4));
 #pragma unroll
-              for (int k = 0; k < 4; ++k) if (k < nq) araw[slot][k] = __ldg(q + k);
+              for (int k = 0; k < (COAL ? 2 : 4); ++k) if (k < nq) araw[slot][k] = __ldg(qd + k);
             }
-            if (P.E.mask) {
+            if (!COAL && P.E.mask) {
               const int nq = P.E.mask_dtype == OF_BF16 ? 2 : 4;
-              const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.mask) +
-                                                              (pix * P.E.mask_stride + c * 16) * (P.E.mask_dtype == OF_BF16 ? 2 : 4));
+              const uint4* qd = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.mask) +
+                                                               (pix * P.E.mask_stride + c * 16) * (P.E.mask_dtype == OF_BF16 ? 2 : 4));
 #pragma unroll
-              for (int k = 0; k < 4; ++k) if (k < nq) mraw[slot][k] = __ldg(q + k);
+              for (int k = 0; k < 4; ++k) if (k < nq) mraw[slot][k] = __ldg(qd + k);
             }
           }
         };
@@ -196,6 +237,41 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           tc::tmem_ld_wait();                            // chunk c has landed (only one tcgen05.ld is ever pending here)
           if (c + 1 < nchunks) issue(c + 1, slot ^ 1);
           const int c0 = c * 16;
+          if constexpr (COAL) {
+            float v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c0 + j];
+            if (P.E.add && valid) {
+              float t[16];
+              uint4 a4[4] = {araw[slot][0], araw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+              unpack16(a4, OF_BF16, t);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += t[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], P.E.act);
+            // own row of the swizzled staging tile: 16-byte units u0, u0 + 1 of the 128-byte row
+            uint8_t* rowp = wstg + lane * 128;
+            const int u0 = (c0 & 63) >> 3;
+            uint4* p0 = reinterpret_cast<uint4*>(rowp + ((u0 ^ (lane & 7)) << 4));
+            uint4* p1 = reinterpret_cast<uint4*>(rowp + (((u0 + 1) ^ (lane & 7)) << 4));
+            if (P.E.mask) {
+              float t[16];
+              uint4 m[4] = {*p0, *p1, make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+              unpack16(m, OF_BF16, t);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], P.E.mask_act);
+            }
+            uint32_t pk[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              __nv_bfloat162 t2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+              pk[j] = *reinterpret_cast<uint32_t*>(&t2);
+            }
+            *p0 = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            *p1 = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            return;
+          } else {
           if (!(valid && c0 < P.E.n_valid)) return;
           if (c0 + 16 <= P.E.n_valid && (P.E.out_stride & 7) == 0 && (P.E.add == nullptr || (P.E.add_stride & 7) == 0) &&
               (P.E.mask == nullptr || (P.E.mask_stride & 7) == 0)) {
@@ -220,12 +296,39 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           } else {
             epilogue_store16(P.E, pix, c0, rr[slot]);    // ragged channel tail / unaligned strides: generic path
           }
+          }
+        };
+        auto begin_group = [&](int g) {                  // mask of group g: registers -> staging, prefetch group g+1
+          if (!mask_coal) return;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            int rs = i * 4 + r_sub;
+            *reinterpret_cast<uint4*>(wstg + rs * 128 + ((u ^ (rs & 7)) << 4)) = mreg[i];
+          }
+          __syncwarp();
+          if ((g + 1) * 64 < P.E.n_valid) load_mask(g + 1);
+        };
+        auto flush_group = [&](int g) {                  // staging -> global, 4 full pixel rows per instruction
+          __syncwarp();
+          const int ch = g * 64 + u * 8;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            int rs = i * 4 + r_sub;
+            size_t cpix;
+            bool ok = copy_pix(i, cpix) && ch + 8 <= P.E.n_valid;
+            uint4 d = *reinterpret_cast<const uint4*>(wstg + rs * 128 + ((u ^ (rs & 7)) << 4));
+            if (ok) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(P.E.out) + cpix * P.E.out_stride + ch) = d;
+          }
+          __syncwarp();
         };
         issue(0, 0);
 #pragma unroll 1
         for (int c = 0; c < nchunks; c += 2) {
+          if (COAL && (c & 3) == 0) begin_group(c >> 2);
           finish(c, 0);
           if (c + 1 < nchunks) finish(c + 1, 1);
+          const int last = c + 1 < nchunks ? c + 1 : c;
+          if (COAL && ((last & 3) == 3 || last == nchunks - 1)) flush_group(last >> 2);
         }
       }
       tc::fence_before_sync();
@@ -236,7 +339,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 5) tc::tmem_dealloc(tmem_base, (uint32_t)P.tmem_cols);
+  if (warp == 9) tc::tmem_dealloc(tmem_base, (uint32_t)P.tmem_cols);
 }
 
 // Returns 1 if handled, 0 if the shape is not this kernel's (caller falls back to conv_tc_kernel), < 0 / > 0 on error.
@@ -268,17 +371,29 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.n_mma = c->n_mma;
   P.slab_bytes = (2 * P.TH + 2) * P.TW * 128;
   P.btile_bytes = ((c->n_mma * 128) + 1023) / 1024 * 1024;
+  P.tw_shift = P.TW == 16 ? 4 : 3;
+  // coalesced bf16 output through the per-warp staging tile: opt-in (OF_T3_COAL=1).  Measured on B200
+  // at N8 192x640: 128->128 242 us staged vs 239 us direct, 64->32 111 vs 97 - with 8 epilogue warps the
+  // row-per-thread stores are no longer the limit and the staging round trip costs more than it saves.
+  const bool mask_coal_ok = c->mask == nullptr || (c->mask_dtype == OF_BF16 && (c->mask_stride % 8) == 0 &&
+                                                   ((uintptr_t)c->mask & 15) == 0);
+  const bool add_coal_ok = c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 8) == 0 &&
+                                                 ((uintptr_t)c->add & 15) == 0 && (c->n_valid % 16) == 0);
+  P.coal = c->out_dtype == OF_BF16 && (c->out_stride % 8) == 0 && ((uintptr_t)c->out & 15) == 0 && c->n_valid >= 8 &&
+           (c->n_valid % 8) == 0 && mask_coal_ok && add_coal_ok && getenv("OF_T3_COAL") != nullptr;
+  if (const char* e = getenv("OF_T3_DBG")) P.dbg = atoi(e);
   // ring depths: TMA latency (~2k cycles loaded) must be covered by the MMAs of the slots in flight.
-  // One slab feeds 24 MMAs (~1.6k cycles at Cout = 128), one weight tile 8 (~0.5k): 3 slabs + >= 5 tiles.
-  const int budget = 204 * 1024;
+  // One slab feeds 24 MMAs (~1.6k cycles at Cout = 128), one weight tile 8 (~0.5k): 3 slabs + >= 4 tiles.
+  const int stg_bytes = P.coal ? T3_EPI_WARPS * T3_WSTG_BYTES : 0;
+  const int budget = 206 * 1024 - stg_bytes;
   P.na = 3;
   P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes;
-  if (P.nb < 5) { P.na = 2; P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes; }
+  if (P.nb < 4) { P.na = 2; P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes; }
   if (P.nb > T3_MAX_B) P.nb = T3_MAX_B;
   if (const char* e = getenv("OF_T3_RINGS")) {            // tuning hook: "na,nb"
     int a_ = 0, b_ = 0;
     if (sscanf(e, "%d,%d", &a_, &b_) == 2 && a_ >= 1 && a_ <= T3_MAX_A && b_ >= 3 && b_ <= T3_MAX_B &&
-        a_ * P.slab_bytes + b_ * P.btile_bytes <= 220 * 1024) { P.na = a_; P.nb = b_; }
+        a_ * P.slab_bytes + b_ * P.btile_bytes <= budget) { P.na = a_; P.nb = b_; }
   }
   if (P.nb < 3) return 0;
   int cols = 4 * c->n_mma;
@@ -298,15 +413,17 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   if (c->num_src == 1) tmA[1] = tmA[0];
   if (int r = of_tc_make_weight_map(&tmB, c->wpacked, 9, c->n_rows, c->k_pad, c->n_mma)) return r;
 
-  size_t smem = 1024 + (size_t)P.na * P.slab_bytes + (size_t)P.nb * P.btile_bytes +
+  size_t smem = 1024 + (size_t)P.na * P.slab_bytes + (size_t)P.nb * P.btile_bytes + stg_bytes +
                 (2 * T3_MAX_A + 2 * T3_MAX_B + 4) * sizeof(uint64_t) + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
-  conv_tc3_kernel<<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
+  if (P.coal) conv_tc3_kernel<true><<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
+  else conv_tc3_kernel<false><<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
   if (int r = of_launch_check("conv_tc3_kernel")) return r;
   return 1;
 }

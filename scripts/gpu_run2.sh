@@ -1,2 +1,4 @@
-timeout 900 python -m pytest tests/test_gpu_conv_tc.py tests/test_gpu_net.py -m gpu -q --timeout 180 > gpurun_out/t_tc.log 2>&1; tail -3 gpurun_out/t_tc.log
-timeout 600 python bench.py --no-cpu-baseline 2>&1 | tail -1 | grep -o '"ms_per_step": [0-9.]*'
+set -x
+python -m pytest tests/test_gpu_conv_tc.py -x -q -m gpu 2>&1 | tail -5
+for v in "" "OF_T3_NO_COAL=1" "OF_T3_DBG=1" "OF_T3_RINGS=2,6" "OF_T3_RINGS=3,3"; do echo "== $v"; env $v python scripts/bench_conv_layer.py; done
+python bench.py --steps 10 --warmup 3 2>&1 | tail -2

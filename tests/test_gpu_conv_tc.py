@@ -124,6 +124,14 @@ def test_tc_dgrad(cuda, cfg):
     assert rel_err(dz, ref2) <= 2 ** -7
 
 
+@pytest.mark.parametrize("cfg", [(2, 24, 32, 64, 3, 64, 1), (1, 16, 48, 128, 3, 96, 1), (1, 9, 13, 64, 3, 32, 1)])
+def test_tc3_staged_epilogue_variant(cuda, cfg, monkeypatch):
+    """conv_tc3.cu's optional staged (coalesced) epilogue, OF_T3_COAL=1: same results as the default."""
+    monkeypatch.setenv("OF_T3_COAL", "1")
+    test_tc_fprop(cuda, cfg)
+    test_tc_dgrad(cuda, cfg)
+
+
 def test_tc_dgrad_segments(cuda):
     """dgrad of the first decoder conv: one launch per concat segment (features | cv+flow)."""
     from optical_flow_b200 import conv_tc
