@@ -419,20 +419,9 @@ def bench_train(args, dev, world, rank):
     peaks = measured_peaks()
     comm = None
     if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8)
-        if rank == 0:
-            import ctypes
-            buf = (ctypes.c_char * 128)()
-            L.check(L.load().of_comm_unique_id(buf), "of_comm_unique_id")
-            uid = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
-        uid = uid.to(dev)
-        dist.broadcast(uid, 0)
-        import ctypes
-        raw = bytes(uid.cpu().numpy().tobytes())
-        out = ctypes.c_void_p()
-        L.check(L.load().of_comm_init(raw, world, rank, ctypes.byref(out)), "of_comm_init")
-        comm = out
-    tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm, world_size=world)
+        from optical_flow_b200 import parallel
+        comm = parallel.CAbiComm.from_torch_dist(dev)          # the library's own NCCL communicator
+    tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm)
     nsets = 2
     batches = [synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev) for k in range(nsets)]
     loss_acc = torch.zeros(1, device=dev)

@@ -15,6 +15,7 @@ import torch
 
 from . import _lib as L
 from . import functional as F
+from . import parallel
 from .loss import LossLayer
 from .model import build_flow_net
 
@@ -27,14 +28,16 @@ learning_rate = 1e-4        # train.py:34
 
 class Trainer:
     def __init__(self, height=img_height, width=img_width, pretrained_weights_path=None, lr=learning_rate,
-                 conv_mode="bf16", warp_mode="ref_ij", comm=None, world_size=1, seed=42):
+                 conv_mode="bf16", warp_mode="ref_ij", comm=None, seed=42):
+        """``comm``: None (single replica) or a parallel.CAbiComm / parallel.TorchDistComm; every
+        replica must be built with the same ``seed`` so the weights start identical."""
         self.flow_net = build_flow_net(height, width, pretrained_weights_path, conv_mode=conv_mode,
                                        warp_mode=warp_mode, seed=seed)
         self.loss_layer = LossLayer(warp_mode=warp_mode)
         self.lr = lr
         self.step = 0
         self.comm = comm
-        self.world_size = world_size
+        self.world_size = comm.world_size if comm is not None else 1
 
     @property
     def trainable_weights(self):
@@ -50,12 +53,9 @@ class Trainer:
     def apply_gradients(self):
         """optimizer.apply_gradients (train.py:56): Adam, Keras defaults (eps 1e-7)."""
         st = self.flow_net.store
-        if self.comm is not None and self.world_size > 1:
-            L.check(L.load().of_comm_allreduce_sum_f32(self.comm, L.ptr(st.grad), st.grad.numel(), L.stream_ptr()),
-                    "of_comm_allreduce_sum_f32")
+        scale = parallel.exchange_gradients(st.grad, self.comm)    # sum over replicas; 1/N goes into Adam
         self.step += 1
-        F.adam_step(st.flat, st.grad, st.adam_m, st.adam_v, self.step, lr=self.lr,
-                    grad_scale=1.0 / self.world_size)
+        F.adam_step(st.flat, st.grad, st.adam_m, st.adam_v, self.step, lr=self.lr, grad_scale=scale)
 
     def train_step(self, batch_imgs, step_count=None):
         """train.py:47-61.  Returns (loss_value [0-d device tensor], flows)."""
