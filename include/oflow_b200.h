@@ -64,6 +64,11 @@ int of_warp_features_bwd(const void* feats, const float* flow, const float* d_ou
                          float* d_feats, float* d_flow,
                          int B, int H, int W, int C, int mode, int dtype, void* stream);
 
+/* same, with the incoming gradient d_out in dtype d_out_dtype (bf16 needs bf16 feats) */
+int of_warp_features_bwd_g(const void* feats, const float* flow, const void* d_out, int d_out_dtype,
+                           float* d_feats, float* d_flow,
+                           int B, int H, int W, int C, int mode, int dtype, void* stream);
+
 /* old/image_warp.py:7-78 image_warp (== image_warp_tf :81-153); f32 only. */
 int of_image_warp_fwd(const float* im, const float* flow, float* out, int32_t* idx,
                       int B, int H, int W, int C, void* stream);
@@ -94,6 +99,13 @@ int of_cost_volume_bwd(const void* f1, const void* f2, const void* d_cv,
                        float* d_f1, float* d_f2,
                        int B, int H, int W, int C, int max_disp, int cv_stride,
                        int dtype, void* stream);
+
+/* Same gradient with bf16 tensors end to end (the tensor-core conv path's activation dtype):
+ * d_f1 = dcv/df1 (+ d_f1_add, nullable bf16 (B,H,W,C): the gradient reaching f1 through the decoder's
+ * first conv, model.py:100-104), d_f2 = dcv/df2; both bf16 (B,H,W,C), overwritten.  max_disp == 3 only. */
+int of_cost_volume_bwd_bf16(const void* f1, const void* f2, const void* d_cv, void* d_f1, void* d_f2,
+                            const void* d_f1_add, int B, int H, int W, int C, int max_disp, int cv_stride,
+                            void* stream);
 
 /* ---- fused pyramid losses -------------------------------------------------
  * loss.py:5-32 LossLayer: for each scale s, resize the full-res 6-channel
@@ -188,6 +200,7 @@ typedef struct {
   float* dw;
   int N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, Cin, Cout;
   long long view_w_stride, view_h_stride, view_n_stride; int stride_w, stride_h;   /* as in of_tc_conv */
+  float* db;   /* nullable: bias gradient db[co] = sum_pix dy[pix][co] (f32, Cout), fused into the same launch */
 } of_tc_wgrad;
 int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream);
 /* Stem (model.py:12, Cin = 3, 7x7 / 2) on tensor cores.  of_pack_image_pair8: imgs (B,H,W,6) f32 -> bf16

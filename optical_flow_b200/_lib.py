@@ -48,7 +48,7 @@ class TcWgrad(C.Structure):
                 ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_t", C.c_int), ("pad_l", C.c_int),
                 ("Cin", C.c_int), ("Cout", C.c_int),
                 ("view_w_stride", C.c_longlong), ("view_h_stride", C.c_longlong), ("view_n_stride", C.c_longlong),
-                ("stride_w", C.c_int), ("stride_h", C.c_int)]
+                ("stride_w", C.c_int), ("stride_h", C.c_int), ("db", C.c_void_p)]
 
 
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
@@ -71,6 +71,7 @@ PROTOTYPES = {
     "of_bilinear_sample_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_warp_features_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_warp_features_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_warp_features_bwd_g": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_image_warp_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "of_image_warp_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "of_resize_bilinear": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
@@ -78,6 +79,7 @@ PROTOTYPES = {
     "of_upscale_flow_bwd": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "of_cost_volume_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_cost_volume_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_cost_volume_bwd_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_loss_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "of_loss_l1_pyramid_fwdbwd": (_i, [_vp, _pp, _pp, _ip, _ip, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
     "of_loss_charbonnier_smooth_fwdbwd": (_i, [_vp, _pp, _pp, _ip, _ip, _i, _vp, _i, _i, _i, _vp, _vp]),

@@ -149,10 +149,14 @@ def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=Tru
     d.dw = dw.data_ptr()
     d.N, d.H, d.W, d.Ho, d.Wo = N, H, W, Ho, Wo
     d.KH, d.KW, d.stride, d.pad_t, d.pad_l, d.Cin, d.Cout = KH, KW, stride, pt, pl, Cin, Cout
+    if need_bias_grad and db is None:
+        db = torch.empty((Cout,), dtype=torch.float32, device=dz.device)
+    # bias gradient fused into the wgrad launch (ones-operand MMA) when a TMEM accumulator is spare
+    fuse_db = need_bias_grad and (Cout + 15) // 16 * 16 <= 128
+    if fuse_db:
+        d.db = db.data_ptr()
     L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad")
-    if need_bias_grad:
-        if db is None:
-            db = torch.empty((Cout,), dtype=torch.float32, device=dz.device)
+    if need_bias_grad and not fuse_db:
         L.check(L.load().of_colsum(L.ptr(dz), L.ptr(db), N * Ho * Wo, Cout, Cout, L.dtype_code(dz), L.stream_ptr()),
                 "of_colsum")
     return dw, db
@@ -206,11 +210,10 @@ def conv1_wgrad_tc(xp, H, W, dz, dw, db):
     d.dw = dwv.data_ptr()
     _stem_view(d, xp, H, W)
     d.Cin, d.Cout = 64, Cout
+    if db is not None:
+        d.db = db.data_ptr()                               # bias gradient fused into the same launch
     L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad(stem)")
     L.check(L.load().of_conv1_unpack_wgrad(L.ptr(dwv), L.ptr(dw), Cout, L.stream_ptr()), "of_conv1_unpack_wgrad")
-    if db is not None:
-        npix = dz.shape[0] * dz.shape[1] * dz.shape[2]
-        L.check(L.load().of_colsum(L.ptr(dz), L.ptr(db), npix, Cout, Cout, L.dtype_code(dz), L.stream_ptr()), "of_colsum")
     return dw, db
 
 
@@ -266,7 +269,7 @@ class Bf16Backend:
             outs = []
             for s in x.sources:
                 n_out = s.t.shape[-1]                    # padded channels of the cv/flow buffer get zeros
-                dt = torch.float32 if s.ci0 == 0 else torch.bfloat16
+                dt = torch.bfloat16                       # features segment too: summed in fp32 inside concat_bwd
                 outs.append(conv2d_dgrad_tc(dz, w, in_hw, 1, seg=(s.ci0, s.valid), out_dtype=dt, out_channels=n_out))
             return tuple(outs)
         return conv2d_dgrad_tc(dz, w, in_hw, layer.stride, out_dtype=torch.bfloat16, mask=mask,
@@ -287,18 +290,19 @@ class Bf16Backend:
         fm.cvflow = cvflow
         return MultiSource([Source(f1, Cc, 0), Source(cvflow, valid, Cc)])
 
-    def concat_bwd(self, fm, d):
-        d_f1, d_cvflow = d                               # fp32 (B,h,w,C), bf16 (B,h,w,64)
-        B, h, w, Cc = d_f1.shape
+    def concat_bwd(self, fm, d, out_f1=None, out_f2=None):
+        """Gradient split of the concat (model.py:100-102) + cost-volume backward, bf16 end to end:
+        d_f1 = conv segment + dcv/df1 written straight into ``out_f1`` (the encoder's incoming
+        gradient); d_f2w goes to ``out_f2`` when there is no warp in between (coarsest level)."""
+        d_f1_conv, d_cvflow = d                          # bf16 (B,h,w,C), bf16 (B,h,w,64)
+        B, h, w, Cc = d_f1_conv.shape
         net = self.net
-        d_f1_b = torch.empty_like(d_f1)
-        d_f2w = torch.empty_like(d_f1)
-        L.check(L.load().of_cost_volume_bwd(L.ptr(fm.f1), L.ptr(fm.f2w), L.ptr(d_cvflow), L.ptr(d_f1_b), L.ptr(d_f2w),
-                                            B, h, w, Cc, net.max_disp, 64, L.OF_BF16, L.stream_ptr()),
-                "of_cost_volume_bwd")
-        n = d_f1.numel()
-        L.check(L.load().of_copy_channels(L.ptr(d_f1_b), 4, L.ptr(d_f1), 4, 4, n // 4, L.OF_F32, L.OF_F32, 1,
-                                          L.stream_ptr()), "of_copy_channels(acc)")
+        d_f1 = out_f1 if out_f1 is not None else torch.empty_like(d_f1_conv)
+        d_f2w = out_f2 if (out_f2 is not None and not fm.has_prev) else torch.empty_like(d_f1_conv)
+        assert d_f1.is_contiguous() and d_f2w.is_contiguous() and d_f1.dtype == torch.bfloat16
+        L.check(L.load().of_cost_volume_bwd_bf16(L.ptr(fm.f1), L.ptr(fm.f2w), L.ptr(d_cvflow), L.ptr(d_f1), L.ptr(d_f2w),
+                                                 L.ptr(d_f1_conv), B, h, w, Cc, net.max_disp, 64, L.stream_ptr()),
+                "of_cost_volume_bwd_bf16")
         d_flow_up = None
         if fm.has_prev:
             d_flow_up = torch.empty((B, h, w, 2), dtype=torch.float32, device=d_f1.device)

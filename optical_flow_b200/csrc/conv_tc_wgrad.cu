@@ -10,12 +10,16 @@
 // decoder concat), all Cout columns, a group of taps (one TMEM accumulator per tap: the dy
 // tile is loaded once per K step and reused by every tap) and a slice of the pixel range
 // (split-K).  Partial results are reduced into dW with red.global.add.f32.
+// Bias gradient (db[co] = sum_pix dy[pix][co]) rides along: the CTAs of job 0 issue one more MMA group
+// per K step whose A operand is a constant all-ones tile, into a spare TMEM accumulator - the dy tile
+// is already in shared memory, so the separate column-sum pass over dy (1.25 ms / step) disappears.
 #include "common.cuh"
 #include "tc_common.cuh"
 
 #define WG_THREADS 192
 #define WG_CHUNK_BYTES 8192   // 64 pixels x 64 bf16
 #define WG_MAX_TAPS 9
+#define WG_ONES_BYTES 4096   // all-ones A operand: 2 chunks x 16 K-rows x 128 B (reused for every K slice)
 
 int of_tc_make_act_map(CUtensorMap* m, const void* base, int c_used, long long stride_elems, int N, int H, int W,
                        int box_w, int box_h, int estride);
@@ -39,6 +43,7 @@ struct WgradParams {
   int Cin, Cout;
   int stages, stage_bytes, tmem_cols;
   float* dw;
+  float* db;                      // nullable: fused bias gradient (job 0 only)
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -46,7 +51,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
                      const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ WgradParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + (size_t)P.stages * P.stage_bytes);
+  uint8_t* ones = tiles + (size_t)P.stages * P.stage_bytes;            // 1024-aligned (stage_bytes is a multiple of 8 KB)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ones + WG_ONES_BYTES);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* acc_full = empty_bar + 8;
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
@@ -58,6 +64,13 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     tc::fence_barrier_init();
   }
   if (warp == 4 && lane == 0) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
+  const bool do_bias = P.db != nullptr && blockIdx.y == 0;
+  if (do_bias) {
+    // bf16 1.0 = 0x3f80; all-ones is invariant under the 128-byte swizzle
+    for (int i = threadIdx.x; i < WG_ONES_BYTES / 16; i += WG_THREADS)
+      reinterpret_cast<uint4*>(ones)[i] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+    tc::fence_proxy_async();                               // generic-proxy writes -> visible to the MMA's reads
+  }
   if (warp == 5) { tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols); tc::tmem_relinquish(); }
   tc::fence_before_sync();
   __syncthreads();
@@ -117,6 +130,14 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
           }
         }
+        if (do_bias) {
+          const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
+            tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma), odesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
+          }
+        }
         tc::mma_commit(&empty_bar[stage]);
         if (++stage == P.stages) { stage = 0; phase ^= 1; }
       }
@@ -157,6 +178,21 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
           }
         }
       }
+      if (do_bias && warp == 0) {
+        // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
+        uint32_t taddr = tmem_base + (uint32_t)(ntaps * P.n_mma);
+        for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
+          __syncwarp();
+          uint32_t rr[16];
+          tc::tmem_ld16(taddr + (uint32_t)c0, rr);
+          tc::tmem_ld_wait();
+          if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < P.n_valid) red_add(P.db + c0 + j, __uint_as_float(rr[j]));
+          }
+        }
+      }
     }
   }
   tc::fence_before_sync();
@@ -174,6 +210,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const int taps = c->KH * c->KW;
   OF_CUDA(cudaMemsetAsync(c->dw, 0, (size_t)taps * c->Cin * c->Cout * sizeof(float), st));
+  if (c->db) OF_CUDA(cudaMemsetAsync(c->db, 0, (size_t)c->Cout * sizeof(float), st));
 
   WgradParams P;
   memset(&P, 0, sizeof(P));
@@ -197,7 +234,11 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.n_chunks = (P.n_mma + 63) / 64;
   P.Cin = c->Cin; P.Cout = c->Cout;
   P.dw = c->dw;
-  int tpp = 512 / P.n_mma;              // taps per pass: one TMEM accumulator (n_mma columns) per tap
+  P.db = c->db;
+  OF_REQUIRE(c->db == nullptr || 2 * P.n_mma <= 512, OF_ERR_UNSUPPORTED,
+             "fused bias gradient needs a spare TMEM accumulator (Cout <= 256 -> n_mma <= 256)");
+  // taps per pass: one TMEM accumulator (n_mma columns) per tap, one more for the fused bias gradient
+  int tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
   if (tpp > taps) tpp = taps;
   // keep >= 2 pipeline stages inside 200 KB of shared memory
   while (tpp > 1 && 2 * (tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES) > 200 * 1024) --tpp;
@@ -254,9 +295,9 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
-  int cols = tpp * P.n_mma;
+  int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
-  size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + 17 * sizeof(uint64_t) + 16;
+  size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
   dim3 grid(splits, jobs);
   conv_tc_wgrad_kernel<<<grid, WG_THREADS, smem, st>>>(tmX[0], tmX[1], tmDY, P);
   if (int r = of_launch_check("conv_tc_wgrad_kernel")) return r;

@@ -137,10 +137,13 @@ cv7_fwd_kernel(const T* __restrict__ f1, const T* __restrict__ f2, T* __restrict
 #define CVB_WORDS 32
 // FROM_F2 = true : d_f1[p,c] = sum_ij g[p, ij]              * f2[p + (i-3, j-3), c]
 // FROM_F2 = false: d_f2[q,c] = sum_ij g[q - (i-3, j-3), ij] * f1[q - (i-3, j-3), c]
-template <typename T, bool FROM_F2>
+// OUT_BF16: the result (+ the optional `add` operand, a gradient that reaches the same tensor by another
+// path) is stored as bf16 - lets the caller write the encoder's incoming gradient directly.
+template <typename T, bool FROM_F2, bool OUT_BF16 = false>
 __global__ void __launch_bounds__(CVB_THREADS, 1)
-cv7_bwd_kernel(const T* __restrict__ feat, const T* __restrict__ d_cv, float* __restrict__ d_out, int B, int H,
-               int W, int C, int cv_stride) {
+cv7_bwd_kernel(const T* __restrict__ feat, const T* __restrict__ d_cv, void* __restrict__ d_out_v, int B, int H,
+               int W, int C, int cv_stride, const __nv_bfloat16* __restrict__ add = nullptr) {
+  float* d_out = reinterpret_cast<float*>(d_out_v);
   using WT = WordTraits<T>;
   constexpr int PW = WT::PER_WORD;
   extern __shared__ uint32_t smw[];
@@ -221,9 +224,21 @@ cv7_bwd_kernel(const T* __restrict__ feat, const T* __restrict__ d_cv, float* __
           for (int k = 0; k < 4; ++k) {
             int xx = x0 + qx * 4 + k;
             if (xx < W) {
-              float* o = d_out + (((size_t)b * H + yy) * W + xx) * C + (size_t)wi * PW;
-              if (PW == 2) *reinterpret_cast<float2*>(o) = make_float2(alo[k], ahi[k]);
-              else *o = alo[k];
+              const size_t e = (((size_t)b * H + yy) * W + xx) * C + (size_t)wi * PW;
+              if (OUT_BF16 && PW == 2) {
+                float lo = alo[k], hi = ahi[k];
+                if (add != nullptr) {
+                  uint32_t a = __ldg(reinterpret_cast<const uint32_t*>(add + e));
+                  lo += __uint_as_float(a << 16);
+                  hi += __uint_as_float(a & 0xffff0000u);
+                }
+                __nv_bfloat162 pk = __floats2bfloat162_rn(lo, hi);
+                *reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<__nv_bfloat16*>(d_out_v) + e) = pk;
+              } else {
+                float* o = d_out + e;
+                if (PW == 2) *reinterpret_cast<float2*>(o) = make_float2(alo[k], ahi[k]);
+                else *o = alo[k];
+              }
             }
           }
         }
@@ -266,6 +281,27 @@ int cv7_bwd(const void* f1, const void* f2, const void* d_cv, float* d_f1, float
   if (int r = of_launch_check("cv7_bwd_kernel<d_f1>")) return r;
   cv7_bwd_kernel<T, false><<<grid, CVB_THREADS, smem, st>>>((const T*)f1, (const T*)d_cv, d_f2, B, H, W, C, cv_stride);
   return of_launch_check("cv7_bwd_kernel<d_f2>");
+}
+
+// bf16 in, bf16 out: d_f1 = cv-gradient (+ d_f1_add), d_f2 = cv-gradient
+int cv7_bwd_bf16(const void* f1, const void* f2, const void* d_cv, void* d_f1, void* d_f2, const void* d_f1_add, int B,
+                 int H, int W, int C, int cv_stride, cudaStream_t st) {
+  typedef __nv_bfloat16 T;
+  size_t smem = (size_t)CV_HR * CV_HC * CVB_WORDS * sizeof(uint32_t) + (size_t)CV_D * CV_TR * CV_TC * 8 * sizeof(float);
+  static bool set = false;
+  if (!set) {
+    OF_CUDA(cudaFuncSetAttribute(cv7_bwd_kernel<T, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    OF_CUDA(cudaFuncSetAttribute(cv7_bwd_kernel<T, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set = true;
+  }
+  long long ntiles = (long long)B * ((W + CV_TC - 1) / CV_TC) * ((H + CV_TR - 1) / CV_TR);
+  int grid = (int)(ntiles < OF_NUM_SMS ? ntiles : OF_NUM_SMS);
+  cv7_bwd_kernel<T, true, true><<<grid, CVB_THREADS, smem, st>>>((const T*)f2, (const T*)d_cv, d_f1, B, H, W, C, cv_stride,
+                                                                 (const T*)d_f1_add);
+  if (int r = of_launch_check("cv7_bwd_kernel<d_f1,bf16>")) return r;
+  cv7_bwd_kernel<T, false, true><<<grid, CVB_THREADS, smem, st>>>((const T*)f1, (const T*)d_cv, d_f2, B, H, W, C, cv_stride,
+                                                                  nullptr);
+  return of_launch_check("cv7_bwd_kernel<d_f2,bf16>");
 }
 
 template int cv7_fwd<float>(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);

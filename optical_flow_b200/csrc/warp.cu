@@ -152,10 +152,11 @@ __device__ __forceinline__ float combine_peers(unsigned peers, int rank, int lan
   return val;
 }
 
-template <typename T, int VEC, int TPP, int SRC>
+// G = dtype of the incoming gradient d_out (float, or bf16 on the tensor-core conv path)
+template <typename T, int VEC, int TPP, int SRC, typename G = float>
 __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ in,
                                                          const float* __restrict__ coords,
-                                                         const float* __restrict__ d_out,
+                                                         const G* __restrict__ d_out,
                                                          float* __restrict__ d_in,
                                                          float* __restrict__ d_coords,
                                                          int B, int H, int W, int C) {
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
           any_dup = __any_sync(0xffffffffu, (__popc(pe[0]) | __popc(pe[1]) | __popc(pe[2]) | __popc(pe[3])) > 1);
         }
         for (int ch = 0; ch < C; ++ch) {
-          float g = valid ? __ldg(d_out + pix * C + ch) : 0.f;
+          float g = valid ? ld_f<G>(d_out + pix * C + ch) : 0.f;
           float v00 = ld_f<T>(in + o00 + ch), v01 = ld_f<T>(in + o01 + ch);
           float v10 = ld_f<T>(in + o10 + ch), v11 = ld_f<T>(in + o11 + ch);
           d0 += g * (t.ay * (v10 - v00) + t.by * (v11 - v01));
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
           if (!valid) continue;
           int ch = v * VEC;
           if (VEC == 4) {
-            float4 g = __ldg(reinterpret_cast<const float4*>(d_out + pix * C + ch));
+            float4 g = ld4<G>(d_out + pix * C + ch);
             float4 v00 = ld4<T>(in + o00 + ch), v01 = ld4<T>(in + o01 + ch);
             float4 v10 = ld4<T>(in + o10 + ch), v11 = ld4<T>(in + o11 + ch);
             d0 += g.x * (t.ay * (v10.x - v00.x) + t.by * (v11.x - v01.x)) +
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
               red_add_v4(d_in + o11 + ch, make_float4(w11 * g.x, w11 * g.y, w11 * g.z, w11 * g.w));
             }
           } else {
-            float g = __ldg(d_out + pix * C + ch);
+            float g = ld_f<G>(d_out + pix * C + ch);
             float v00 = ld_f<T>(in + o00 + ch), v01 = ld_f<T>(in + o01 + ch);
             float v10 = ld_f<T>(in + o10 + ch), v11 = ld_f<T>(in + o11 + ch);
             d0 += g * (t.ay * (v10 - v00) + t.by * (v11 - v01));
@@ -280,8 +281,8 @@ static int launch_fwd(const void* in, const float* coords, void* out, int32_t* i
   return of_launch_check("sample_fwd_kernel");
 }
 
-template <typename T, int SRC>
-static int launch_bwd(const void* in, const float* coords, const float* d_out, float* d_in, float* d_coords,
+template <typename T, int SRC, typename G = float>
+static int launch_bwd(const void* in, const float* coords, const void* d_out, float* d_in, float* d_coords,
                       int B, int H, int W, int C, cudaStream_t st) {
   long long ntiles = (long long)B * ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
   int grid = grid_for(ntiles);
@@ -290,8 +291,8 @@ static int launch_bwd(const void* in, const float* coords, const float* d_out, f
     if (e != cudaSuccess) { of_set_error("memset d_in: %s", cudaGetErrorString(e)); return (int)e; }
   }
 #define L(VEC, TPP)                                                                          \
-  sample_bwd_kernel<T, VEC, TPP, SRC><<<grid, 256, 0, st>>>((const T*)in, coords, d_out, d_in, \
-                                                            d_coords, B, H, W, C)
+  sample_bwd_kernel<T, VEC, TPP, SRC, G><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
+                                                               d_coords, B, H, W, C)
   if (C % 4 == 0) {
     int cv = C / 4;
     if (cv >= 32) L(4, 32);
@@ -327,13 +328,17 @@ static int fwd_dispatch(const void* in, const float* coords, void* out, int32_t*
 }
 
 template <int SRC>
-static int bwd_dispatch(const void* in, const float* coords, const float* d_out, float* d_in, float* d_coords,
-                        int B, int H, int W, int C, int dtype, void* stream) {
+static int bwd_dispatch(const void* in, const float* coords, const void* d_out, float* d_in, float* d_coords,
+                        int B, int H, int W, int C, int dtype, void* stream, int g_dtype = OF_F32) {
   OF_REQUIRE(in && coords && d_out, OF_ERR_ARG, "null pointer argument");
   OF_REQUIRE(d_in || d_coords, OF_ERR_ARG, "both gradient outputs are null");
   OF_REQUIRE(of_valid_dtype(dtype), OF_ERR_ARG, "bad dtype %d", dtype);
   if (int r = check_dims(B, H, W, C)) return r;
   cudaStream_t st = (cudaStream_t)stream;
+  if (g_dtype == OF_BF16) {
+    OF_REQUIRE(dtype == OF_BF16, OF_ERR_UNSUPPORTED, "a bf16 incoming gradient needs bf16 features");
+    return launch_bwd<__nv_bfloat16, SRC, __nv_bfloat16>(in, coords, d_out, d_in, d_coords, B, H, W, C, st);
+  }
   if (dtype == OF_F32) return launch_bwd<float, SRC>(in, coords, d_out, d_in, d_coords, B, H, W, C, st);
   return launch_bwd<__nv_bfloat16, SRC>(in, coords, d_out, d_in, d_coords, B, H, W, C, st);
 }
@@ -363,6 +368,15 @@ int of_warp_features_bwd(const void* feats, const float* flow, const float* d_ou
   if (mode == OF_WARP_REF_IJ)
     return bwd_dispatch<SRC_REF_IJ>(feats, flow, d_out, d_feats, d_flow, B, H, W, C, dtype, stream);
   return bwd_dispatch<SRC_XY>(feats, flow, d_out, d_feats, d_flow, B, H, W, C, dtype, stream);
+}
+
+int of_warp_features_bwd_g(const void* feats, const float* flow, const void* d_out, int d_out_dtype, float* d_feats,
+                           float* d_flow, int B, int H, int W, int C, int mode, int dtype, void* stream) {
+  OF_REQUIRE(mode == OF_WARP_REF_IJ || mode == OF_WARP_XY, OF_ERR_ARG, "bad warp mode %d", mode);
+  OF_REQUIRE(of_valid_dtype(d_out_dtype), OF_ERR_ARG, "bad d_out dtype %d", d_out_dtype);
+  if (mode == OF_WARP_REF_IJ)
+    return bwd_dispatch<SRC_REF_IJ>(feats, flow, d_out, d_feats, d_flow, B, H, W, C, dtype, stream, d_out_dtype);
+  return bwd_dispatch<SRC_XY>(feats, flow, d_out, d_feats, d_flow, B, H, W, C, dtype, stream, d_out_dtype);
 }
 
 int of_image_warp_fwd(const float* im, const float* flow, float* out, int32_t* idx, int B, int H, int W,

@@ -64,12 +64,13 @@ def warp_features_fwd(flow, feats, mode="ref_ij", return_indices=False, out=None
 
 def warp_features_bwd(flow, feats, d_out, mode="ref_ij", need_feats_grad=True, need_flow_grad=True):
     B, H, W, Cc = feats.shape
-    assert d_out.dtype == torch.float32 and tuple(d_out.shape) == tuple(feats.shape)
+    assert tuple(d_out.shape) == tuple(feats.shape)
+    assert d_out.dtype == torch.float32 or (d_out.dtype == torch.bfloat16 and feats.dtype == torch.bfloat16)
     d_feats = torch.empty((B, H, W, Cc), dtype=torch.float32, device=feats.device) if need_feats_grad else None
     d_flow = torch.empty((B, H, W, 2), dtype=torch.float32, device=feats.device) if need_flow_grad else None
-    L.check(L.load().of_warp_features_bwd(L.ptr(feats), L.ptr(flow), L.ptr(d_out), L.ptr(d_feats), L.ptr(d_flow),
-                                          B, H, W, Cc, _mode_code(mode), L.dtype_code(feats), L.stream_ptr()),
-            "of_warp_features_bwd")
+    L.check(L.load().of_warp_features_bwd_g(L.ptr(feats), L.ptr(flow), L.ptr(d_out), L.dtype_code(d_out), L.ptr(d_feats),
+                                            L.ptr(d_flow), B, H, W, Cc, _mode_code(mode), L.dtype_code(feats),
+                                            L.stream_ptr()), "of_warp_features_bwd_g")
     return d_feats, d_flow
 
 

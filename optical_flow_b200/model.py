@@ -268,14 +268,15 @@ class FlowModule:
             x = conv.forward(x)
         return x                                                  # (B, h, w, 2) float32
 
-    def backward(self, d_flow):
-        """d_flow: f32 gradient w.r.t. this level's flow.  Returns (d_f1, d_f2, d_prev_flow),
-        d_f1/d_f2 float32."""
+    def backward(self, d_flow, out_f1=None, out_f2=None):
+        """d_flow: f32 gradient w.r.t. this level's flow.  Returns (d_f1, d_f2, d_prev_flow).
+        ``out_f1`` / ``out_f2`` (optional, activation dtype): where the caller wants the feature
+        gradients; a back-end that can write them in place returns those very tensors."""
         net = self.net
         d = d_flow                      # the flow head has no activation: its dz is the fp32 d_flow
         for conv in reversed(self.convs):
             d = conv.backward(d)
-        d_f1, d_f2w, d_flow_up = net.backend_concat_bwd(self, d)
+        d_f1, d_f2w, d_flow_up = net.backend_concat_bwd(self, d, out_f1, out_f2)
         if self.has_prev:
             d_f2, d_flow_up_b = F.warp_features_bwd(self.flow_up, self.f2, d_f2w, mode=net.warp_mode)
             _accumulate(d_flow_up, d_flow_up_b)
@@ -359,9 +360,9 @@ class FlowNet:
             _copy_channels(flow_up, 0, x, C + fm.ncv, 2)
         return x
 
-    def backend_concat_bwd(self, fm, dx):
+    def backend_concat_bwd(self, fm, dx, out_f1=None, out_f2=None):
         if hasattr(self.backend, "concat_bwd"):
-            return self.backend.concat_bwd(fm, dx)
+            return self.backend.concat_bwd(fm, dx, out_f1, out_f2)
         B, h, w, _ = dx.shape
         C = fm.C
         d_f1 = torch.empty((B, h, w, C), dtype=torch.float32, device=dx.device)
@@ -420,11 +421,13 @@ class FlowNet:
             if carry is not None:
                 _accumulate(carry, d)      # carry is our own buffer: d(loss)/d(flow) + d(finer level)/d(flow)
                 d = carry
-            d_f1, d_f2, carry = self.flow_modules[lvl].backward(d)
             e = self.enc_outs[3 - lvl]
             de = torch.empty(e.shape, dtype=self.backend.act_dtype, device=e.device)
-            _copy_channels(d_f1, 0, de[:B], 0, d_f1.shape[-1])
-            _copy_channels(d_f2, 0, de[B:], 0, d_f2.shape[-1])
+            d_f1, d_f2, carry = self.flow_modules[lvl].backward(d, de[:B], de[B:])
+            if d_f1.data_ptr() != de.data_ptr():              # back-end did not write in place
+                _copy_channels(d_f1, 0, de[:B], 0, d_f1.shape[-1])
+            if d_f2.data_ptr() != de[B:].data_ptr():
+                _copy_channels(d_f2, 0, de[B:], 0, d_f2.shape[-1])
             d_enc[3 - lvl] = de
         self.encoder.backward(d_enc)
 

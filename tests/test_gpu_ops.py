@@ -230,6 +230,53 @@ def test_cost_volume_fwd_bwd(cuda, shape):
     assert_close_maxrel(d2, e2, what="d_f2")
 
 
+@pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128)])
+def test_cost_volume_bwd_bf16_fused(cuda, shape):
+    """of_cost_volume_bwd_bf16 (bf16 tensors, d_f1 += the conv-path gradient) vs the oracle on the same
+    bf16-rounded inputs; the only extra error is the final bf16 rounding (2^-8 relative to the value)."""
+    from optical_flow_b200 import _lib as L
+    B, H, W, C = shape
+    r = rng(12)
+    bf = lambda a: torch.tensor(a).bfloat16()
+    f1, f2 = bf(r.standard_normal(shape).astype(np.float32)), bf(r.standard_normal(shape).astype(np.float32))
+    g = np.zeros((B, H, W, 64), np.float32)
+    g[..., :49] = r.standard_normal((B, H, W, 49))
+    g = bf(g)
+    add = bf(r.standard_normal(shape).astype(np.float32) * 3)
+    e1, e2 = O.create_cost_volume_bwd(f1.float().numpy(), f2.float().numpy(), 3, g.float().numpy()[..., :49])
+    e1 = e1 + add.float().numpy()
+    d1 = torch.empty(shape, dtype=torch.bfloat16, device=cuda)
+    d2 = torch.empty(shape, dtype=torch.bfloat16, device=cuda)
+    f1d, f2d, gd, addd = f1.to(cuda), f2.to(cuda), g.to(cuda), add.to(cuda)
+    L.check(L.load().of_cost_volume_bwd_bf16(L.ptr(f1d), L.ptr(f2d), L.ptr(gd), L.ptr(d1), L.ptr(d2), L.ptr(addd),
+                                             B, H, W, C, 3, 64, L.stream_ptr()), "of_cost_volume_bwd_bf16")
+    for got, exp in ((d1, e1), (d2, e2)):
+        err = np.abs(got.float().cpu().numpy() - exp)
+        assert (err <= 2.0 ** -8 * np.abs(exp) + 1e-5 * np.abs(exp).max()).all(), err.max()
+    # without the add operand
+    L.check(L.load().of_cost_volume_bwd_bf16(L.ptr(f1d), L.ptr(f2d), L.ptr(gd), L.ptr(d1), L.ptr(d2), None,
+                                             B, H, W, C, 3, 64, L.stream_ptr()), "of_cost_volume_bwd_bf16")
+    exp = e1 - add.float().numpy()
+    err = np.abs(d1.float().cpu().numpy() - exp)
+    assert (err <= 2.0 ** -8 * np.abs(exp) + 1e-5 * np.abs(e1).max()).all(), err.max()
+
+
+def test_warp_features_bwd_bf16_incoming_gradient(cuda):
+    """of_warp_features_bwd_g with a bf16 d_out == the fp32-d_out call on the same (bf16-representable) values."""
+    from optical_flow_b200 import functional as F
+    r = rng(13)
+    shape = (2, 12, 20, 64)
+    feats = torch.tensor(r.standard_normal(shape).astype(np.float32)).bfloat16().to(cuda)
+    flow = torch.tensor((r.standard_normal((2, 12, 20, 2)) * 3.0).astype(np.float32)).to(cuda)
+    g16 = torch.tensor(r.standard_normal(shape).astype(np.float32)).bfloat16().to(cuda)
+    for mode in ("ref_ij", "xy"):
+        a1, b1 = F.warp_features_bwd(flow, feats, g16, mode=mode)
+        a2, b2 = F.warp_features_bwd(flow, feats, g16.float(), mode=mode)
+        # scatter order differs run to run (atomics): compare with an fp32 summation bound
+        assert (a1 - a2).abs().max().item() <= 1e-5 * a2.abs().max().item()
+        assert torch.equal(b1, b2)
+
+
 def test_cost_volume_shape_assert(cuda):
     from optical_flow_b200.model import create_cost_volume
     a = torch.zeros((1, 4, 4, 8), device=cuda)
