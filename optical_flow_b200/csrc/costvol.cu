@@ -105,6 +105,10 @@ int cv7_bwd(const void* f1, const void* f2, const void* d_cv, float* d_f1, float
             int cv_stride, cudaStream_t st);
 int cv7_bwd_bf16(const void* f1, const void* f2, const void* d_cv, void* d_f1, void* d_f2, const void* d_f1_add, int B,
                  int H, int W, int C, int cv_stride, cudaStream_t st);
+// tensor-core path (costvol_tc.cu): 1 = handled, 0 = not applicable
+int cvtc_fwd_try(const void* f1, const void* f2, void* cv, int B, int H, int W, int C, int cv_stride, cudaStream_t st);
+int cvtc_bwd_try(const void* f1, const void* f2, const void* d_cv, void* d_f1, void* d_f2, const void* d_f1_add, int B,
+                 int H, int W, int C, int cv_stride, cudaStream_t st);
 template <typename T> static bool cv7_ok(int C, int D) { return D == 7 && (C * (int)sizeof(T)) % 16 == 0; }
 
 template <typename T>
@@ -164,6 +168,8 @@ int of_cost_volume_fwd(const void* f1, const void* f2, void* cv, int B, int H, i
   OF_REQUIRE(f1 && f2 && cv, OF_ERR_ARG, "null pointer argument");
   if (int r = cv_check(B, H, W, C, max_disp, cv_stride, dtype)) return r;
   if (dtype == OF_F32) return cv_fwd<float>(f1, f2, cv, B, H, W, C, max_disp, cv_stride, (cudaStream_t)stream);
+  if (max_disp == 3)
+    if (int r = cvtc_fwd_try(f1, f2, cv, B, H, W, C, cv_stride, (cudaStream_t)stream)) return r == 1 ? 0 : r;
   return cv_fwd<__nv_bfloat16>(f1, f2, cv, B, H, W, C, max_disp, cv_stride, (cudaStream_t)stream);
 }
 
@@ -183,6 +189,8 @@ int of_cost_volume_bwd_bf16(const void* f1, const void* f2, const void* d_cv, vo
   if (int r = cv_check(B, H, W, C, max_disp, cv_stride, OF_BF16)) return r;
   OF_REQUIRE(cv7_ok<__nv_bfloat16>(C, 2 * max_disp + 1), OF_ERR_UNSUPPORTED,
              "bf16-output cost-volume backward needs max_disp == 3 and C %% 8 == 0 (got %d, %d)", max_disp, C);
+  if (int r = cvtc_bwd_try(f1, f2, d_cv, d_f1, d_f2, d_f1_add, B, H, W, C, cv_stride, (cudaStream_t)stream))
+    return r == 1 ? 0 : r;
   return cv7_bwd_bf16(f1, f2, d_cv, d_f1, d_f2, d_f1_add, B, H, W, C, cv_stride, (cudaStream_t)stream);
 }
 

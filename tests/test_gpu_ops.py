@@ -230,11 +230,37 @@ def test_cost_volume_fwd_bwd(cuda, shape):
     assert_close_maxrel(d2, e2, what="d_f2")
 
 
-@pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128)])
-def test_cost_volume_bwd_bf16_fused(cuda, shape):
+@pytest.mark.parametrize("tc", [True, False])
+@pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128), (1, 6, 200, 64), (3, 5, 300, 128)])
+def test_cost_volume_fwd_bf16(cuda, shape, tc, monkeypatch):
+    """bf16 cost volume written into the 64-channel decoder input buffer: the tcgen05 banded-GEMM kernel
+    (costvol_tc.cu) and the SIMT kernel (costvol7.cu, OF_CV_NO_TC=1) against the oracle on bf16-rounded inputs."""
+    from optical_flow_b200 import _lib as L
+    if not tc:
+        monkeypatch.setenv("OF_CV_NO_TC", "1")
+    B, H, W, C = shape
+    r = rng(14)
+    bf = lambda a: torch.tensor(a).bfloat16()
+    f1, f2 = bf(r.standard_normal(shape).astype(np.float32)), bf(r.standard_normal(shape).astype(np.float32))
+    exp = O.create_cost_volume(f1.float().numpy(), f2.float().numpy(), 3)
+    cv = torch.full((B, H, W, 64), 7.0, dtype=torch.bfloat16, device=cuda)
+    f1d, f2d = f1.to(cuda), f2.to(cuda)
+    L.check(L.load().of_cost_volume_fwd(L.ptr(f1d), L.ptr(f2d), L.ptr(cv), B, H, W, C, 3, 64, L.OF_BF16, L.stream_ptr()),
+            "of_cost_volume_fwd")
+    got = cv.float().cpu().numpy()
+    assert (got[..., 49:] == 7.0).all()                      # channels 49..63 belong to the caller (flow, padding)
+    err = np.abs(got[..., :49] - exp)
+    assert (err <= 2.0 ** -8 * np.abs(exp) + 1e-5 * np.abs(exp).max()).all(), err.max()
+
+
+@pytest.mark.parametrize("tc", [True, False])
+@pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128), (1, 6, 200, 64), (3, 5, 300, 128)])
+def test_cost_volume_bwd_bf16_fused(cuda, shape, tc, monkeypatch):
     """of_cost_volume_bwd_bf16 (bf16 tensors, d_f1 += the conv-path gradient) vs the oracle on the same
     bf16-rounded inputs; the only extra error is the final bf16 rounding (2^-8 relative to the value)."""
     from optical_flow_b200 import _lib as L
+    if not tc:
+        monkeypatch.setenv("OF_CV_NO_TC", "1")
     B, H, W, C = shape
     r = rng(12)
     bf = lambda a: torch.tensor(a).bfloat16()
