@@ -211,6 +211,12 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream);
 int of_pack_image_pair8(const float* imgs, void* out, int B, int H, int W, void* stream);
 int of_conv1_pack_weights(const float* w_hwio, void* packed, int Cout, void* stream);
 int of_conv1_unpack_wgrad(const float* dw_view, float* dw_hwio, int Cout, void* stream);
+/* Backward of the flow head, model.py:114 Conv2D(2, 3, padding='same'), in one pass: x (N,H,W,Cin<=32) dtype =
+ * the head's input (= the previous conv's post-activation output), dy (N,H,W,2) f32, w (3,3,Cin,2) f32.
+ * dw (3,3,Cin,2) f32 and db (2) f32 (nullable) are overwritten; dz (nullable, dtype, (N,H,W,Cin)) =
+ * dgrad * act'(x), i.e. already the previous layer's pre-activation gradient (act = its activation). */
+int of_flow_head_bwd(const void* x, const float* dy, const float* w, float* dw, float* db, void* dz,
+                     int N, int H, int W, int Cin, int act, int dtype, void* stream);
 /* out (N,H,W,C) = dy (N,Ho,Wo,C) with zeros inserted (out[2i,2j] = dy[i,j]): a stride-2 conv's
  * dgrad is the stride-1 dgrad of this tensor. */
 int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,

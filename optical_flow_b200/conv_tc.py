@@ -255,6 +255,21 @@ class Bf16Backend:
             assert not isinstance(x, MultiSource)
             F.conv2d_wgrad(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
 
+    def head_bwd(self, layer, dy):
+        """model.py:114 flow head backward in one launch (csrc/head.cu): fills the layer's dw / db and
+        returns the previous conv's dz (its activation derivative applied from x = its output)."""
+        x = layer.x
+        N, H, W, Cin = x.shape
+        chain = layer.prev_chain
+        act = chain.act if chain is not None else L.OF_ACT_NONE
+        dz = torch.empty_like(x)
+        L.check(L.load().of_flow_head_bwd(L.ptr(x), L.ptr(dy), L.ptr(layer.w_eff), L.ptr(layer._g("/kernel")),
+                                          L.ptr(layer._g("/bias")), L.ptr(dz), N, H, W, Cin, act, L.dtype_code(x),
+                                          L.stream_ptr()), "of_flow_head_bwd")
+        if chain is not None and act != L.OF_ACT_NONE:
+            chain.incoming_is_dz = True
+        return dz
+
     def dgrad(self, layer, dz, w, in_hw, chain=None):
         """Returns dx; with `chain` (the ConvLayer producing this layer's input, sole consumer)
         the epilogue multiplies by act'(chain.y) and the result is already chain's dz."""

@@ -380,7 +380,12 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   const bool add_coal_ok = c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 8) == 0 &&
                                                  ((uintptr_t)c->add & 15) == 0 && (c->n_valid % 16) == 0);
   P.coal = c->out_dtype == OF_BF16 && (c->out_stride % 8) == 0 && ((uintptr_t)c->out & 15) == 0 && c->n_valid >= 8 &&
-           (c->n_valid % 8) == 0 && mask_coal_ok && add_coal_ok && getenv("OF_T3_COAL") != nullptr;
+           (c->n_valid % 8) == 0 && mask_coal_ok && add_coal_ok;
+  {
+    const char* e = getenv("OF_T3_COAL");                 // 1 = always, 2 = only with a mask operand (dgrad)
+    const int mode = e ? atoi(e) : 0;
+    P.coal = P.coal && (mode == 1 || (mode == 2 && c->mask != nullptr));
+  }
   if (const char* e = getenv("OF_T3_DBG")) P.dbg = atoi(e);
   // ring depths: TMA latency (~2k cycles loaded) must be covered by the MMAs of the slots in flight.
   // One slab feeds 24 MMAs (~1.6k cycles at Cout = 128), one weight tile 8 (~0.5k): 3 slabs + >= 4 tiles.

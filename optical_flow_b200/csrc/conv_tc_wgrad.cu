@@ -44,6 +44,9 @@ struct WgradParams {
   int stages, stage_bytes, tmem_cols;
   float* dw;
   float* db;                      // nullable: fused bias gradient (job 0 only)
+  // Cin <= 64 (one chunk): the two 64-row halves of an accumulator hold two different TAPS of that chunk
+  // instead of two channel chunks - no zero half, half the MMAs.  job_tap0 / job_ntaps then count accumulators.
+  int pack2, taps;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -95,14 +98,15 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
         for (int t = 0; t < ntaps; ++t) {
-          int tap = tap0 + t;
-          int kh = tap / P.KW, kw = tap - kh * P.KW;
-          int cw = w0 * P.stride_w + kw - P.pad_l, ch = h0 * P.stride_h + kh - P.pad_t;
           for (int c = 0; c < 2; ++c) {
-            // a chunk with no source reads channel coordinate far outside the tensor -> TMA zero fill
-            const int cm = P.chunk_map[mt * 2 + c];
+            const int tap = P.pack2 ? 2 * (tap0 + t) + c : tap0 + t;
+            const int chunk = P.pack2 ? 0 : mt * 2 + c;
+            int kh = tap / P.KW, kw = tap - kh * P.KW;
+            int cw = w0 * P.stride_w + kw - P.pad_l, ch = h0 * P.stride_h + kh - P.pad_t;
+            // a half with no source reads channel coordinate far outside the tensor -> TMA zero fill
+            const int cm = tap < P.taps ? P.chunk_map[chunk] : -1;
             const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
-            int cc = cm < 0 ? (1 << 20) : P.chunk_c0[mt * 2 + c];
+            int cc = cm < 0 ? (1 << 20) : P.chunk_c0[chunk];
             tc::tma_load_4d(base + (size_t)(t * 2 + c) * WG_CHUNK_BYTES, tm, &full_bar[stage], cc, cw, ch, n);
           }
         }
@@ -150,12 +154,14 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       tc::mbar_wait(acc_full, 0);
       tc::fence_after_sync();
       int row = warp * 32 + lane;
-      int c = mt * 2 + (row >> 6), rc = row & 63;
-      bool valid = P.chunk_map[c] >= 0 && rc < P.chunk_cnt[c];
+      const int c = P.pack2 ? 0 : mt * 2 + (row >> 6), rc = row & 63;
+      const bool row_ok = P.chunk_map[c] >= 0 && rc < P.chunk_cnt[c];
       int ci = P.chunk_ci[c] + rc;
       const bool vec4 = (P.Cout % 4) == 0;
       for (int t = 0; t < ntaps; ++t) {
-        float* dst_row = P.dw + ((size_t)(tap0 + t) * P.Cin + (valid ? ci : 0)) * P.Cout;
+        const int tap = P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
+        const bool valid = row_ok && tap < P.taps;
+        float* dst_row = P.dw + ((size_t)(valid ? tap : 0) * P.Cin + (valid ? ci : 0)) * P.Cout;
         uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * P.n_mma);
         for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
           __syncwarp();
@@ -275,12 +281,22 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
+  P.taps = taps;
+  P.pack2 = (nch == 1 && taps > 1 && !getenv("OF_WG_NO_PACK2")) ? 1 : 0;
+  const int units = P.pack2 ? (taps + 1) / 2 : taps;       // accumulators needed per M tile
+  if (P.pack2) {
+    tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
+    if (tpp > units) tpp = units;
+    while (tpp > 1 && 2 * (tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES) > 200 * 1024) --tpp;
+    passes = (units + tpp - 1) / tpp;
+    tpp = (units + passes - 1) / passes;
+  }
   int m_tiles = (nch + 1) / 2;
   int jobs = 0;
   for (int mt = 0; mt < m_tiles; ++mt)
     for (int p = 0; p < passes; ++p) {
       int t0 = p * tpp;
-      int nt = taps - t0 < tpp ? taps - t0 : tpp;
+      int nt = units - t0 < tpp ? units - t0 : tpp;
       if (nt <= 0) break;
       OF_REQUIRE(jobs < WG_MAX_JOBS, OF_ERR_SHAPE, "too many wgrad jobs");
       P.job_mt[jobs] = mt; P.job_tap0[jobs] = t0; P.job_ntaps[jobs] = nt;

@@ -110,6 +110,9 @@ class ConvLayer:
     def backward(self, dy, need_dx=True):
         """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None."""
         net = self.net
+        if (need_dx and self.bn is None and self.act == L.OF_ACT_NONE and self.k == 3 and self.stride == 1
+                and self.cout == 2 and self.cin <= 32 and self.use_bias and hasattr(net.backend, "head_bwd")):
+            return net.backend.head_bwd(self, dy)     # flow head: dw, db and the chained dz in one pass
         if self.incoming_is_dz:
             dz, self.incoming_is_dz = dy, False
         else:

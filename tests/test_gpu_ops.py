@@ -303,6 +303,41 @@ def test_warp_features_bwd_bf16_incoming_gradient(cuda):
         assert torch.equal(b1, b2)
 
 
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+@pytest.mark.parametrize("shape", [(2, 12, 20, 32), (1, 7, 150, 32), (1, 5, 9, 16)])
+def test_flow_head_backward_fused(cuda, shape, dtype):
+    """of_flow_head_bwd (model.py:114 head: dw, db, chained dz in one pass) vs torch-CPU autograd of
+    leaky_relu -> conv3x3(Cout = 2)."""
+    from optical_flow_b200 import _lib as L
+    N, H, W, Cin = shape
+    r = rng(15)
+    y_prev = r.standard_normal(shape).astype(np.float32)             # previous conv's post-activation output
+    if dtype == "bf16":
+        y_prev = torch.tensor(y_prev).bfloat16().float().numpy()
+    w = (r.standard_normal((3, 3, Cin, 2)) / 10).astype(np.float32)
+    g = r.standard_normal((N, H, W, 2)).astype(np.float32)
+    xt = torch.tensor(y_prev, requires_grad=True)
+    wt = torch.tensor(w, requires_grad=True)
+    bt = torch.zeros(2, requires_grad=True)
+    T.conv2d_same(xt, wt, bt, 1).backward(torch.tensor(g))
+    exp_dz = xt.grad.numpy() * np.where(y_prev > 0, 1.0, 0.3)
+    tdt = torch.float32 if dtype == "f32" else torch.bfloat16
+    xd = torch.tensor(y_prev, device=cuda).to(tdt)
+    dz = torch.empty_like(xd)
+    dw = torch.empty((3, 3, Cin, 2), device=cuda)
+    db = torch.empty((2,), device=cuda)
+    gd, wd = dev(g, cuda), dev(w, cuda)                               # keep the device buffers alive across the call
+    L.check(L.load().of_flow_head_bwd(L.ptr(xd), L.ptr(gd), L.ptr(wd), L.ptr(dw), L.ptr(db), L.ptr(dz),
+                                      N, H, W, Cin, L.OF_ACT_LEAKY, L.dtype_code(xd), L.stream_ptr()), "of_flow_head_bwd")
+    assert_close_maxrel(dw, wt.grad.numpy(), what="head dw")
+    assert_close_maxrel(db, bt.grad.numpy(), what="head db")
+    if dtype == "f32":
+        assert_close_maxrel(dz, exp_dz, what="head dz")
+    else:
+        err = np.abs(dz.float().cpu().numpy() - exp_dz)
+        assert (err <= 2.0 ** -8 * np.abs(exp_dz) + 1e-6).all(), err.max()
+
+
 def test_cost_volume_shape_assert(cuda):
     from optical_flow_b200.model import create_cost_volume
     a = torch.zeros((1, 4, 4, 8), device=cuda)
