@@ -47,6 +47,10 @@ struct WgradParams {
   // Cin <= 64 (one chunk): the two 64-row halves of an accumulator hold two different TAPS of that chunk
   // instead of two channel chunks - no zero half, half the MMAs.  job_tap0 / job_ntaps then count accumulators.
   int pack2, taps;
+  // 3x3 / stride 1 with >= 128 input channels per M tile: a job is one kw column; ONE TMA box
+  // {64, TW, TH + 2} per chunk (the "slab") serves its three kh taps as descriptors at row offsets
+  // kh * TW * 128 B (multiples of the 1024-byte swizzle atom) - half the L2 -> SM bytes of tap-by-tap loads.
+  int slab, slab_bytes;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -84,7 +88,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
   const int k_begin = blockIdx.x * P.ktiles_per_split;
   const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
-  const int a_bytes = ntaps * 2 * WG_CHUNK_BYTES;
+  const int a_bytes = P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
   const int tx_bytes = a_bytes + P.n_chunks * WG_CHUNK_BYTES;
 
   if (warp == 4) {
@@ -97,6 +101,14 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         tc::mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
+        if (P.slab) {
+          for (int c = 0; c < 2; ++c) {
+            const int cm = P.chunk_map[mt * 2 + c];
+            const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
+            int cc = cm < 0 ? (1 << 20) : P.chunk_c0[mt * 2 + c];
+            tc::tma_load_4d(base + (size_t)c * P.slab_bytes, tm, &full_bar[stage], cc, w0 + tap0 - P.pad_l, h0 - P.pad_t, n);
+          }
+        } else
         for (int t = 0; t < ntaps; ++t) {
           for (int c = 0; c < 2; ++c) {
             const int tap = P.pack2 ? 2 * (tap0 + t) + c : tap0 + t;
@@ -125,11 +137,12 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
         uint32_t b_addr = base + (uint32_t)a_bytes;
         for (int t = 0; t < ntaps; ++t) {
-          uint32_t a_addr = base + (uint32_t)(t * 2 * WG_CHUNK_BYTES);
+          uint32_t a_addr = P.slab ? base + (uint32_t)(t * P.TW * 128) : base + (uint32_t)(t * 2 * WG_CHUNK_BYTES);
+          const uint32_t a_lbo = P.slab ? (uint32_t)P.slab_bytes : (uint32_t)WG_CHUNK_BYTES;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             // 16 pixels (K) per MMA = 16 rows of 128 B = 2048 B
-            uint64_t adesc = tc::desc_sw128_mnmajor(a_addr + k * 2048, WG_CHUNK_BYTES);
+            uint64_t adesc = tc::desc_sw128_mnmajor(a_addr + k * 2048, a_lbo);
             uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
             tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
           }
@@ -159,7 +172,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       int ci = P.chunk_ci[c] + rc;
       const bool vec4 = (P.Cout % 4) == 0;
       for (int t = 0; t < ntaps; ++t) {
-        const int tap = P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
+        const int tap = P.slab ? t * P.KW + tap0 : P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
         const bool valid = row_ok && tap < P.taps;
         float* dst_row = P.dw + ((size_t)(valid ? tap : 0) * P.Cin + (valid ? ci : 0)) * P.Cout;
         uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * P.n_mma);
@@ -251,14 +264,22 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int passes = (taps + tpp - 1) / tpp;
   tpp = (taps + passes - 1) / passes;   // balance the groups
 
+  // (slab mode is decided before the tensor maps: its x boxes are TH + 2 rows tall)
+  int x_chunks = 0;
+  for (int s_ = 0; s_ < c->num_src; ++s_) x_chunks += (c->x_valid[s_] + 63) / 64;
+  P.slab = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view && x_chunks >= 2 &&
+            (512 - (c->db ? P.n_mma : 0)) / P.n_mma >= 3 && P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_SLAB"))
+               ? 1 : 0;
+  P.slab_bytes = (P.TH + 2) * P.TW * 128;
+  if (P.slab) { tpp = 3; passes = 3; }
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
   for (int s = 0; s < c->num_src; ++s) {
     long long ws_ = view ? c->view_w_stride : c->x_stride[s];
     long long hs_ = view ? c->view_h_stride : (long long)c->W * c->x_stride[s];
     long long ns_ = view ? c->view_n_stride : (long long)c->H * c->W * c->x_stride[s];
-    if (int r = of_tc_make_view_map(&tmX[s], c->x[s], c->x_c[s], ws_, hs_, ns_, c->N, c->H, c->W, P.TW, P.TH,
-                                    P.stride_w, P.stride_h))
+    if (int r = of_tc_make_view_map(&tmX[s], c->x[s], c->x_c[s], ws_, hs_, ns_, c->N, c->H, c->W, P.TW,
+                                    P.slab ? P.TH + 2 : P.TH, P.stride_w, P.stride_h))
       return r;
   }
   if (c->num_src == 1) tmX[1] = tmX[0];
@@ -295,8 +316,8 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int jobs = 0;
   for (int mt = 0; mt < m_tiles; ++mt)
     for (int p = 0; p < passes; ++p) {
-      int t0 = p * tpp;
-      int nt = units - t0 < tpp ? units - t0 : tpp;
+      int t0 = P.slab ? p : p * tpp;                  // slab: the job's kw; its three taps are kh = 0..2
+      int nt = P.slab ? 3 : (units - t0 < tpp ? units - t0 : tpp);
       if (nt <= 0) break;
       OF_REQUIRE(jobs < WG_MAX_JOBS, OF_ERR_SHAPE, "too many wgrad jobs");
       P.job_mt[jobs] = mt; P.job_tap0[jobs] = t0; P.job_ntaps[jobs] = nt;
@@ -307,7 +328,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (splits < 1) splits = 1;
   P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
-  P.stage_bytes = tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES;
+  P.stage_bytes = (P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) + P.n_chunks * WG_CHUNK_BYTES;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");

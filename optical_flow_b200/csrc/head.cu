@@ -14,6 +14,7 @@
 
 #define HD_SEG 64
 #define HD_WARPS 8
+#define HD_CTAS_PER_SM 6
 
 template <typename TX>
 __global__ void __launch_bounds__(HD_WARPS * 32)
@@ -47,36 +48,51 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
       c0[rr] = (row_ok[rr] && x0 - 1 >= 0) ? __ldg(dy2 + rowbase[rr] + x0 - 1) : make_float2(0.f, 0.f);
       c1[rr] = row_ok[rr] ? __ldg(dy2 + rowbase[rr] + x0) : make_float2(0.f, 0.f);
     }
-    for (int q = x0; q < x1; ++q) {
+    // 4 pixels per iteration: their 12 window columns and 4 activations are loaded up front (16 independent
+    // loads in flight per warp), then consumed in order - the walk is latency-bound otherwise
+    for (int q0 = x0; q0 < x1; q0 += 4) {
+      float2 cn[4][3];
+      float xin[4];
 #pragma unroll
-      for (int rr = 0; rr < 3; ++rr)
-        c2[rr] = (row_ok[rr] && q + 1 < W) ? __ldg(dy2 + rowbase[rr] + q + 1) : make_float2(0.f, 0.f);
-      const size_t e = (rowbase[1] + q) * Cin + ci;
-      const float xv = ch_ok ? ld_f<TX>(x + e) : 0.f;
-      float d = 0.f;
-      // tap (kh,kw) pairs with dy[q - (kh-1, kw-1)] = window[row 2-kh][col 2-kw]
+      for (int k = 0; k < 4; ++k) {
 #pragma unroll
-      for (int kh = 0; kh < 3; ++kh) {
-        const float2 wc[3] = {c0[2 - kh], c1[2 - kh], c2[2 - kh]};
+        for (int rr = 0; rr < 3; ++rr)
+          cn[k][rr] = (row_ok[rr] && q0 + k + 1 < W) ? __ldg(dy2 + rowbase[rr] + q0 + k + 1) : make_float2(0.f, 0.f);
+        xin[k] = (ch_ok && q0 + k < x1) ? ld_f<TX>(x + (rowbase[1] + q0 + k) * Cin + ci) : 0.f;
+      }
 #pragma unroll
-        for (int kw = 0; kw < 3; ++kw) {
-          const float2 g = wc[2 - kw];
-          const int t = kh * 3 + kw;
-          acc[t][0] = fmaf(xv, g.x, acc[t][0]);
-          acc[t][1] = fmaf(xv, g.y, acc[t][1]);
-          d = fmaf(wr[t][0], g.x, d);
-          d = fmaf(wr[t][1], g.y, d);
+      for (int k = 0; k < 4; ++k) {
+        const int q = q0 + k;
+        if (q < x1) {                                   // warp-uniform
+#pragma unroll
+          for (int rr = 0; rr < 3; ++rr) c2[rr] = cn[k][rr];
+          const float xv = xin[k];
+          float d = 0.f;
+          // tap (kh,kw) pairs with dy[q - (kh-1, kw-1)] = window[row 2-kh][col 2-kw]
+#pragma unroll
+          for (int kh = 0; kh < 3; ++kh) {
+            const float2 wc[3] = {c0[2 - kh], c1[2 - kh], c2[2 - kh]};
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+              const float2 g = wc[2 - kw];
+              const int t = kh * 3 + kw;
+              acc[t][0] = fmaf(xv, g.x, acc[t][0]);
+              acc[t][1] = fmaf(xv, g.y, acc[t][1]);
+              d = fmaf(wr[t][0], g.x, d);
+              d = fmaf(wr[t][1], g.y, d);
+            }
+          }
+          bsum[0] += c1[1].x; bsum[1] += c1[1].y;
+          if (dz != nullptr && ch_ok) {
+            float slope = 1.f;
+            if (act == OF_ACT_RELU) slope = xv > 0.f ? 1.f : 0.f;
+            else if (act == OF_ACT_LEAKY) slope = xv > 0.f ? 1.f : 0.3f;
+            st_f<TX>(dz + (rowbase[1] + q) * Cin + ci, d * slope);
+          }
+#pragma unroll
+          for (int rr = 0; rr < 3; ++rr) { c0[rr] = c1[rr]; c1[rr] = c2[rr]; }
         }
       }
-      bsum[0] += c1[1].x; bsum[1] += c1[1].y;
-      if (dz != nullptr && ch_ok) {
-        float slope = 1.f;
-        if (act == OF_ACT_RELU) slope = xv > 0.f ? 1.f : 0.f;
-        else if (act == OF_ACT_LEAKY) slope = xv > 0.f ? 1.f : 0.3f;
-        st_f<TX>(dz + e, d * slope);
-      }
-#pragma unroll
-      for (int rr = 0; rr < 3; ++rr) { c0[rr] = c1[rr]; c1[rr] = c2[rr]; }
     }
   }
   // CTA reduction, then one atomic per value per CTA
@@ -114,7 +130,7 @@ int of_flow_head_bwd(const void* x, const float* dy, const float* w, float* dw, 
   if (db) OF_CUDA(cudaMemsetAsync(db, 0, 2 * sizeof(float), st));
   const long long nseg = (long long)N * H * ((W + HD_SEG - 1) / HD_SEG);
   long long blocks = (nseg + HD_WARPS - 1) / HD_WARPS;
-  if (blocks > OF_NUM_SMS * 4) blocks = OF_NUM_SMS * 4;
+  if (blocks > OF_NUM_SMS * HD_CTAS_PER_SM) blocks = OF_NUM_SMS * HD_CTAS_PER_SM;
   if (dtype == OF_F32)
     flow_head_bwd_kernel<float><<<(int)blocks, HD_WARPS * 32, 0, st>>>((const float*)x, dy, w, dw, db, (float*)dz, N, H, W, Cin, act);
   else
