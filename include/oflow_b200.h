@@ -136,6 +136,10 @@ int of_maxpool2_fwd(const void* in, void* out, int B, int H, int W, int C, int d
 /* gradient goes to the first maximum in window scan order; d_in overwritten. */
 int of_maxpool2_bwd(const void* in, const void* d_out, void* d_in,
                     int B, int H, int W, int C, int dtype, void* stream);
+/* one pass for the stem's backward entry (model.py:12-17): dz = (maxpool2_bwd(in, d_out) + add) * act'(in);
+ * in = the pool input (stem output, post-activation), add = a gradient that reaches it directly. */
+int of_maxpool2_bwd_add_act(const void* in, const void* d_out, const void* add, void* dz,
+                            int B, int H, int W, int C, int act, int dtype, void* stream);
 /* resnet/models.py:31-34: out = relu(a + b) */
 int of_add_relu_fwd(const void* a, const void* b, void* out, size_t n, int dtype, void* stream);
 /* d = d_out * (out > 0) */

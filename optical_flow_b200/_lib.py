@@ -86,6 +86,7 @@ PROTOTYPES = {
     "of_loss_charbonnier_smooth_fwdbwd": (_i, [_vp, _pp, _pp, _ip, _ip, _i, _vp, _i, _i, _i, _vp, _vp]),
     "of_maxpool2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_maxpool2_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "of_maxpool2_bwd_add_act": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_add_relu_fwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "of_relu_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "of_act_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),

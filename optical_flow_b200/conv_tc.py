@@ -107,7 +107,7 @@ def zero_upsample2(dy, H, W):
 
 
 def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloat16, mask=None,
-                    mask_act=L.OF_ACT_NONE, out_channels=None):
+                    mask_act=L.OF_ACT_NONE, out_channels=None, add=None):
     """dx for input channels [seg[0], seg[0]+seg[1]) (default: all).  dz: bf16 (N,Ho,Wo,Cout).
     stride 2 is handled by zero-insertion of dz followed by the stride-1 kernel."""
     KH, KW, Cin, Cout = w_hwio.shape
@@ -123,7 +123,9 @@ def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloa
     kpad = _ceil(dz.shape[-1], 64)
     wp = pack_weights(w_hwio, [(ci0, cnt, 0)], n_mma, kpad, transpose=True)
     out = torch.empty((N, H, W, n_out), dtype=out_dtype, device=dz.device)
-    return tc_run([Source(dz)], wp, n_mma, n_out, N, H, W, H, W, KH, KW, 1, pt, pl, -1, out, mask=mask, mask_act=mask_act)
+    assert add is None or tuple(add.shape) == tuple(out.shape)
+    return tc_run([Source(dz)], wp, n_mma, n_out, N, H, W, H, W, KH, KW, 1, pt, pl, -1, out, mask=mask, mask_act=mask_act,
+                  add=add)
 
 
 def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=True):
@@ -270,8 +272,10 @@ class Bf16Backend:
             chain.incoming_is_dz = True
         return dz
 
-    def dgrad(self, layer, dz, w, in_hw, chain=None):
-        """Returns dx; with `chain` (the ConvLayer producing this layer's input, sole consumer)
+    dgrad_can_add = True
+
+    def dgrad(self, layer, dz, w, in_hw, chain=None, add=None):
+        """Returns dx (+ ``add``, summed in the epilogue); with `chain` (the ConvLayer producing this layer's input, sole consumer)
         the epilogue multiplies by act'(chain.y) and the result is already chain's dz."""
         x = layer.x
         if not self._tc_ok(layer):                       # flow heads: dz is the fp32 d_flow
@@ -287,8 +291,9 @@ class Bf16Backend:
                 dt = torch.bfloat16                       # features segment too: summed in fp32 inside concat_bwd
                 outs.append(conv2d_dgrad_tc(dz, w, in_hw, 1, seg=(s.ci0, s.valid), out_dtype=dt, out_channels=n_out))
             return tuple(outs)
+        assert add is None or self._tc_ok(layer)
         return conv2d_dgrad_tc(dz, w, in_hw, layer.stride, out_dtype=torch.bfloat16, mask=mask,
-                               mask_act=mask_act if mask is not None else L.OF_ACT_NONE)
+                               mask_act=mask_act if mask is not None else L.OF_ACT_NONE, add=add)
 
     # concat [features1, cost_volume, flow_up] (model.py:97-102) as two K-sources
     def concat_fwd(self, fm, f1, f2w, flow_up):

@@ -135,6 +135,42 @@ __global__ void __launch_bounds__(256) maxpool2_bwd_kernel(const T* __restrict__
   }
 }
 
+__device__ __forceinline__ float act_grad(float y, int act);
+__device__ __forceinline__ float4 add_mask4(float4 g, float4 a, float4 y, int act) {
+  return make_float4((g.x + a.x) * act_grad(y.x, act), (g.y + a.y) * act_grad(y.y, act), (g.z + a.z) * act_grad(y.z, act),
+                     (g.w + a.w) * act_grad(y.w, act));
+}
+// model.py:12-17 backward in one pass: dz = (maxpool2_bwd(in, d_out) + add) * act'(in), where `in` is the
+// stem's post-activation output (pool input), `add` the gradient reaching it directly (the finest decoder
+// level reads it too) - replaces three full-tensor passes (pool bwd, accumulate, activation bwd).
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2_bwd_add_act_kernel(const T* __restrict__ in, const T* __restrict__ d_out,
+                                                                   const T* __restrict__ add, T* __restrict__ dz, int B,
+                                                                   int H, int W, int C, int act) {
+  const int oh = H / 2, ow = W / 2, CV = C / 4;
+  size_t total = (size_t)B * oh * ow * CV;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int v = (int)(e % CV);
+    size_t r = e / CV;
+    int x = (int)(r % ow); r /= ow;
+    int y = (int)(r % oh);
+    int b = (int)(r / oh);
+    size_t o = (((size_t)b * H + 2 * y) * W + 2 * x) * C + v * 4;
+    const size_t o1 = o + C, o2 = o + (size_t)W * C, o3 = o2 + C;
+    float4 a = ld4<T>(in + o), bq = ld4<T>(in + o1), c = ld4<T>(in + o2), d = ld4<T>(in + o3);
+    float4 g = ld4<T>(d_out + (((size_t)b * oh + y) * ow + x) * C + v * 4);
+    float4 ga, gb, gc, gd;
+    route4(a.x, bq.x, c.x, d.x, g.x, ga.x, gb.x, gc.x, gd.x);
+    route4(a.y, bq.y, c.y, d.y, g.y, ga.y, gb.y, gc.y, gd.y);
+    route4(a.z, bq.z, c.z, d.z, g.z, ga.z, gb.z, gc.z, gd.z);
+    route4(a.w, bq.w, c.w, d.w, g.w, ga.w, gb.w, gc.w, gd.w);
+    st4<T>(dz + o, add_mask4(ga, ld4<T>(add + o), a, act));
+    st4<T>(dz + o1, add_mask4(gb, ld4<T>(add + o1), bq, act));
+    st4<T>(dz + o2, add_mask4(gc, ld4<T>(add + o2), c, act));
+    st4<T>(dz + o3, add_mask4(gd, ld4<T>(add + o3), d, act));
+  }
+}
+
 // ---- elementwise -------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) add_relu_kernel(const T* __restrict__ a, const T* __restrict__ b,
@@ -232,6 +268,22 @@ int of_maxpool2_bwd(const void* in, const void* d_out, void* d_in, int B, int H,
     maxpool2_bwd_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)in, (const __nv_bfloat16*)d_out, (__nv_bfloat16*)d_in, B, H, W, C);
   return of_launch_check("maxpool2_bwd");
+}
+
+int of_maxpool2_bwd_add_act(const void* in, const void* d_out, const void* add, void* dz, int B, int H, int W, int C,
+                            int act, int dtype, void* stream) {
+  OF_REQUIRE(in && d_out && add && dz, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype) && H % 2 == 0 && W % 2 == 0 && C % 4 == 0, OF_ERR_SHAPE,
+             "maxpool2 backward needs even H, W and C %% 4 == 0");
+  OF_REQUIRE(act >= OF_ACT_NONE && act <= OF_ACT_LEAKY, OF_ERR_ARG, "bad activation %d", act);
+  size_t total = (size_t)B * (H / 2) * (W / 2) * (C / 4);
+  if (dtype == OF_F32)
+    maxpool2_bwd_add_act_kernel<float><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const float*)in, (const float*)d_out, (const float*)add, (float*)dz, B, H, W, C, act);
+  else
+    maxpool2_bwd_add_act_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)in, (const __nv_bfloat16*)d_out, (const __nv_bfloat16*)add, (__nv_bfloat16*)dz, B, H, W, C, act);
+  return of_launch_check("maxpool2_bwd_add_act");
 }
 
 int of_add_relu_fwd(const void* a, const void* b, void* out, size_t n, int dtype, void* stream) {

@@ -225,6 +225,16 @@ def maxpool2_bwd(x, d_out):
     return d_in
 
 
+def maxpool2_bwd_add_act(x, d_out, add, act):
+    """dz = (maxpool2_bwd(x, d_out) + add) * act'(x) in one pass (x = the pool input, post-activation)."""
+    B, H, W, Cc = x.shape
+    assert d_out.dtype == x.dtype and add.dtype == x.dtype and tuple(add.shape) == tuple(x.shape)
+    dz = torch.empty_like(x)
+    L.check(L.load().of_maxpool2_bwd_add_act(L.ptr(x), L.ptr(d_out), L.ptr(add), L.ptr(dz), B, H, W, Cc, act,
+                                             L.dtype_code(x), L.stream_ptr()), "of_maxpool2_bwd_add_act")
+    return dz
+
+
 def add_relu_fwd(a, b):
     out = torch.empty_like(a)
     L.check(L.load().of_add_relu_fwd(L.ptr(a), L.ptr(b), L.ptr(out), a.numel(), L.dtype_code(a), L.stream_ptr()),

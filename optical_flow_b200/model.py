@@ -107,8 +107,9 @@ class ConvLayer:
         self.y = self.net.backend.fprop(self, x, self.w_eff, self.b_eff)
         return self.y
 
-    def backward(self, dy, need_dx=True):
-        """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None."""
+    def backward(self, dy, need_dx=True, add=None):
+        """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None.
+        ``add`` (back-ends with ``dgrad_can_add``): a tensor summed into dx by the dgrad epilogue."""
         net = self.net
         if (need_dx and self.bn is None and self.act == L.OF_ACT_NONE and self.k == 3 and self.stride == 1
                 and self.cout == 2 and self.cin <= 32 and self.use_bias and hasattr(net.backend, "head_bwd")):
@@ -136,6 +137,9 @@ class ConvLayer:
                 "of_bn_fold_bwd")
         if not need_dx:
             return None
+        if add is not None:
+            return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self.prev_chain,
+                                     add=add)
         return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self.prev_chain)
 
 
@@ -184,11 +188,11 @@ class ResnetBlock:
     def backward(self, d_out):
         d_pre = F.act_bwd(self.out, d_out, L.OF_ACT_RELU)        # relu3
         d_y1 = self.conv2.backward(d_pre)
+        skip = self.shortcut.backward(d_pre) if self.down else d_pre
+        if getattr(self.net.backend, "dgrad_can_add", False):
+            return self.conv1.backward(d_y1, add=skip)            # residual sum in the dgrad epilogue
         d_x = self.conv1.backward(d_y1)
-        if self.down:
-            _accumulate(d_x, self.shortcut.backward(d_pre))
-        else:
-            _accumulate(d_x, d_pre)
+        _accumulate(d_x, skip)
         return d_x
 
 
@@ -228,9 +232,10 @@ class Encoder:
             d = self.blocks[k].backward(d)
             if k % 2 == 0 and k > 0:
                 _accumulate(d, d_outs[k // 2])       # output of the previous stage also feeds the decoder
-        d_out0 = F.maxpool2_bwd(self.out0, d)
-        _accumulate(d_out0, d_outs[0])
-        self.conv1.backward(d_out0, need_dx=False)   # images are constants
+        # pool backward + the finest decoder level's gradient + the stem's ReLU derivative, one pass
+        dz0 = F.maxpool2_bwd_add_act(self.out0, d, d_outs[0], self.conv1.act)
+        self.conv1.incoming_is_dz = True
+        self.conv1.backward(dz0, need_dx=False)      # images are constants
 
 
 class FlowModule:

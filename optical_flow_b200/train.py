@@ -64,6 +64,53 @@ class Trainer:
         return loss_value, flows
 
 
+class HostBatchPrefetcher:
+    """Feeds ``Trainer.train_step`` from HOST batches (what data_reader.py:35-64 yields): two device
+    buffers and a copy stream, so the pinned host -> device copy of batch i+1 runs under the compute
+    of batch i.  ``batches`` is any iterable of pinned (B,H,W,6) float32 CPU tensors."""
+
+    def __init__(self, batches, device):
+        self.it = iter(batches)
+        self.device = device
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.bufs = [None, None]
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.k = 0
+        self.pending = None
+        self._issue()
+
+    def _issue(self):
+        try:
+            h = next(self.it)
+        except StopIteration:
+            self.pending = None
+            return
+        slot = self.k % 2
+        if self.bufs[slot] is None or self.bufs[slot].shape != h.shape:
+            self.bufs[slot] = torch.empty(h.shape, dtype=h.dtype, device=self.device)
+            self.free[slot].record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.free[slot])       # the step that last read this buffer is done
+            self.bufs[slot].copy_(h, non_blocking=True)
+            self.ready[slot].record(self.copy_stream)
+        self.pending = slot
+        self.k += 1
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        """Returns (device_batch, release): call ``release()`` after launching the step that reads it."""
+        if self.pending is None:
+            raise StopIteration
+        slot = self.pending
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self.ready[slot])
+        self._issue()                                          # next copy goes out before this step's kernels
+        return self.bufs[slot], (lambda: self.free[slot].record(cur))
+
+
 _default_trainer = None
 
 

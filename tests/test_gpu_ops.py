@@ -494,3 +494,17 @@ def test_adam_steps(cuda):
     # m, v: one fp32 rounding of O(1e-3) values (FMA contraction order) -> absolute floor 1e-9
     np.testing.assert_allclose(md.cpu().numpy(), m, rtol=1e-6, atol=1e-9)
     np.testing.assert_allclose(vd.cpu().numpy(), v, rtol=1e-6, atol=1e-13)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_maxpool2_bwd_add_act_equals_three_passes(cuda, dtype):
+    """of_maxpool2_bwd_add_act == maxpool2_bwd, then += add, then act_bwd (the three passes it replaces)."""
+    from optical_flow_b200 import functional as F, _lib as L
+    r = rng(16)
+    shape = (2, 12, 20, 64)
+    x = torch.tensor(r.standard_normal(shape).astype(np.float32), device=cuda).to(dtype)
+    add = torch.tensor(r.standard_normal(shape).astype(np.float32), device=cuda).to(dtype)
+    d = torch.tensor(r.standard_normal((2, 6, 10, 64)).astype(np.float32), device=cuda).to(dtype)
+    fused = F.maxpool2_bwd_add_act(x, d, add, L.OF_ACT_RELU)
+    ref = (F.maxpool2_bwd(x, d).float() + add.float()) * (x.float() > 0)
+    assert torch.equal(fused.float(), ref.to(dtype).float())
