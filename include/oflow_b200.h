@@ -188,7 +188,12 @@ typedef struct {
   const float* bias; int act;
   const void* add; int add_dtype; int add_stride;
   const void* mask; int mask_dtype; int mask_stride; int mask_act;
+  /* Sign-bit activation masks (3x3 / stride-1 layers with Cout %% 16 == 0, Cout <= 128): sign_out (nullable)
+   * receives 16 bytes per output pixel, bit c = (activated output channel c > 0); a later dgrad passes that
+   * buffer as `mask` with mask_dtype = OF_MASK_BITS instead of re-reading the bf16 activation. */
+  void* sign_out;
 } of_tc_conv;
+#define OF_MASK_BITS 2
 int of_conv_tc_run(const of_tc_conv* c, void* stream);
 /* fp32 HWIO weights -> bf16 packed [taps][rows][cols] (cols %% 64 == 0).  transpose=0: rows = co,
  * cols = packed ci; transpose=1: rows = packed ci, cols = co.  Segment s maps original ci in

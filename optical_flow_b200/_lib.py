@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liboflow_b200.so")
 
 OF_F32, OF_BF16 = 0, 1
+OF_MASK_BITS = 2      # of_tc_conv.mask_dtype: sign-bit mask written by a conv_tc3 fprop (sign_out)
 OF_WARP_REF_IJ, OF_WARP_XY = 0, 1
 OF_ACT_NONE, OF_ACT_RELU, OF_ACT_LEAKY = 0, 1, 2
 
@@ -35,7 +36,8 @@ class TcConv(C.Structure):
                 ("out", C.c_void_p), ("out_dtype", C.c_int), ("out_stride", C.c_int),
                 ("bias", C.c_void_p), ("act", C.c_int),
                 ("add", C.c_void_p), ("add_dtype", C.c_int), ("add_stride", C.c_int),
-                ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("mask_stride", C.c_int), ("mask_act", C.c_int)]
+                ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("mask_stride", C.c_int), ("mask_act", C.c_int),
+                ("sign_out", C.c_void_p)]
 
 
 class TcWgrad(C.Structure):

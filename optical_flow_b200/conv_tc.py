@@ -56,7 +56,7 @@ def pack_weights(w_hwio, segs, rows, cols, transpose, out=None):
 
 
 def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, sign, out,
-           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE):
+           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE, sign_out=None, mask_bits=None):
     d = L.TcConv()
     for k, s in enumerate(sources):
         d.src[k] = s.t.data_ptr()
@@ -75,13 +75,24 @@ def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pa
         d.add, d.add_dtype, d.add_stride = add.data_ptr(), L.dtype_code(add), add.shape[-1]
     if mask is not None:
         d.mask, d.mask_dtype, d.mask_stride, d.mask_act = mask.data_ptr(), L.dtype_code(mask), mask.shape[-1], mask_act
+    if mask_bits is not None:                    # 16 B / pixel sign bits of the producing layer's output
+        assert mask is None and mask_bits.dtype == torch.uint8 and mask_bits.shape[-1] == 16
+        d.mask, d.mask_dtype, d.mask_stride, d.mask_act = mask_bits.data_ptr(), L.OF_MASK_BITS, 0, mask_act
+    if sign_out is not None:
+        assert sign_out.dtype == torch.uint8 and sign_out.shape[-1] == 16
+        d.sign_out = sign_out.data_ptr()
     L.check(L.load().of_conv_tc_run(C.byref(d), L.stream_ptr()), "of_conv_tc_run")
     return out
 
 
 # ------------------------------------------------------------------ functional --
 
-def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None):
+def sign_bits_ok(ksize, stride, cout):
+    """Layers whose fprop can emit (and whose consumers' dgrad can read) the 16 B / pixel sign-bit mask."""
+    return ksize == 3 and stride == 1 and 16 <= cout <= 128 and cout % 16 == 0
+
+
+def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None, sign_out=None):
     """Keras Conv2D(padding='same') forward on tensor cores.  x: bf16 tensor or MultiSource."""
     srcs = _sources_of(x)
     N, H, W = srcs[0].t.shape[:3]
@@ -95,7 +106,8 @@ def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torc
     n_mma = _ceil(Cout, 16)
     wp = pack_weights(w_hwio, segs, n_mma, kb, transpose=False)
     out = torch.empty((N, Ho, Wo, Cout), dtype=out_dtype, device=w_hwio.device)
-    return tc_run(srcs, wp, n_mma, Cout, N, H, W, Ho, Wo, KH, KW, stride, pt, pl, +1, out, bias=bias, act=act, add=add)
+    return tc_run(srcs, wp, n_mma, Cout, N, H, W, Ho, Wo, KH, KW, stride, pt, pl, +1, out, bias=bias, act=act, add=add,
+                  sign_out=sign_out)
 
 
 def zero_upsample2(dy, H, W):
@@ -107,7 +119,7 @@ def zero_upsample2(dy, H, W):
 
 
 def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloat16, mask=None,
-                    mask_act=L.OF_ACT_NONE, out_channels=None, add=None):
+                    mask_act=L.OF_ACT_NONE, out_channels=None, add=None, mask_bits=None):
     """dx for input channels [seg[0], seg[0]+seg[1]) (default: all).  dz: bf16 (N,Ho,Wo,Cout).
     stride 2 is handled by zero-insertion of dz followed by the stride-1 kernel."""
     KH, KW, Cin, Cout = w_hwio.shape
@@ -125,7 +137,7 @@ def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloa
     out = torch.empty((N, H, W, n_out), dtype=out_dtype, device=dz.device)
     assert add is None or tuple(add.shape) == tuple(out.shape)
     return tc_run([Source(dz)], wp, n_mma, n_out, N, H, W, H, W, KH, KW, 1, pt, pl, -1, out, mask=mask, mask_act=mask_act,
-                  add=add)
+                  add=add, mask_bits=mask_bits)
 
 
 def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=True):
@@ -241,7 +253,11 @@ class Bf16Backend:
         if layer.cin < 32:          # conv1 (Cin = 3, 7x7/2): 7-tap tensor-core conv over the packed image
             return conv1_fprop_tc(x, self.img_hw[0], self.img_hw[1], w, b, act=layer.act)
         out_dtype = torch.float32 if layer.cout < 16 else torch.bfloat16     # flow heads stay fp32
-        return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype)
+        layer.ybits = None
+        if layer.act != L.OF_ACT_NONE and sign_bits_ok(layer.k, layer.stride, layer.cout) and layer.cin >= 32:
+            t0 = x.sources[0].t if isinstance(x, MultiSource) else x
+            layer.ybits = torch.empty((t0.shape[0], t0.shape[1], t0.shape[2], 16), dtype=torch.uint8, device=t0.device)
+        return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype, sign_out=layer.ybits)
 
     def act_bwd(self, layer, y, dy):
         if layer.act == L.OF_ACT_NONE:
@@ -280,10 +296,13 @@ class Bf16Backend:
         x = layer.x
         if not self._tc_ok(layer):                       # flow heads: dz is the fp32 d_flow
             return F.conv2d_dgrad(dz, w, in_hw, stride=layer.stride, out_dtype=torch.bfloat16)
-        mask = mask_act = None
+        mask = mask_act = mask_bits = None
         if chain is not None and chain.act != L.OF_ACT_NONE:
             mask, mask_act = chain.y, chain.act
             chain.incoming_is_dz = True
+            # the producer's fprop left a 16 B / pixel sign-bit mask: read that instead of the bf16 activation
+            if getattr(chain, "ybits", None) is not None and layer.k == 3 and layer.stride == 1 and not isinstance(x, MultiSource):
+                mask, mask_bits = None, chain.ybits
         if isinstance(x, MultiSource):
             outs = []
             for s in x.sources:
@@ -293,7 +312,8 @@ class Bf16Backend:
             return tuple(outs)
         assert add is None or self._tc_ok(layer)
         return conv2d_dgrad_tc(dz, w, in_hw, layer.stride, out_dtype=torch.bfloat16, mask=mask,
-                               mask_act=mask_act if mask is not None else L.OF_ACT_NONE, add=add)
+                               mask_act=mask_act if (mask is not None or mask_bits is not None) else L.OF_ACT_NONE,
+                               add=add, mask_bits=mask_bits)
 
     # concat [features1, cost_volume, flow_up] (model.py:97-102) as two K-sources
     def concat_fwd(self, fm, f1, f2w, flow_up):

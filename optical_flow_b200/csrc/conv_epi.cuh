@@ -73,7 +73,9 @@ struct ConvEpi {
   const void* add; int add_dtype; long long add_stride;
   const void* mask; int mask_dtype; long long mask_stride; int mask_act;
   int n_valid;
+  void* sign_out;      // nullable: 16 bytes per pixel, bit c = (output channel c > 0) - a later dgrad's activation mask
 };
+#define OF_MASK_BITS 2   // mask_dtype: `mask` is such a sign-bit buffer (conv_tc3 only)
 
 struct ConvEpi;
 __device__ __forceinline__ void store16(const ConvEpi& E, size_t pix, int c0, const float (&v)[16]);

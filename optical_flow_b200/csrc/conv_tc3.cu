@@ -202,6 +202,14 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         }
       };
       if (mask_coal && !(P.dbg & 2)) load_mask(0);       // in flight while the accumulator is still being produced
+      // sign-bit activation mask (16 B / pixel, written by the producing layer's fprop): one load per row
+      const bool mask_bits = !COAL && P.E.mask != nullptr && P.E.mask_dtype == OF_MASK_BITS;
+      uint64_t mb_lo = 0, mb_hi = 0, sb_lo = 0, sb_hi = 0;
+      if (mask_bits && valid) {
+        const uint4 mb = __ldg(reinterpret_cast<const uint4*>(P.E.mask) + pix);
+        mb_lo = (uint64_t)mb.x | ((uint64_t)mb.y << 32);
+        mb_hi = (uint64_t)mb.z | ((uint64_t)mb.w << 32);
+      }
 
       tc::mbar_wait(&tmem_full[buf], use & 1);
       tc::fence_after_sync();
@@ -223,7 +231,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 #pragma unroll
               for (int k = 0; k < (COAL ? 2 : 4); ++k) if (k < nq) araw[slot][k] = __ldg(qd + k);
             }
-            if (!COAL && P.E.mask) {
+            if (!COAL && P.E.mask && !mask_bits) {
               const int nq = P.E.mask_dtype == OF_BF16 ? 2 : 4;
               const uint4* qd = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.mask) +
                                                                (pix * P.E.mask_stride + c * 16) * (P.E.mask_dtype == OF_BF16 ? 2 : 4));
@@ -286,7 +294,18 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             }
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], P.E.act);
-            if (P.E.mask) {
+            if (P.E.sign_out) {
+              uint32_t m16 = 0;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) m16 |= (v[j] > 0.f ? 1u : 0u) << j;
+              if (c < 4) sb_lo |= (uint64_t)m16 << (16 * c); else sb_hi |= (uint64_t)m16 << (16 * (c - 4));
+            }
+            if (mask_bits) {
+              const uint32_t m16 = (uint32_t)((c < 4 ? mb_lo >> (16 * c) : mb_hi >> (16 * (c - 4))) & 0xffffu);
+              const float s0 = P.E.mask_act == OF_ACT_RELU ? 0.f : (P.E.mask_act == OF_ACT_LEAKY ? 0.3f : 1.f);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] *= ((m16 >> j) & 1u) ? 1.f : s0;
+            } else if (P.E.mask) {
               float t[16];
               unpack16(mraw[slot], P.E.mask_dtype, t);
 #pragma unroll
@@ -330,6 +349,9 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           const int last = c + 1 < nchunks ? c + 1 : c;
           if (COAL && ((last & 3) == 3 || last == nchunks - 1)) flush_group(last >> 2);
         }
+        if (!COAL && P.E.sign_out && valid)
+          reinterpret_cast<uint4*>(P.E.sign_out)[pix] = make_uint4((uint32_t)sb_lo, (uint32_t)(sb_lo >> 32), (uint32_t)sb_hi,
+                                                                    (uint32_t)(sb_hi >> 32));
       }
       tc::fence_before_sync();
       __syncwarp();
@@ -387,6 +409,14 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     P.coal = P.coal && (mode == 1 || (mode == 2 && c->mask != nullptr));
   }
   if (const char* e = getenv("OF_T3_DBG")) P.dbg = atoi(e);
+  const bool bits = c->sign_out != nullptr || (c->mask != nullptr && c->mask_dtype == OF_MASK_BITS);
+  if (bits) {
+    OF_REQUIRE((c->n_valid % 16) == 0 && c->n_valid <= 128 && (c->out_stride % 8) == 0 &&
+                   (((uintptr_t)c->sign_out | (uintptr_t)(c->mask_dtype == OF_MASK_BITS ? c->mask : nullptr)) & 15) == 0 &&
+                   (c->add == nullptr || (c->add_stride % 8) == 0),
+               OF_ERR_UNSUPPORTED, "sign-bit masks need Cout %% 16 == 0, Cout <= 128 and 16-byte aligned rows");
+    P.coal = 0;
+  }
   // ring depths: TMA latency (~2k cycles loaded) must be covered by the MMAs of the slots in flight.
   // One slab feeds 24 MMAs (~1.6k cycles at Cout = 128), one weight tile 8 (~0.5k): 3 slabs + >= 4 tiles.
   const int stg_bytes = P.coal ? T3_EPI_WARPS * T3_WSTG_BYTES : 0;
@@ -408,6 +438,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.E.add = c->add; P.E.add_dtype = c->add_dtype; P.E.add_stride = c->add_stride;
   P.E.mask = c->mask; P.E.mask_dtype = c->mask_dtype; P.E.mask_stride = c->mask_stride; P.E.mask_act = c->mask_act;
   P.E.n_valid = c->n_valid;
+  P.E.sign_out = c->sign_out;
 
   CUtensorMap tmA[2], tmB;
   memset(tmA, 0, sizeof(tmA));

@@ -1,4 +1,3 @@
 set -x
 python -m pytest tests -x -q -m gpu 2>&1 | tail -8
 python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | cut -c1-200
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | grep -o '"e2e": {[^}]*}'

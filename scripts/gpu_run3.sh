@@ -1,6 +1,5 @@
 set -x
-python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2>&1 || exit 1
-ncu --set full --clock-control none -k regex:"cv7|colsum|copy_channels|sample_bwd|smallcout|act_bwd|zero_upsample|gemm_simt" -c 60 -o /tmp/misc_full -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu3.log 2>&1
-echo rc $?
-ncu -i /tmp/misc_full.ncu-rep --page raw --csv > gpurun_out/r01_misc_raw.csv 2>/dev/null
-ls -la /tmp/misc_full.ncu-rep gpurun_out/
+python scripts/prof_conv_pair.py || exit 1
+ncu --set full --clock-control none -k regex:"conv_tc3" -s 6 -c 3 -o /tmp/pair -f python scripts/prof_conv_pair.py > gpurun_out/ncu3.log 2>&1
+ncu -i /tmp/pair.ncu-rep --page raw --csv > gpurun_out/r01_conv_pair_raw.csv 2>/dev/null
+ls -la /tmp/pair.ncu-rep

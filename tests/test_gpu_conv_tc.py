@@ -132,6 +132,30 @@ def test_tc3_staged_epilogue_variant(cuda, cfg, monkeypatch):
     test_tc_dgrad(cuda, cfg)
 
 
+@pytest.mark.parametrize("cfg", [(2, 24, 32, 64, 3, 64, 1), (1, 16, 48, 128, 3, 96, 1), (1, 9, 13, 64, 3, 32, 1)])
+def test_tc3_sign_bit_mask(cuda, cfg):
+    """fprop emits 16 B / pixel sign bits of its activated output; a dgrad that takes them as its mask gives
+    exactly what the bf16-activation mask gives."""
+    from optical_flow_b200 import conv_tc, _lib as L
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 6)
+    xd = torch.tensor(x, device=cuda).bfloat16()
+    bits = torch.zeros((N, H, W, 16), dtype=torch.uint8, device=cuda)
+    y = conv_tc.conv2d_fprop_tc(xd, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), act=L.OF_ACT_LEAKY,
+                                sign_out=bits)
+    exp_bits = (y.float() > 0).cpu().numpy()
+    got = np.unpackbits(bits.cpu().numpy(), axis=-1, bitorder="little")[..., :Cout].astype(bool)
+    assert np.array_equal(got, exp_bits)
+    # a following layer (Cout -> Cin2) whose dgrad masks with this layer's activation
+    r = np.random.default_rng(7)
+    Cin2 = 64
+    w2 = bf16_round((r.standard_normal((3, 3, Cout, Cin2)) / 20).astype(np.float32))
+    g = torch.tensor(bf16_round(r.standard_normal((N, H, W, Cin2)).astype(np.float32)), device=cuda).bfloat16()
+    a = conv_tc.conv2d_dgrad_tc(g, torch.tensor(w2, device=cuda), (H, W), 1, mask=y, mask_act=L.OF_ACT_LEAKY)
+    bq = conv_tc.conv2d_dgrad_tc(g, torch.tensor(w2, device=cuda), (H, W), 1, mask_bits=bits, mask_act=L.OF_ACT_LEAKY)
+    assert torch.equal(a, bq)
+
+
 def test_tc_dgrad_segments(cuda):
     """dgrad of the first decoder conv: one launch per concat segment (features | cv+flow)."""
     from optical_flow_b200 import conv_tc
