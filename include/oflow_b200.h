@@ -213,10 +213,11 @@ typedef struct {
 } of_tc_wgrad;
 int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream);
 /* Stem (model.py:12, Cin = 3, 7x7 / 2) on tensor cores.  of_pack_image_pair8: imgs (B,H,W,6) f32 -> bf16
- * (2B, H+5, W+6, 8): frame 1s then frame 2s, TF-SAME zero border (2 top/left, 3 bottom / 4 right), channels
- * 3..7 zero.  A window of 8 consecutive pixels is then one 64-element K chunk (kw*8 + c) and the 7x7/2 conv is
- * a 7-tap (kh) conv over the view {W pitch 16 elements, H pitch (W+6)*8}.  of_conv1_pack_weights: folded f32
- * (7,7,3,Cout) -> bf16 [7][Cout][64]; of_conv1_unpack_wgrad: dw_view f32 [7][64][Cout] -> (7,7,3,Cout). */
+ * (2B, (H+6)/2, W+6, 2, 4): frame 1s then frame 2s, TF-SAME zero border (2 rows / cols before, 4 after); one 16-byte
+ * texel = the pixels of two consecutive rows (2 pr - 2, 2 pr - 1) x 4 channels (3 used).  A window of 8 texels is one
+ * 64-element K chunk ((kw, p, c) -> kw*8 + p*4 + c, kh = 2 tap + p) and the 7x7/2 conv is a 4-tap stride-1 conv
+ * over the view {W pitch 16 elements, H pitch (W+6)*8}.  of_conv1_pack_weights: folded f32 (7,7,3,Cout) -> bf16
+ * [4][Cout][64]; of_conv1_unpack_wgrad: dw_view f32 [4][64][Cout] -> (7,7,3,Cout). */
 int of_pack_image_pair8(const float* imgs, void* out, int B, int H, int W, void* stream);
 int of_conv1_pack_weights(const float* w_hwio, void* packed, int Cout, void* stream);
 int of_conv1_unpack_wgrad(const float* dw_view, float* dw_hwio, int Cout, void* stream);

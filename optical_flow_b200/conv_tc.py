@@ -8,6 +8,7 @@ tensor-core shaped (Cin = 3 stem, Cout = 2 flow heads' dgrad/wgrad) use the SIMT
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -166,7 +167,7 @@ def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=Tru
     if need_bias_grad and db is None:
         db = torch.empty((Cout,), dtype=torch.float32, device=dz.device)
     # bias gradient fused into the wgrad launch (ones-operand MMA) when a TMEM accumulator is spare
-    fuse_db = need_bias_grad and (Cout + 15) // 16 * 16 <= 128
+    fuse_db = need_bias_grad and (Cout + 15) // 16 * 16 <= 128 and not os.environ.get("OF_WG_NO_BIAS")
     if fuse_db:
         d.db = db.data_ptr()
     L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad")
@@ -179,28 +180,30 @@ def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=Tru
 # ------------------------------------------------------- stem (Cin = 3) on tensor cores --
 
 def pack_image_pair8(batch_imgs):
-    """(B,H,W,6) f32 -> bf16 (2B, H+5, W+6, 8): frame 1s then frame 2s (model.py:122-123,131-132), TF-SAME
-    zero border of the 7x7/2 stem, channels 3..7 zero.  8 consecutive pixels = one 64-wide K chunk."""
+    """(B,H,W,6) f32 -> bf16 (2B, (H+6)/2, W+6, 8): frame 1s then frame 2s (model.py:122-123,131-132), TF-SAME
+    zero border of the 7x7/2 stem; a texel holds the pixels of two consecutive rows x 4 channels (3 used), so 8
+    consecutive texels = one 64-wide K chunk covering two kh taps."""
     B, H, W, _ = batch_imgs.shape
-    out = torch.empty((2 * B, H + 5, W + 6, 8), dtype=torch.bfloat16, device=batch_imgs.device)
+    assert H % 2 == 0 and W % 2 == 0
+    out = torch.empty((2 * B, (H + 6) // 2, W + 6, 8), dtype=torch.bfloat16, device=batch_imgs.device)
     L.check(L.load().of_pack_image_pair8(L.ptr(batch_imgs), L.ptr(out), B, H, W, L.stream_ptr()), "of_pack_image_pair8")
     return out
 
 
 def _stem_view(d, xp, H, W):
     """Describe the packed image as the strided view the stem convolves: windows of 8 pixels every 2."""
-    Hp, Wp = H + 5, W + 6
+    Hp, Wp = (H + 6) // 2, W + 6                      # row pairs, padded columns
     d.N, d.H, d.W, d.Ho, d.Wo = xp.shape[0], Hp, W // 2, H // 2, W // 2
-    d.KH, d.KW, d.stride, d.pad_t, d.pad_l = 7, 1, 2, 0, 0
-    d.stride_w, d.stride_h = 1, 2
+    d.KH, d.KW, d.stride, d.pad_t, d.pad_l = 4, 1, 1, 0, 0
+    d.stride_w, d.stride_h = 1, 1
     d.view_w_stride, d.view_h_stride, d.view_n_stride = 16, Wp * 8, Hp * Wp * 8
 
 
 def conv1_fprop_tc(xp, H, W, w_hwio, bias, act=L.OF_ACT_RELU, out_dtype=torch.bfloat16):
-    """model.py:12-15 stem: Conv2D(64, 7, strides=2, 'same') (+ folded BN + ReLU) as a 7-tap conv over the view."""
+    """model.py:12-15 stem: Conv2D(64, 7, strides=2, 'same') (+ folded BN + ReLU) as a 4-tap (row pair) conv over the view."""
     Cout = w_hwio.shape[3]
     assert tuple(w_hwio.shape[:3]) == (7, 7, 3) and Cout % 16 == 0
-    wp = torch.empty((7, Cout, 64), dtype=torch.bfloat16, device=xp.device)
+    wp = torch.empty((4, Cout, 64), dtype=torch.bfloat16, device=xp.device)
     L.check(L.load().of_conv1_pack_weights(L.ptr(w_hwio), L.ptr(wp), Cout, L.stream_ptr()), "of_conv1_pack_weights")
     out = torch.empty((xp.shape[0], H // 2, W // 2, Cout), dtype=out_dtype, device=xp.device)
     d = L.TcConv()
@@ -217,7 +220,7 @@ def conv1_fprop_tc(xp, H, W, w_hwio, bias, act=L.OF_ACT_RELU, out_dtype=torch.bf
 def conv1_wgrad_tc(xp, H, W, dz, dw, db):
     """dw (7,7,3,Cout) f32, db (Cout) f32 of the stem from the packed image and bf16 dz."""
     Cout = dz.shape[-1]
-    dwv = torch.empty((7, 64, Cout), dtype=torch.float32, device=dz.device)
+    dwv = torch.empty((4, 64, Cout), dtype=torch.float32, device=dz.device)
     d = L.TcWgrad()
     d.x[0], d.x_c[0], d.x_stride[0], d.x_valid[0], d.x_ci0[0], d.num_src = xp.data_ptr(), 64, 16, 64, 0, 1
     d.dy, d.dy_c, d.dy_stride = dz.data_ptr(), Cout, Cout
@@ -250,7 +253,7 @@ class Bf16Backend:
         return pack_image_pair8(batch_imgs)
 
     def fprop(self, layer, x, w, b):
-        if layer.cin < 32:          # conv1 (Cin = 3, 7x7/2): 7-tap tensor-core conv over the packed image
+        if layer.cin < 32:          # conv1 (Cin = 3, 7x7/2): 4-tap (row pair) tensor-core conv over the packed image
             return conv1_fprop_tc(x, self.img_hw[0], self.img_hw[1], w, b, act=layer.act)
         out_dtype = torch.float32 if layer.cout < 16 else torch.bfloat16     # flow heads stay fp32
         layer.ybits = None

@@ -136,7 +136,12 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
     int stage = 0; uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x) {
       int b, y, x0; ct_decode(P, tile, b, y, x0);
-      uint32_t w[32];                                   // from_f2: this pixel's 49 gradient values (bf16 pairs)
+      // All gradient values this thread needs for the tile's 7 steps are fetched up front (the loads are
+      // independent, their latency overlaps the pipeline); per step only shared-memory stores remain.
+      //   from_f2 : own pixel (y, x0 + tb), all 49 values (7 x 16 B)
+      //   else    : window column tb (and tb + 128 for tb < 6) of row y - i + 3, the 7 values of step i
+      //             = 14 B at byte offset 14 i -> the four 32-bit words from word (14 i - 2 (i & 1)) / 4
+      uint32_t w[28], wa[7][4], wb[7][4];
       if (P.from_f2) {
         const int x = x0 + tb;
         if (x < P.W) {
@@ -149,6 +154,23 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
         } else {
 #pragma unroll
           for (int q = 0; q < 28; ++q) w[q] = 0;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const int ys = y - i + 3;
+          const bool row_ok = ys >= 0 && ys < P.H;
+          const int wofs = (14 * i - 2 * (i & 1)) / 4;
+          const int xa = x0 - 3 + tb, xb = xa + 128;
+          const bool oka = row_ok && xa >= 0 && xa < P.W;
+          const bool okb = row_ok && tb < 6 && xb < P.W;
+          const uint32_t* pa = reinterpret_cast<const uint32_t*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (oka ? xa : 0)) * P.cv_stride) + wofs;
+          const uint32_t* pb = reinterpret_cast<const uint32_t*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (okb ? xb : 0)) * P.cv_stride) + wofs;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            wa[i][q] = oka ? __ldg(pa + q) : 0u;
+            wb[i][q] = okb ? __ldg(pb + q) : 0u;
+          }
         }
       }
 #pragma unroll
@@ -163,26 +185,16 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
             g_store(G, tb, tb + j, v);
           }
         } else {
-          const int ys = y - i + 3;
-          const bool row_ok = ys >= 0 && ys < P.H;
-          for (int nn = tb; nn < CT_NB - 10; nn += 128) {          // columns 134..143 never reach the band
-            const int xn = x0 - 3 + nn;
-            uint32_t ww[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) ww[q] = 0;
-            const int q0 = (i * 14) >> 4;                           // first 16-byte unit holding element i*7
-            if (row_ok && xn >= 0 && xn < P.W) {
-              const uint4* src = reinterpret_cast<const uint4*>(P.d_cv + (((size_t)b * P.H + ys) * P.W + xn) * P.cv_stride);
-              uint4 v0 = __ldg(src + q0), v1 = __ldg(src + q0 + 1);
-              ww[0] = v0.x; ww[1] = v0.y; ww[2] = v0.z; ww[3] = v0.w;
-              ww[4] = v1.x; ww[5] = v1.y; ww[6] = v1.z; ww[7] = v1.w;
-            }
-#pragma unroll
-            for (int j = 0; j < 7; ++j) {
-              const int e = i * 7 + j - 8 * q0;                     // element inside the 16-element window
-              const uint16_t v = (uint16_t)((e & 1) ? (ww[e >> 1] >> 16) : (ww[e >> 1] & 0xffffu));
-              const int mm = nn - 6 + j;
-              if (mm >= 0 && mm < CT_M) g_store(G, mm, nn, v);
+          for (int j = 0; j < 7; ++j) {
+            const int h = (i & 1) + j;                               // half-word inside the 4-word window
+            const uint16_t va = (uint16_t)((h & 1) ? (wa[i][h >> 1] >> 16) : (wa[i][h >> 1] & 0xffffu));
+            const int ma = tb - 6 + j;
+            if (ma >= 0) g_store(G, ma, tb, va);                     // ma <= tb <= 127
+            if (tb < 6) {
+              const uint16_t vb = (uint16_t)((h & 1) ? (wb[i][h >> 1] >> 16) : (wb[i][h >> 1] & 0xffffu));
+              const int mb = tb + 128 - 6 + j;
+              if (mb < CT_M) g_store(G, mb, tb + 128, vb);
             }
           }
         }

@@ -111,40 +111,50 @@ __global__ void __launch_bounds__(256) zero_upsample2_kernel(const T* __restrict
 }
 
 // ---- stem (Cin = 3, 7x7 / 2) on tensor cores: packed image + weight (un)packing ------------------
-// out (2B, H+5, W+6, 8) bf16: frame 1s then frame 2s, TF-SAME zero border, channels 3..7 zero.
+// out (2B, (H+6)/2, W+6, 2, 4) bf16: frame 1s then frame 2s; TF-SAME zero border (2 rows / 2 cols before, 4 after);
+// one 16-byte texel = the pixel of TWO consecutive image rows (row pair pr = rows 2 pr - 2, 2 pr - 1) x 4 channels
+// (3 used).  A window of 8 texels is then one 64-element K chunk holding two kh taps x 7 kw x 3 channels, and the
+// 7x7 / 2 stem is a 4-tap, stride-1 conv over row pairs (K = 256 instead of 7 x 64 = 448).
 __global__ void __launch_bounds__(256) pack_pair8_kernel(const float* __restrict__ imgs, uint4* __restrict__ out,
                                                          int B, int H, int W) {
-  const int Hp = H + 5, Wp = W + 6;
+  const int Hp = (H + 6) / 2, Wp = W + 6;
   size_t total = (size_t)2 * B * Hp * Wp;
   for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(e % Wp) - 2;
     size_t r2 = e / Wp;
-    int r = (int)(r2 % Hp) - 2;
+    int r0 = 2 * (int)(r2 % Hp) - 2;
     int n = (int)(r2 / Hp);
     int half = n >= B, b = n - half * B;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (r >= 0 && r < H && c >= 0 && c < W) {
-      const float* p = imgs + (((size_t)b * H + r) * W + c) * 6 + half * 3;
-      __nv_bfloat162 a = __floats2bfloat162_rn(__ldg(p), __ldg(p + 1));
-      __nv_bfloat162 d = __floats2bfloat162_rn(__ldg(p + 2), 0.f);
-      v.x = *reinterpret_cast<uint32_t*>(&a);
-      v.y = *reinterpret_cast<uint32_t*>(&d);
+    uint32_t wv[4] = {0u, 0u, 0u, 0u};
+    if (c >= 0 && c < W) {
+#pragma unroll
+      for (int p = 0; p < 2; ++p) {
+        const int r = r0 + p;
+        if (r >= 0 && r < H) {
+          const float* q = imgs + (((size_t)b * H + r) * W + c) * 6 + half * 3;
+          __nv_bfloat162 a = __floats2bfloat162_rn(__ldg(q), __ldg(q + 1));
+          __nv_bfloat162 d = __floats2bfloat162_rn(__ldg(q + 2), 0.f);
+          wv[2 * p] = *reinterpret_cast<uint32_t*>(&a);
+          wv[2 * p + 1] = *reinterpret_cast<uint32_t*>(&d);
+        }
+      }
     }
-    out[e] = v;
+    out[e] = make_uint4(wv[0], wv[1], wv[2], wv[3]);
   }
 }
-// w (7,7,3,Cout) f32 -> bf16 [kh][co][kw*8 + c]  (kw = 7 and c >= 3 are zero)
+// w (7,7,3,Cout) f32 -> bf16 [tap][co][kw*8 + p*4 + c],  kh = 2 tap + p  (kh = 7, kw = 7 and c = 3 are zero)
 __global__ void __launch_bounds__(256) conv1_pack_w_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out,
                                                            int Cout) {
-  int total = 7 * Cout * 64;
+  int total = 4 * Cout * 64;
   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
-    int col = e & 63, co = (e >> 6) % Cout, kh = (e >> 6) / Cout;
-    int kw = col >> 3, c = col & 7;
-    float v = (kw < 7 && c < 3) ? w[((size_t)(kh * 7 + kw) * 3 + c) * Cout + co] : 0.f;
+    int col = e & 63, co = (e >> 6) % Cout, tap = (e >> 6) / Cout;
+    int kw = col >> 3, p = (col >> 2) & 1, c = col & 3;
+    int kh = 2 * tap + p;
+    float v = (kh < 7 && kw < 7 && c < 3) ? w[((size_t)(kh * 7 + kw) * 3 + c) * Cout + co] : 0.f;
     out[e] = __float2bfloat16_rn(v);
   }
 }
-// dw_view [kh][kw*8 + c][co] f32 -> dw (7,7,3,Cout)
+// dw_view [tap][kw*8 + p*4 + c][co] f32 -> dw (7,7,3,Cout)
 __global__ void __launch_bounds__(256) conv1_unpack_dw_kernel(const float* __restrict__ dwv, float* __restrict__ dw,
                                                               int Cout) {
   int total = 7 * 7 * 3 * Cout;
@@ -152,7 +162,7 @@ __global__ void __launch_bounds__(256) conv1_unpack_dw_kernel(const float* __res
     int co = e % Cout, t = e / Cout;
     int c = t % 3; t /= 3;
     int kw = t % 7, kh = t / 7;
-    dw[e] = dwv[((size_t)kh * 64 + kw * 8 + c) * Cout + co];
+    dw[e] = dwv[((size_t)(kh >> 1) * 64 + kw * 8 + (kh & 1) * 4 + c) * Cout + co];
   }
 }
 
@@ -229,14 +239,14 @@ int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const flo
 int of_pack_image_pair8(const float* imgs, void* out, int B, int H, int W, void* stream) {
   OF_REQUIRE(imgs && out, OF_ERR_ARG, "null pointer argument");
   OF_REQUIRE(B > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, OF_ERR_SHAPE, "bad dims (even H, W)");
-  size_t total = (size_t)2 * B * (H + 5) * (W + 6);
+  size_t total = (size_t)2 * B * ((H + 6) / 2) * (W + 6);
   pack_pair8_kernel<<<g_grid(total), 256, 0, (cudaStream_t)stream>>>(imgs, (uint4*)out, B, H, W);
   return of_launch_check("pack_pair8_kernel");
 }
 
 int of_conv1_pack_weights(const float* w_hwio, void* packed, int Cout, void* stream) {
   OF_REQUIRE(w_hwio && packed && Cout > 0, OF_ERR_ARG, "bad argument");
-  conv1_pack_w_kernel<<<g_grid((size_t)7 * Cout * 64), 256, 0, (cudaStream_t)stream>>>(w_hwio, (__nv_bfloat16*)packed, Cout);
+  conv1_pack_w_kernel<<<g_grid((size_t)4 * Cout * 64), 256, 0, (cudaStream_t)stream>>>(w_hwio, (__nv_bfloat16*)packed, Cout);
   return of_launch_check("conv1_pack_w_kernel");
 }
 

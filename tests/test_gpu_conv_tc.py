@@ -224,7 +224,7 @@ def test_tc_wgrad_two_sources(cuda):
 # ------------------------------------------------------------------ stem (Cin = 3, 7x7 / 2) --
 @pytest.mark.parametrize("B,H,W", [(1, 32, 48), (2, 64, 96), (1, 128, 416)])
 def test_tc_stem_fprop_wgrad(cuda, B, H, W):
-    """model.py:12-15 conv1 as a 7-tap tensor-core conv over overlapping 8-pixel windows of the packed
+    """model.py:12-15 conv1 as a 4-tap (row pair) tensor-core conv over overlapping 8-texel windows of the packed
     image pair (an overlapping-stride TMA view), forward and weight gradient, vs torch on the same
     bf16-rounded operands."""
     from optical_flow_b200 import conv_tc, _lib as L
@@ -237,7 +237,7 @@ def test_tc_stem_fprop_wgrad(cuda, B, H, W):
     zt = T.conv2d_same(torch.tensor(x2), wt, bt, 2)
     ref = torch.relu(zt).detach().numpy()
     xp = conv_tc.pack_image_pair8(torch.tensor(imgs, device=cuda))
-    assert tuple(xp.shape) == (2 * B, H + 5, W + 6, 8)
+    assert tuple(xp.shape) == (2 * B, (H + 6) // 2, W + 6, 8)
     y = conv_tc.conv1_fprop_tc(xp, H, W, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), act=L.OF_ACT_RELU)
     assert tuple(y.shape) == ref.shape
     assert rel_err(y, ref) <= 2.0 ** -7, rel_err(y, ref)
