@@ -467,8 +467,12 @@ def bench_train(args, dev, world, rank):
         # dominant kernel = conv_tc3_kernel on the decoder's finest level (model.py:104-114; 55 % of the
         # step's FLOPs are level-3 3x3 convs): its 128->128 layer timed live, alone, with CUDA events
         dom = time_dominant_conv(torch, dev, B, H // 2, W // 2, 128, 128, iters=max(args.steps, 10))
+        traffic = None                                   # DRAM bytes per launch of that kernel, from the committed ncu capture
+        tpath = os.path.join(ROOT, "profiles", "r01_roofline_traffic.json")
+        if (B, H, W) == (8, 384, 1280) and os.path.exists(tpath):
+            traffic = json.load(open(tpath))["conv_tc3_fprop_N8_192x640_128_128"]["traffic_bytes"]
         roof = {"bound": "tensor", "achieved": dom["tflops"], "peak": peaks["tf_burst"], "unit": "TFLOP/s",
-                "frac": dom["tflops"] / peaks["tf_burst"], "traffic": None,
+                "frac": dom["tflops"] / peaks["tf_burst"], "traffic": traffic,
                 "kernel": "conv_tc3_kernel (tcgen05 implicit GEMM), decoder level-3 conv 128->128 3x3 fprop: "
                           "M=%d K=1152 N=128, %.1f us/launch over %d launches" % (B * (H // 2) * (W // 2), dom["us"], dom["iters"]),
                 "algorithmic_flops": dom["flops"], "peak_source": peaks["src"] + " (burst bf16: kernel timed alone)",

@@ -32,6 +32,28 @@ void of_set_error(const char* fmt, ...);
 
 void of_count_launch(void);
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------
+// The tensor-core kernels are launched with programmatic stream serialization: the next kernel's CTAs may
+// become resident (barrier init, TMEM allocation, tensor-map prefetch) while the previous kernel drains.
+// Every such kernel executes OF_PDL_WAIT() before its first access to global memory (the wait returns when
+// the previous grid has completed and its writes are visible) and OF_PDL_TRIGGER() at its start.
+#define OF_PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#define OF_PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#ifdef __CUDACC__
+#include <stdlib.h>
+template <typename... KArgs, typename... Args>
+static inline cudaError_t of_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                        Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = getenv("OF_NO_PDL") ? 0 : 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 static inline int of_launch_check(const char* what) {
   of_count_launch();
   cudaError_t e = cudaGetLastError();

@@ -69,6 +69,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols);
     tc::tmem_relinquish();
   }
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
+  OF_PDL_WAIT();                                     // nothing above touches global memory
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -417,7 +419,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
     attr_set = true;
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
-  conv_tc_kernel<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
+  OF_CUDA(of_launch_pdl(conv_tc_kernel, dim3(grid), dim3(TC_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   return of_launch_check("conv_tc_kernel");
 }
 

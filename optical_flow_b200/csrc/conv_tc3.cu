@@ -70,7 +70,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   __shared__ float s_bias[128];                     // n_mma <= 128: bias read once, not per chunk per pixel
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x < 128) s_bias[threadIdx.x] = (P.E.bias && (int)threadIdx.x < P.E.n_valid) ? P.E.bias[threadIdx.x] : 0.f;
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
   if (threadIdx.x == 0) {
     for (int s = 0; s < P.na; ++s) { tc::mbar_init(&a_full[s], 1); tc::mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < P.nb; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
@@ -86,6 +86,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols);
     tc::tmem_relinquish();
   }
+  OF_PDL_WAIT();                                     // first global access below: the bias
+  if (threadIdx.x < 128) s_bias[threadIdx.x] = (P.E.bias && (int)threadIdx.x < P.E.n_valid) ? P.E.bias[threadIdx.x] : 0.f;
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -458,8 +460,8 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     attr_set = true;
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
-  if (P.coal) conv_tc3_kernel<true><<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
-  else conv_tc3_kernel<false><<<grid, T3_THREADS, smem, (cudaStream_t)stream>>>(tmA[0], tmA[1], tmB, P);
+  if (P.coal) OF_CUDA(of_launch_pdl(conv_tc3_kernel<true>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+  else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   if (int r = of_launch_check("conv_tc3_kernel")) return r;
   return 1;
 }

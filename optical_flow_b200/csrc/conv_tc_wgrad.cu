@@ -79,6 +79,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     tc::fence_proxy_async();                               // generic-proxy writes -> visible to the MMA's reads
   }
   if (warp == 5) { tc::tmem_alloc(tmem_base_slot, (uint32_t)P.tmem_cols); tc::tmem_relinquish(); }
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
+  OF_PDL_WAIT();                                     // nothing above touches global memory
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -336,7 +338,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
   dim3 grid(splits, jobs);
-  conv_tc_wgrad_kernel<<<grid, WG_THREADS, smem, st>>>(tmX[0], tmX[1], tmDY, P);
+  OF_CUDA(of_launch_pdl(conv_tc_wgrad_kernel, grid, dim3(WG_THREADS), smem, st, tmX[0], tmX[1], tmDY, P));
   if (int r = of_launch_check("conv_tc_wgrad_kernel")) return r;
   return 0;
 }

@@ -80,6 +80,8 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
     for (int i = threadIdx.x; i < CT_G_BYTES / 16; i += CT_THREADS)
       reinterpret_cast<uint4*>(base + (size_t)s * P.stage_bytes)[i] = make_uint4(0, 0, 0, 0);
   tc::fence_proxy_async();
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
+  OF_PDL_WAIT();                                     // nothing above touches global memory
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -286,6 +288,8 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
   }
   if (warp == 0 && lane == 0) { tc::prefetch_tmap(&tmF1); tc::prefetch_tmap(&tmF2); }
   if (warp == 1) { tc::tmem_alloc(tmem_slot, 512); tc::tmem_relinquish(); }
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
+  OF_PDL_WAIT();                                     // nothing above touches global memory
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -458,7 +462,7 @@ int cvtc_fwd_try(const void* f1, const void* f2, void* cv, int B, int H, int W, 
   if (int r = of_tc_make_view_map(&tm2, f2, C, C, (long long)W * C, (long long)H * W * C, B, H, W, CT_NB, 1, 1, 1)) return r;
   size_t smem = 1024 + (size_t)P.a_bufs * P.nchunks * CT_A_BYTES + (size_t)P.stages * P.stage_bytes + 256;
   int grid = P.ntiles < OF_NUM_SMS ? P.ntiles : OF_NUM_SMS;
-  cvtc_fwd_kernel<<<grid, CT_THREADS, smem, st>>>(tm1, tm2, P);
+  OF_CUDA(of_launch_pdl(cvtc_fwd_kernel, dim3(grid), dim3(CT_THREADS), smem, st, tm1, tm2, P));
   if (int r = of_launch_check("cvtc_fwd_kernel")) return r;
   return 1;
 }
@@ -483,12 +487,12 @@ int cvtc_bwd_try(const void* f1, const void* f2, const void* d_cv, void* d_f1, v
   // d_f1: features = f2
   if (int r = of_tc_make_view_map(&tm, f2, C, C, (long long)W * C, (long long)H * W * C, B, H, W, CT_NB, 1, 1, 1)) return r;
   P.from_f2 = 1; P.out = (__nv_bfloat16*)d_f1; P.add = (const __nv_bfloat16*)d_f1_add;
-  cvtc_bwd_kernel<<<grid, CT_THREADS, smem, st>>>(tm, P);
+  OF_CUDA(of_launch_pdl(cvtc_bwd_kernel, dim3(grid), dim3(CT_THREADS), smem, st, tm, P));
   if (int r = of_launch_check("cvtc_bwd_kernel<d_f1>")) return r;
   // d_f2: features = f1
   if (int r = of_tc_make_view_map(&tm, f1, C, C, (long long)W * C, (long long)H * W * C, B, H, W, CT_NB, 1, 1, 1)) return r;
   P.from_f2 = 0; P.out = (__nv_bfloat16*)d_f2; P.add = nullptr;
-  cvtc_bwd_kernel<<<grid, CT_THREADS, smem, st>>>(tm, P);
+  OF_CUDA(of_launch_pdl(cvtc_bwd_kernel, dim3(grid), dim3(CT_THREADS), smem, st, tm, P));
   if (int r = of_launch_check("cvtc_bwd_kernel<d_f2>")) return r;
   return 1;
 }
