@@ -10,6 +10,7 @@
 // Index arithmetic follows the reference's op order literally so the int32 tap
 // indices are bit-exact; products/sums use __fmul_rn/__fadd_rn (no FMA
 // contraction) in the reference's accumulate order so fp32 outputs are too.
+#include <stdlib.h>
 #include "common.cuh"
 
 enum { SRC_PTS = 0, SRC_REF_IJ = 1, SRC_XY = 2, SRC_UNFLOW = 3 };
@@ -153,7 +154,12 @@ __device__ __forceinline__ float combine_peers(unsigned peers, int rank, int lan
 }
 
 // G = dtype of the incoming gradient d_out (float, or bf16 on the tensor-core conv path)
-template <typename T, int VEC, int TPP, int SRC, typename G = float>
+// RUN (VEC == 4, C / 4 == TPP): a thread group keeps row i fixed and walks j through the tile; each of its four
+// taps sits in a register slot that accumulates while consecutive pixels hit the SAME destination texel and is
+// flushed (one red.global.add.v4) when the address changes.  Under model.py:65-71's row/column swap every output
+// column j >= H - 1 - flow reads the clamped last row, so ~70 % of a 192 x 640 level's pixels scatter into one row:
+// the run merge turns 4 atomics per pixel there into 4 per 16-pixel run.
+template <typename T, int VEC, int TPP, int SRC, typename G = float, bool RUN = false>
 __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ in,
                                                          const float* __restrict__ coords,
                                                          const G* __restrict__ d_out,
@@ -168,10 +174,14 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
   const int grp = threadIdx.x / TPP;       // pixel slot within the pass
   constexpr int PIX_PER_PASS = 256 / TPP;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    float4 racc[4];                                   // RUN: pending contribution per tap slot
+    size_t raddr[4];
+    bool rvalid[4] = {false, false, false, false};
     for (int p0 = 0; p0 < TILE * TILE; p0 += PIX_PER_PASS) {
       int p = p0 + grp;
       int b, i, j;
-      bool valid = tile_pixel(tile, p, H, W, tiles_x, tiles_y, b, i, j);
+      // RUN walks the tile column by column: pixel p -> (row p % TILE, column p / TILE)
+      bool valid = tile_pixel(tile, RUN ? (p % TILE) * TILE + p / TILE : p, H, W, tiles_x, tiles_y, b, i, j);
       size_t pix = valid ? ((size_t)b * H + i) * W + j : 0;
       float2 c = valid ? __ldg(reinterpret_cast<const float2*>(coords) + pix) : make_float2(0.f, 0.f);
       Taps t = make_taps<SRC>(c.x, c.y, valid ? i : 0, valid ? j : 0, H, W);
@@ -230,10 +240,25 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
                   g.z * (t.ax * (v01.z - v00.z) + t.bx * (v11.z - v10.z)) +
                   g.w * (t.ax * (v01.w - v00.w) + t.bx * (v11.w - v10.w));
             if (d_in != nullptr) {
-              red_add_v4(d_in + o00 + ch, make_float4(w00 * g.x, w00 * g.y, w00 * g.z, w00 * g.w));
-              red_add_v4(d_in + o01 + ch, make_float4(w01 * g.x, w01 * g.y, w01 * g.z, w01 * g.w));
-              red_add_v4(d_in + o10 + ch, make_float4(w10 * g.x, w10 * g.y, w10 * g.z, w10 * g.w));
-              red_add_v4(d_in + o11 + ch, make_float4(w11 * g.x, w11 * g.y, w11 * g.z, w11 * g.w));
+              if (RUN) {
+                const size_t offs[4] = {o00 + ch, o01 + ch, o10 + ch, o11 + ch};
+                const float ws[4] = {w00, w01, w10, w11};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float4 val = make_float4(ws[k] * g.x, ws[k] * g.y, ws[k] * g.z, ws[k] * g.w);
+                  if (rvalid[k] && raddr[k] == offs[k]) {
+                    racc[k].x += val.x; racc[k].y += val.y; racc[k].z += val.z; racc[k].w += val.w;
+                  } else {
+                    if (rvalid[k]) red_add_v4(d_in + raddr[k], racc[k]);
+                    racc[k] = val; raddr[k] = offs[k]; rvalid[k] = true;
+                  }
+                }
+              } else {
+                red_add_v4(d_in + o00 + ch, make_float4(w00 * g.x, w00 * g.y, w00 * g.z, w00 * g.w));
+                red_add_v4(d_in + o01 + ch, make_float4(w01 * g.x, w01 * g.y, w01 * g.z, w01 * g.w));
+                red_add_v4(d_in + o10 + ch, make_float4(w10 * g.x, w10 * g.y, w10 * g.z, w10 * g.w));
+                red_add_v4(d_in + o11 + ch, make_float4(w11 * g.x, w11 * g.y, w11 * g.z, w11 * g.w));
+              }
             }
           } else {
             float g = ld_f<G>(d_out + pix * C + ch);
@@ -258,6 +283,11 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
       if (valid && sub == 0 && d_coords != nullptr) {
         reinterpret_cast<float2*>(d_coords)[pix] = make_float2(d0, d1);
       }
+    }
+    if (RUN) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (rvalid[k]) red_add_v4(d_in + raddr[k], racc[k]);
     }
   }
 }
@@ -293,9 +323,15 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
 #define L(VEC, TPP)                                                                          \
   sample_bwd_kernel<T, VEC, TPP, SRC, G><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
                                                                d_coords, B, H, W, C)
+#define LRUN(TPP)                                                                                    \
+  sample_bwd_kernel<T, 4, TPP, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
+                                                                   d_coords, B, H, W, C)
+  const bool run = SRC == SRC_REF_IJ && d_in != nullptr && !getenv("OF_WARP_NO_RUN");
   if (C % 4 == 0) {
     int cv = C / 4;
-    if (cv >= 32) L(4, 32);
+    if (run && cv == 32) LRUN(32);
+    else if (run && cv == 16) LRUN(16);
+    else if (cv >= 32) L(4, 32);
     else if (cv >= 16) L(4, 16);
     else if (cv >= 8) L(4, 8);
     else if (cv >= 4) L(4, 4);
@@ -307,6 +343,7 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
     L(1, 8);
   }
 #undef L
+#undef LRUN
   return of_launch_check("sample_bwd_kernel");
 }
 
