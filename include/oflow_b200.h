@@ -255,6 +255,14 @@ int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const flo
                    float eps, const float* dw_folded, const float* db_folded, float* dw, float* db, float* dgamma,
                    float* dbeta, int K, int Cout, void* stream);
 
+/* ---- data path ------------------------------------------
+ * data_reader.py:45-64 read_item + :36-41 batch assembly on the device: img1 / img2 = decoded uint8 BGR frames
+ * (src_h, src_w, 3) in device memory; out = the item's (H, W, 6) f32 slice of the batch:
+ * cv2.resize(INTER_LINEAR, bit-exact fixed point) -> / 255 -> minus [123,117,104]/255; flip != 0 swaps the pair
+ * (the np.random.rand() < 0.5 branch of :46-51 is drawn by the caller). */
+int of_preprocess_pair(const uint8_t* img1, const uint8_t* img2, int src_h, int src_w, float* out,
+                       int H, int W, int flip, void* stream);
+
 /* ---- optimiser ------------------------------------------------------------
  * train.py:34,56 tf.keras.optimizers.Adam: p -= lr_t * m / (sqrt(v) + eps),
  * lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t); grad is multiplied by grad_scale

@@ -81,6 +81,7 @@ PROTOTYPES = {
     "of_upscale_flow_bwd": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "of_cost_volume_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_cost_volume_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "of_preprocess_pair": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _i, _vp]),
     "of_flow_head_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_cost_volume_bwd_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_loss_workspace_bytes": (_sz, [_i, _i, _i, _i]),

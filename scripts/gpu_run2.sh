@@ -1,3 +1,1 @@
-timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b1.json 2>gpurun_out/b1.err
-OF_WARP_NO_RUN=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b2.json 2>gpurun_out/b2.err
+timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -6
