@@ -403,6 +403,10 @@ int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int 
     int ppp = 256 / (C / 4);
     size_t blocks = (npix + ppp - 1) / ppp;
     if (blocks > (size_t)OF_NUM_SMS * 8) blocks = (size_t)OF_NUM_SMS * 8;
+    // every CTA ends with C same-address atomics: give each thread >= 32 pixels so they stay a small share
+    size_t cap = npix / ((size_t)ppp * 32);
+    if (cap < 1) cap = 1;
+    if (blocks > cap) blocks = cap;
     if (dtype == OF_F32)
       colsum4_kernel<float><<<(int)blocks, 256, 0, st>>>((const float*)dy, db, npix, C, dy_stride);
     else
