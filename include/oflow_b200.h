@@ -192,6 +192,10 @@ typedef struct {
    * receives 16 bytes per output pixel, bit c = (activated output channel c > 0); a later dgrad passes that
    * buffer as `mask` with mask_dtype = OF_MASK_BITS instead of re-reading the bf16 activation. */
   void* sign_out;
+  /* Split output (3x3 / stride-1, bf16): output columns >= out_split are written to out2 (pixel stride out2_stride,
+   * column - out_split) - the dgrad of a conv whose input is a concat writes each segment's gradient tensor from
+   * ONE launch (model.py:100-104). */
+  void* out2; int out2_stride; int out_split;
 } of_tc_conv;
 #define OF_MASK_BITS 2
 int of_conv_tc_run(const of_tc_conv* c, void* stream);

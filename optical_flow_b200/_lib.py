@@ -37,7 +37,8 @@ class TcConv(C.Structure):
                 ("bias", C.c_void_p), ("act", C.c_int),
                 ("add", C.c_void_p), ("add_dtype", C.c_int), ("add_stride", C.c_int),
                 ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("mask_stride", C.c_int), ("mask_act", C.c_int),
-                ("sign_out", C.c_void_p)]
+                ("sign_out", C.c_void_p),
+                ("out2", C.c_void_p), ("out2_stride", C.c_int), ("out_split", C.c_int)]
 
 
 class TcWgrad(C.Structure):

@@ -57,7 +57,7 @@ def pack_weights(w_hwio, segs, rows, cols, transpose, out=None):
 
 
 def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, sign, out,
-           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE, sign_out=None, mask_bits=None):
+           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE, sign_out=None, mask_bits=None, out2=None, out_split=0):
     d = L.TcConv()
     for k, s in enumerate(sources):
         d.src[k] = s.t.data_ptr()
@@ -79,6 +79,8 @@ def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pa
     if mask_bits is not None:                    # 16 B / pixel sign bits of the producing layer's output
         assert mask is None and mask_bits.dtype == torch.uint8 and mask_bits.shape[-1] == 16
         d.mask, d.mask_dtype, d.mask_stride, d.mask_act = mask_bits.data_ptr(), L.OF_MASK_BITS, 0, mask_act
+    if out2 is not None:
+        d.out2, d.out2_stride, d.out_split = out2.data_ptr(), out2.shape[-1], out_split
     if sign_out is not None:
         assert sign_out.dtype == torch.uint8 and sign_out.shape[-1] == 16
         d.sign_out = sign_out.data_ptr()
@@ -306,6 +308,21 @@ class Bf16Backend:
             # the producer's fprop left a 16 B / pixel sign-bit mask: read that instead of the bf16 activation
             if getattr(chain, "ybits", None) is not None and layer.k == 3 and layer.stride == 1 and not isinstance(x, MultiSource):
                 mask, mask_bits = None, chain.ybits
+        if (isinstance(x, MultiSource) and len(x.sources) == 2 and layer.k == 3 and layer.stride == 1
+                and all(s.t.shape[-1] % 16 == 0 for s in x.sources) and sum(s.t.shape[-1] for s in x.sources) <= 128
+                and not os.environ.get("OF_DGRAD_NO_SPLIT")):
+            # both concat segments from ONE launch: dz is read once, each segment's gradient goes to its own tensor
+            s0, s1 = x.sources
+            n0, n1 = s0.t.shape[-1], s1.t.shape[-1]
+            N = dz.shape[0]
+            H, W = in_hw
+            _, pt, _ = F.same_pad(H, 3, 1)
+            _, pl, _ = F.same_pad(W, 3, 1)
+            wp = pack_weights(w, [(s0.ci0, s0.valid, 0), (s1.ci0, s1.valid, n0)], n0 + n1, _ceil(dz.shape[-1], 64), transpose=True)
+            o0 = torch.empty((N, H, W, n0), dtype=torch.bfloat16, device=dz.device)
+            o1 = torch.empty((N, H, W, n1), dtype=torch.bfloat16, device=dz.device)
+            tc_run([Source(dz)], wp, n0 + n1, n0 + n1, N, H, W, H, W, 3, 3, 1, pt, pl, -1, o0, out2=o1, out_split=n0)
+            return (o0, o1)
         if isinstance(x, MultiSource):
             outs = []
             for s in x.sources:

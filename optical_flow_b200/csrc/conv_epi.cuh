@@ -73,6 +73,7 @@ struct ConvEpi {
   const void* add; int add_dtype; long long add_stride;
   const void* mask; int mask_dtype; long long mask_stride; int mask_act;
   int n_valid;
+  void* out2; long long out2_stride; int split;   // split > 0: output columns >= split go to out2 (column - split)
   void* sign_out;      // nullable: 16 bytes per pixel, bit c = (output channel c > 0) - a later dgrad's activation mask
 };
 #define OF_MASK_BITS 2   // mask_dtype: `mask` is such a sign-bit buffer (conv_tc3 only)
@@ -138,7 +139,9 @@ __device__ __forceinline__ void epilogue_store16(const ConvEpi& E, size_t pix, i
 // aligned full chunk: 16 finished values -> bf16 (2 x 16 B) or f32 (4 x 16 B)
 __device__ __forceinline__ void store16(const ConvEpi& E, size_t pix, int c0, const float (&v)[16]) {
   if (E.out_dtype == OF_BF16) {
-    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(E.out) + pix * E.out_stride + c0;
+    __nv_bfloat16* o = (E.split > 0 && c0 >= E.split)
+                           ? reinterpret_cast<__nv_bfloat16*>(E.out2) + pix * E.out2_stride + (c0 - E.split)
+                           : reinterpret_cast<__nv_bfloat16*>(E.out) + pix * E.out_stride + c0;
     uint32_t pk[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {

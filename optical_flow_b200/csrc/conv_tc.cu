@@ -353,6 +353,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
              "bad packed weight dims / out dtype");
   for (int s = 0; s < c->num_src; ++s) OF_REQUIRE(c->src[s] && c->src_c[s] > 0, OF_ERR_ARG, "bad source %d", s);
   if (int r = of_conv_tc3_try(c, stream)) return r < 0 || r > 1 ? r : 0;    // 3x3 / stride-1 fast path
+  OF_REQUIRE(c->out2 == nullptr, OF_ERR_UNSUPPORTED, "split outputs are a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
   OF_REQUIRE(c->sign_out == nullptr && !(c->mask != nullptr && c->mask_dtype == 2), OF_ERR_UNSUPPORTED,
              "sign-bit activation masks are a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
   OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");

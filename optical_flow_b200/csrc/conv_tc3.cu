@@ -441,6 +441,14 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.E.mask = c->mask; P.E.mask_dtype = c->mask_dtype; P.E.mask_stride = c->mask_stride; P.E.mask_act = c->mask_act;
   P.E.n_valid = c->n_valid;
   P.E.sign_out = c->sign_out;
+  if (c->out2 != nullptr) {
+    OF_REQUIRE(c->out_split > 0 && (c->out_split % 16) == 0 && c->out_split < c->n_valid && (c->n_valid % 16) == 0 &&
+                   c->out_dtype == OF_BF16 && (c->out_stride % 8) == 0 && (c->out2_stride % 8) == 0 &&
+                   (((uintptr_t)c->out | (uintptr_t)c->out2) & 15) == 0 && c->add == nullptr && c->mask == nullptr,
+               OF_ERR_UNSUPPORTED, "split output needs bf16, 16-aligned column split and no add / mask operand");
+    P.E.out2 = c->out2; P.E.out2_stride = c->out2_stride; P.E.split = c->out_split;
+    P.coal = 0;
+  }
 
   CUtensorMap tmA[2], tmB;
   memset(tmA, 0, sizeof(tmA));

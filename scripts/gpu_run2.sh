@@ -1,1 +1,3 @@
-for v in "" "OF_LF_DBG=4" "OF_LF_DBG=5" "OF_LF_DBG=6" "OF_LF_DBG=7" "OF_LF_LEAD=8" "OF_LF_LEAD=2"; do echo "== $v"; env $v python bench.py --workload loss --steps 30 --warmup 5 --no-cpu-baseline 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['ms_per_step']*1e3, d['roofline']['frac'])"; done
+timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -6
+python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b1.json 2>gpurun_out/b1.err
+OF_DGRAD_NO_SPLIT=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b2.json 2>gpurun_out/b2.err

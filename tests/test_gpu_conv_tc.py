@@ -156,6 +156,26 @@ def test_tc3_sign_bit_mask(cuda, cfg):
     assert torch.equal(a, bq)
 
 
+def test_tc_dgrad_split_output_equals_per_segment_launches(cuda):
+    """of_tc_conv.out2 / out_split: both concat segments' gradients from one launch == one launch per segment."""
+    from optical_flow_b200 import conv_tc, functional as F
+    r = np.random.default_rng(8)
+    N, H, W, Cout = 2, 24, 32, 128
+    C0, V1 = 64, 51                                      # features | cost volume + flow (51 of 64 channels real)
+    w = torch.tensor(bf16_round((r.standard_normal((3, 3, C0 + V1, Cout)) / 30).astype(np.float32)), device=cuda)
+    dz = torch.tensor(bf16_round(r.standard_normal((N, H, W, Cout)).astype(np.float32)), device=cuda).bfloat16()
+    a0 = conv_tc.conv2d_dgrad_tc(dz, w, (H, W), 1, seg=(0, C0), out_channels=64)
+    a1 = conv_tc.conv2d_dgrad_tc(dz, w, (H, W), 1, seg=(C0, V1), out_channels=64)
+    wp = conv_tc.pack_weights(w, [(0, C0, 0), (C0, V1, 64)], 128, 128, transpose=True)
+    o0 = torch.empty((N, H, W, 64), dtype=torch.bfloat16, device=cuda)
+    o1 = torch.full((N, H, W, 64), 3.0, dtype=torch.bfloat16, device=cuda)
+    _, pt, _ = F.same_pad(H, 3, 1)
+    _, pl, _ = F.same_pad(W, 3, 1)
+    conv_tc.tc_run([conv_tc.Source(dz)], wp, 128, 128, N, H, W, H, W, 3, 3, 1, pt, pl, -1, o0, out2=o1, out_split=64)
+    assert torch.equal(o0, a0) and torch.equal(o1, a1)
+    assert (o1[..., V1:] == 0).all()                     # padded channels of the second segment get zeros
+
+
 def test_tc_dgrad_segments(cuda):
     """dgrad of the first decoder conv: one launch per concat segment (features | cv+flow)."""
     from optical_flow_b200 import conv_tc
