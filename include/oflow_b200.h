@@ -205,6 +205,16 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream);
 int of_conv_tc_pack_weights(const float* w_hwio, void* packed, int taps, int Cin, int Cout, int rows, int cols,
                             int transpose, int nseg, const int* seg_off, const int* seg_cnt, const int* seg_base,
                             void* stream);
+/* The same packing for many tensors in one launch.  jobs_device: DEVICE array of njobs entries sorted by
+ * block_begin; job j owns blocks [block_begin_j, block_begin_{j+1}) of 2048 output elements each
+ * (ceil(taps*rows*cols / 2048) blocks); total_blocks = their sum. */
+typedef struct {
+  const float* w; void* out;
+  int taps, Cin, Cout, rows, cols, transpose, nseg;
+  int seg_off[3], seg_cnt[3], seg_base[3];
+  int block_begin, reserved;
+} of_pack_job;
+int of_conv_tc_pack_weights_batch(const of_pack_job* jobs_device, int njobs, int total_blocks, void* stream);
 /* dw[tap][ci][co] (f32 HWIO, overwritten) = sum_pix x[pix (+) tap][ci] * dy[pix][co]; x = up to two
  * bf16 NHWC sources (x_valid real channels each, the first mapping to original ci = x_ci0). */
 typedef struct {

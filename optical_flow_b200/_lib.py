@@ -54,9 +54,19 @@ class TcWgrad(C.Structure):
                 ("stride_w", C.c_int), ("stride_h", C.c_int), ("db", C.c_void_p)]
 
 
+class PackJob(C.Structure):
+    """of_pack_job (include/oflow_b200.h)."""
+    _fields_ = [("w", C.c_void_p), ("out", C.c_void_p),
+                ("taps", C.c_int), ("Cin", C.c_int), ("Cout", C.c_int), ("rows", C.c_int), ("cols", C.c_int),
+                ("transpose", C.c_int), ("nseg", C.c_int),
+                ("seg_off", C.c_int * 3), ("seg_cnt", C.c_int * 3), ("seg_base", C.c_int * 3),
+                ("block_begin", C.c_int), ("reserved", C.c_int)]
+
+
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
 PROTOTYPES = {
     "of_conv_tc_run": (C.c_int, [C.POINTER(TcConv), C.c_void_p]),
+    "of_conv_tc_pack_weights_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "of_conv_tc_pack_weights": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                           C.c_void_p]),

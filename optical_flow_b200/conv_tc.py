@@ -42,8 +42,64 @@ def _sources_of(x):
     return x.sources if isinstance(x, MultiSource) else [Source(x)]
 
 
-def pack_weights(w_hwio, segs, rows, cols, transpose, out=None):
+class PackCache:
+    """Weight packings of a whole model, refreshed by ONE launch per step (of_conv_tc_pack_weights_batch).
+
+    The first request for a (weight tensor, layout) packs it on the spot and registers the job; after
+    ``refresh()`` (called once the step's effective weights exist, before the first conv) every registered
+    packing is current and ``get`` returns the persistent buffer without launching anything.  Only meant for
+    weights that live at fixed addresses (the model's parameter / folded-weight buffers)."""
+    BLOCK = 2048
+
+    def __init__(self):
+        self.jobs = {}            # key -> (packed tensor, PackJob fields)
+        self.table = None         # device copy of the job table
+        self.total_blocks = 0
+        self.fresh = False
+
+    def get(self, w_hwio, segs, rows, cols, transpose):
+        key = (w_hwio.data_ptr(), tuple(w_hwio.shape), tuple(tuple(s) for s in segs), rows, cols, bool(transpose))
+        hit = self.jobs.get(key)
+        if hit is not None and self.fresh:
+            return hit[0]
+        if hit is None:
+            out = torch.empty((w_hwio.shape[0] * w_hwio.shape[1], rows, cols), dtype=torch.bfloat16, device=w_hwio.device)
+            self.jobs[key] = (out, w_hwio)            # keeps the source tensor (and so its address) alive
+            self.table = None
+        return pack_weights(w_hwio, segs, rows, cols, transpose, out=self.jobs[key][0])
+
+    def refresh(self):
+        if not self.jobs:
+            return
+        if self.table is None:
+            arr = (L.PackJob * len(self.jobs))()
+            blk = 0
+            for k, (key, (out, w)) in enumerate(self.jobs.items()):
+                _, shape, segs, rows, cols, transpose = key
+                j = arr[k]
+                j.w, j.out = w.data_ptr(), out.data_ptr()
+                j.taps, j.Cin, j.Cout, j.rows, j.cols = shape[0] * shape[1], shape[2], shape[3], rows, cols
+                j.transpose, j.nseg = int(transpose), len(segs)
+                for i, sg in enumerate(segs):
+                    j.seg_off[i], j.seg_cnt[i], j.seg_base[i] = sg
+                j.block_begin = blk
+                blk += (j.taps * rows * cols + self.BLOCK - 1) // self.BLOCK
+            self.total_blocks = blk
+            raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            dev = next(iter(self.jobs.values()))[0].device
+            self.table = raw.to(dev)
+        L.check(L.load().of_conv_tc_pack_weights_batch(L.ptr(self.table), len(self.jobs), self.total_blocks, L.stream_ptr()),
+                "of_conv_tc_pack_weights_batch")
+        self.fresh = True
+
+    def invalidate(self):
+        self.fresh = False
+
+
+def pack_weights(w_hwio, segs, rows, cols, transpose, out=None, cache=None):
     """fp32 HWIO -> bf16 [taps][rows][cols]; segs = [(orig_ci_off, count, packed_base), ...]."""
+    if cache is not None:
+        return cache.get(w_hwio, segs, rows, cols, transpose)
     KH, KW, Cin, Cout = w_hwio.shape
     taps = KH * KW
     if out is None:
@@ -95,7 +151,8 @@ def sign_bits_ok(ksize, stride, cout):
     return ksize == 3 and stride == 1 and 16 <= cout <= 128 and cout % 16 == 0
 
 
-def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None, sign_out=None):
+def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None, sign_out=None,
+                    cache=None):
     """Keras Conv2D(padding='same') forward on tensor cores.  x: bf16 tensor or MultiSource."""
     srcs = _sources_of(x)
     N, H, W = srcs[0].t.shape[:3]
@@ -107,7 +164,7 @@ def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torc
         segs.append((s.ci0, s.valid, kb))
         kb += _ceil(s.t.shape[-1], 64)
     n_mma = _ceil(Cout, 16)
-    wp = pack_weights(w_hwio, segs, n_mma, kb, transpose=False)
+    wp = pack_weights(w_hwio, segs, n_mma, kb, transpose=False, cache=cache)
     out = torch.empty((N, Ho, Wo, Cout), dtype=out_dtype, device=w_hwio.device)
     return tc_run(srcs, wp, n_mma, Cout, N, H, W, Ho, Wo, KH, KW, stride, pt, pl, +1, out, bias=bias, act=act, add=add,
                   sign_out=sign_out)
@@ -122,7 +179,7 @@ def zero_upsample2(dy, H, W):
 
 
 def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloat16, mask=None,
-                    mask_act=L.OF_ACT_NONE, out_channels=None, add=None, mask_bits=None):
+                    mask_act=L.OF_ACT_NONE, out_channels=None, add=None, mask_bits=None, cache=None):
     """dx for input channels [seg[0], seg[0]+seg[1]) (default: all).  dz: bf16 (N,Ho,Wo,Cout).
     stride 2 is handled by zero-insertion of dz followed by the stride-1 kernel."""
     KH, KW, Cin, Cout = w_hwio.shape
@@ -136,7 +193,7 @@ def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloa
     n_out = out_channels or cnt
     n_mma = _ceil(n_out, 16)
     kpad = _ceil(dz.shape[-1], 64)
-    wp = pack_weights(w_hwio, [(ci0, cnt, 0)], n_mma, kpad, transpose=True)
+    wp = pack_weights(w_hwio, [(ci0, cnt, 0)], n_mma, kpad, transpose=True, cache=cache)
     out = torch.empty((N, H, W, n_out), dtype=out_dtype, device=dz.device)
     assert add is None or tuple(add.shape) == tuple(out.shape)
     return tc_run([Source(dz)], wp, n_mma, n_out, N, H, W, H, W, KH, KW, 1, pt, pl, -1, out, mask=mask, mask_act=mask_act,
@@ -244,6 +301,7 @@ class Bf16Backend:
 
     def __init__(self, net):
         self.net = net
+        self.pack_cache = None if os.environ.get("OF_NO_PACK_CACHE") else PackCache()
 
     @staticmethod
     def _tc_ok(layer):
@@ -262,7 +320,8 @@ class Bf16Backend:
         if layer.act != L.OF_ACT_NONE and sign_bits_ok(layer.k, layer.stride, layer.cout) and layer.cin >= 32:
             t0 = x.sources[0].t if isinstance(x, MultiSource) else x
             layer.ybits = torch.empty((t0.shape[0], t0.shape[1], t0.shape[2], 16), dtype=torch.uint8, device=t0.device)
-        return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype, sign_out=layer.ybits)
+        return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype, sign_out=layer.ybits,
+                               cache=self.pack_cache)
 
     def act_bwd(self, layer, y, dy):
         if layer.act == L.OF_ACT_NONE:
@@ -318,7 +377,8 @@ class Bf16Backend:
             H, W = in_hw
             _, pt, _ = F.same_pad(H, 3, 1)
             _, pl, _ = F.same_pad(W, 3, 1)
-            wp = pack_weights(w, [(s0.ci0, s0.valid, 0), (s1.ci0, s1.valid, n0)], n0 + n1, _ceil(dz.shape[-1], 64), transpose=True)
+            wp = pack_weights(w, [(s0.ci0, s0.valid, 0), (s1.ci0, s1.valid, n0)], n0 + n1, _ceil(dz.shape[-1], 64), transpose=True,
+                              cache=self.pack_cache)
             o0 = torch.empty((N, H, W, n0), dtype=torch.bfloat16, device=dz.device)
             o1 = torch.empty((N, H, W, n1), dtype=torch.bfloat16, device=dz.device)
             tc_run([Source(dz)], wp, n0 + n1, n0 + n1, N, H, W, H, W, 3, 3, 1, pt, pl, -1, o0, out2=o1, out_split=n0)
@@ -328,12 +388,13 @@ class Bf16Backend:
             for s in x.sources:
                 n_out = s.t.shape[-1]                    # padded channels of the cv/flow buffer get zeros
                 dt = torch.bfloat16                       # features segment too: summed in fp32 inside concat_bwd
-                outs.append(conv2d_dgrad_tc(dz, w, in_hw, 1, seg=(s.ci0, s.valid), out_dtype=dt, out_channels=n_out))
+                outs.append(conv2d_dgrad_tc(dz, w, in_hw, 1, seg=(s.ci0, s.valid), out_dtype=dt, out_channels=n_out,
+                                            cache=self.pack_cache))
             return tuple(outs)
         assert add is None or self._tc_ok(layer)
         return conv2d_dgrad_tc(dz, w, in_hw, layer.stride, out_dtype=torch.bfloat16, mask=mask,
                                mask_act=mask_act if (mask is not None or mask_bits is not None) else L.OF_ACT_NONE,
-                               add=add, mask_bits=mask_bits)
+                               add=add, mask_bits=mask_bits, cache=self.pack_cache)
 
     # concat [features1, cost_volume, flow_up] (model.py:97-102) as two K-sources
     def concat_fwd(self, fm, f1, f2w, flow_up):

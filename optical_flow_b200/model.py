@@ -76,6 +76,10 @@ class ConvLayer:
         self.x = self.y = None
         self.prev_chain = None         # ConvLayer whose output is exactly this layer's input (sole consumer)
         self.incoming_is_dz = False    # set by a fused dgrad epilogue: dy already multiplied by act'(y)
+        self.weights_ready = False     # FlowNet.prepare_weights() already produced w_eff / b_eff for this step
+        if not hasattr(net, "conv_layers"):
+            net.conv_layers = []
+        net.conv_layers.append(self)
 
     # parameters (views into the flat buffers)
     def _p(self, suffix):
@@ -103,7 +107,9 @@ class ConvLayer:
 
     def forward(self, x):
         self.x = x
-        self.w_eff, self.b_eff = self.effective_weights()
+        if not self.weights_ready:
+            self.w_eff, self.b_eff = self.effective_weights()
+        self.weights_ready = False
         self.y = self.net.backend.fprop(self, x, self.w_eff, self.b_eff)
         return self.y
 
@@ -398,6 +404,7 @@ class FlowNet:
         B, H, W, c6 = batch_imgs.shape
         assert (H, W, c6) == (self.height, self.width, 6) and batch_imgs.dtype == torch.float32
         self.B = B
+        self.prepare_weights()
         x2 = self.backend_split(batch_imgs)                       # (2B, H, W, 3): frame 1s then frame 2s
         enc = self.encoder(x2)
         self.enc_outs = enc
@@ -408,6 +415,18 @@ class FlowNet:
             prev = self.flow_modules[lvl].forward(e[:B], e[B:], prev)
             flows.append(prev)
         return [flows[3], flows[2], flows[1], flows[0]]            # model.py:140
+
+    def prepare_weights(self):
+        """Effective (BN-folded) weights of every conv for this step, then - on back-ends that keep packed copies -
+        all of their tensor-core packings in one launch."""
+        cache = getattr(self.backend, "pack_cache", None)
+        if cache is None:
+            return
+        cache.invalidate()
+        for layer in self.conv_layers:
+            layer.w_eff, layer.b_eff = layer.effective_weights()
+            layer.weights_ready = True
+        cache.refresh()
 
     def backend_split(self, batch_imgs):
         if hasattr(self.backend, "split"):
