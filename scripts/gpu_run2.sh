@@ -1,4 +1,3 @@
-timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -6
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b1.json 2>gpurun_out/b1.err
-OF_NO_PACK_CACHE=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/b2.json 2>gpurun_out/b2.err
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2>&1 || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
+echo ncu rc $?
