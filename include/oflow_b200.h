@@ -277,6 +277,35 @@ int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const flo
 int of_preprocess_pair(const uint8_t* img1, const uint8_t* img2, int src_h, int src_w, float* out,
                        int H, int W, int flip, void* stream);
 
+/* ---- depth / pose re-projection ---------------------------
+ * transformations.py:12-67,133-191.  points are (B,H,W,4) f32 homogeneous, depth (B,H,W,1) f32, pixel
+ * coordinates (B,H,W,2) f32 (x, y) - what of_bilinear_sample_fwd takes; T (B,4,4) f32 row-major on the
+ * device; intrinsics K / Kinv are 9 floats row-major in HOST memory (constructor constants of the layers).
+ * Nullable gradient outputs are skipped; d_T is zeroed by the callee, then reduced over the pixels. */
+/* BackprojectLayer.__call__ :24-30: points = [depth * (Kinv @ [x, y, 1]), 1] */
+int of_backproject_fwd(const float* depth, const float* kinv_host, float* points, int B, int H, int W, void* stream);
+int of_backproject_bwd(const float* d_points, const float* kinv_host, float* d_depth, int B, int H, int W,
+                       void* stream);
+/* ProjectLayer.__call__ :39-44: hom = [K | 0] @ p; pix = hom[:2] / (hom[2] + 1e-7) */
+int of_project_fwd(const float* k_host, const float* points, float* pix, int B, int H, int W, void* stream);
+int of_project_bwd(const float* k_host, const float* points, const float* d_pix, float* d_points, int B, int H,
+                   int W, void* stream);
+/* transform3d :61-67: out[b,i,j] = T[b] @ points[b,i,j] */
+int of_transform3d_fwd(const float* T, const float* points, float* out, int B, int H, int W, void* stream);
+int of_transform3d_bwd(const float* T, const float* points, const float* d_out, float* d_points, float* d_T, int B,
+                       int H, int W, void* stream);
+/* WarpLayer.__call__ :52-58 coordinate chain in one pass: pix = project(transform3d(T, points)); the image
+ * lookup that follows is of_bilinear_sample_fwd/bwd on pix */
+int of_view_coords_fwd(const float* k_host, const float* T, const float* points, float* pix, int B, int H, int W,
+                       void* stream);
+int of_view_coords_bwd(const float* k_host, const float* T, const float* points, const float* d_pix,
+                       float* d_points, float* d_T, int B, int H, int W, void* stream);
+/* make_transformation_matrix :176-191 (+ rotation_from_axisangle :133-173): raw (B,6) = axis-angle, translation
+ * -> (B,4,4); invert != 0 gives the inverse rigid transform */
+int of_make_transformation_matrix_fwd(const float* raw, int invert, float* out, int B, void* stream);
+int of_make_transformation_matrix_bwd(const float* raw, int invert, const float* d_out, float* d_raw, int B,
+                                      void* stream);
+
 /* ---- optimiser ------------------------------------------------------------
  * train.py:34,56 tf.keras.optimizers.Adam: p -= lr_t * m / (sqrt(v) + eps),
  * lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t); grad is multiplied by grad_scale

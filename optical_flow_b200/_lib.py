@@ -22,6 +22,7 @@ OF_ACT_NONE, OF_ACT_RELU, OF_ACT_LEAKY = 0, 1, 2
 _vp, _i, _sz, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_float
 _pp = C.POINTER(C.c_void_p)
 _ip = C.POINTER(C.c_int)
+_fp9 = C.POINTER(C.c_float)   # 9 host floats (row-major 3x3 intrinsics)
 
 class TcConv(C.Structure):
     """of_tc_conv (include/oflow_b200.h)."""
@@ -111,6 +112,16 @@ PROTOTYPES = {
     "of_copy_channels": (_i, [_vp, _i, _vp, _i, _i, _sz, _i, _i, _i, _vp]),
     "of_bn_fold_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _i, _vp]),
     "of_bn_fold_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "of_backproject_fwd": (_i, [_vp, _fp9, _vp, _i, _i, _i, _vp]),
+    "of_backproject_bwd": (_i, [_vp, _fp9, _vp, _i, _i, _i, _vp]),
+    "of_project_fwd": (_i, [_fp9, _vp, _vp, _i, _i, _i, _vp]),
+    "of_project_bwd": (_i, [_fp9, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "of_transform3d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "of_transform3d_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "of_view_coords_fwd": (_i, [_fp9, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "of_view_coords_bwd": (_i, [_fp9, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "of_make_transformation_matrix_fwd": (_i, [_vp, _i, _vp, _i, _vp]),
+    "of_make_transformation_matrix_bwd": (_i, [_vp, _i, _vp, _vp, _i, _vp]),
     "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
     "of_comm_unique_id": (_i, [_vp]),
     "of_comm_init": (_i, [_vp, _i, _i, _pp]),
@@ -177,6 +188,14 @@ def ptr_array(tensors):
     for k, t in enumerate(tensors):
         arr[k] = ptr(t)
     return arr
+
+
+def mat3_host(m):
+    """3x3 intrinsics (numpy / nested lists / CPU tensor) -> 9 host floats, row-major."""
+    import numpy as np
+    a = np.ascontiguousarray(np.asarray(m, dtype=np.float32)).reshape(-1)
+    assert a.size == 9, "intrinsics matrix must be (3, 3)"
+    return (C.c_float * 9)(*[float(v) for v in a])
 
 
 def int_array(vals):

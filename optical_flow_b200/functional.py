@@ -305,3 +305,114 @@ def adam_step(param, grad, m, v, step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-7
     L.check(L.load().of_adam_step(L.ptr(param), L.ptr(grad), L.ptr(m), L.ptr(v), param.numel(), int(step),
                                   float(lr), float(beta1), float(beta2), float(eps), float(grad_scale),
                                   L.stream_ptr()), "of_adam_step")
+
+
+# ------------------------------------------- depth / pose re-projection (8f rank 3) --
+
+def _f32(shape, like):
+    return torch.empty(shape, dtype=torch.float32, device=like.device)
+
+
+def backproject_fwd(depth, kinv):
+    """transformations.py:24-30; depth (B,h,w,1) -> points3d_hom (B,h,w,4)."""
+    B, H, W, one = depth.shape
+    assert one == 1 and depth.dtype == torch.float32
+    out = _f32((B, H, W, 4), depth)
+    L.check(L.load().of_backproject_fwd(L.ptr(depth), L.mat3_host(kinv), L.ptr(out), B, H, W, L.stream_ptr()),
+            "of_backproject_fwd")
+    return out
+
+
+def backproject_bwd(d_points, kinv):
+    B, H, W, four = d_points.shape
+    assert four == 4 and d_points.dtype == torch.float32
+    d_depth = _f32((B, H, W, 1), d_points)
+    L.check(L.load().of_backproject_bwd(L.ptr(d_points), L.mat3_host(kinv), L.ptr(d_depth), B, H, W, L.stream_ptr()),
+            "of_backproject_bwd")
+    return d_depth
+
+
+def project_fwd(points, k):
+    """transformations.py:39-44; points3d_hom (B,h,w,4) -> pixel_coords (B,h,w,2)."""
+    B, H, W, four = points.shape
+    assert four == 4 and points.dtype == torch.float32
+    pix = _f32((B, H, W, 2), points)
+    L.check(L.load().of_project_fwd(L.mat3_host(k), L.ptr(points), L.ptr(pix), B, H, W, L.stream_ptr()),
+            "of_project_fwd")
+    return pix
+
+
+def project_bwd(points, k, d_pix):
+    B, H, W, _ = points.shape
+    assert tuple(d_pix.shape) == (B, H, W, 2) and d_pix.dtype == torch.float32
+    d_points = _f32((B, H, W, 4), points)
+    L.check(L.load().of_project_bwd(L.mat3_host(k), L.ptr(points), L.ptr(d_pix), L.ptr(d_points), B, H, W,
+                                    L.stream_ptr()), "of_project_bwd")
+    return d_points
+
+
+def _check_T(T, B):
+    assert T.dtype == torch.float32 and tuple(T.shape) == (B, 4, 4), "T must be (batch_size, 4, 4) float32"
+
+
+def transform3d_fwd(T, points):
+    """transformations.py:61-67."""
+    B, H, W, four = points.shape
+    assert four == 4 and points.dtype == torch.float32
+    _check_T(T, B)
+    out = torch.empty_like(points)
+    L.check(L.load().of_transform3d_fwd(L.ptr(T), L.ptr(points), L.ptr(out), B, H, W, L.stream_ptr()),
+            "of_transform3d_fwd")
+    return out
+
+
+def transform3d_bwd(T, points, d_out, need_points_grad=True, need_T_grad=True):
+    B, H, W, _ = points.shape
+    _check_T(T, B)
+    assert tuple(d_out.shape) == tuple(points.shape) and d_out.dtype == torch.float32
+    d_points = torch.empty_like(points) if need_points_grad else None
+    d_T = _f32((B, 4, 4), points) if need_T_grad else None
+    L.check(L.load().of_transform3d_bwd(L.ptr(T), L.ptr(points), L.ptr(d_out), L.ptr(d_points), L.ptr(d_T), B, H, W,
+                                        L.stream_ptr()), "of_transform3d_bwd")
+    return d_points, d_T
+
+
+def view_coords_fwd(k, T, points):
+    """transformations.py:56-57 (transform3d + ProjectLayer) in one pass."""
+    B, H, W, four = points.shape
+    assert four == 4 and points.dtype == torch.float32
+    _check_T(T, B)
+    pix = _f32((B, H, W, 2), points)
+    L.check(L.load().of_view_coords_fwd(L.mat3_host(k), L.ptr(T), L.ptr(points), L.ptr(pix), B, H, W,
+                                        L.stream_ptr()), "of_view_coords_fwd")
+    return pix
+
+
+def view_coords_bwd(k, T, points, d_pix, need_points_grad=True, need_T_grad=True):
+    B, H, W, _ = points.shape
+    _check_T(T, B)
+    assert tuple(d_pix.shape) == (B, H, W, 2) and d_pix.dtype == torch.float32
+    d_points = torch.empty_like(points) if need_points_grad else None
+    d_T = _f32((B, 4, 4), points) if need_T_grad else None
+    L.check(L.load().of_view_coords_bwd(L.mat3_host(k), L.ptr(T), L.ptr(points), L.ptr(d_pix), L.ptr(d_points),
+                                        L.ptr(d_T), B, H, W, L.stream_ptr()), "of_view_coords_bwd")
+    return d_points, d_T
+
+
+def make_transformation_matrix_fwd(raw, invert):
+    """transformations.py:176-191."""
+    B, six = raw.shape
+    assert six == 6 and raw.dtype == torch.float32
+    out = _f32((B, 4, 4), raw)
+    L.check(L.load().of_make_transformation_matrix_fwd(L.ptr(raw), int(bool(invert)), L.ptr(out), B, L.stream_ptr()),
+            "of_make_transformation_matrix_fwd")
+    return out
+
+
+def make_transformation_matrix_bwd(raw, invert, d_out):
+    B, _ = raw.shape
+    assert tuple(d_out.shape) == (B, 4, 4) and d_out.dtype == torch.float32
+    d_raw = torch.empty_like(raw)
+    L.check(L.load().of_make_transformation_matrix_bwd(L.ptr(raw), int(bool(invert)), L.ptr(d_out), L.ptr(d_raw), B,
+                                                       L.stream_ptr()), "of_make_transformation_matrix_bwd")
+    return d_raw

@@ -148,7 +148,7 @@ def stack(xs, axis=0):
 
 
 def concat(xs, axis):
-    return torch.cat(list(xs), dim=axis)
+    return torch.cat([_t(x) for x in xs], dim=axis)
 
 
 def transpose(x, perm=None):
@@ -189,8 +189,8 @@ def add_n(xs):
     return out
 
 
-def norm(x, axis=None):
-    return torch.linalg.norm(x) if axis is None else torch.linalg.norm(x, dim=axis)
+def norm(x, axis=None, keepdims=False):
+    return torch.linalg.norm(x) if axis is None else torch.linalg.norm(x, dim=axis, keepdim=keepdims)
 
 
 def argmax(x, axis=None):
@@ -208,7 +208,7 @@ math = _Math()
 
 
 class _Linalg:
-    matvec = staticmethod(lambda a, b: torch.matmul(a, b.unsqueeze(-1)).squeeze(-1))
+    matvec = staticmethod(lambda a, b: torch.matmul(_t(a), _t(b).unsqueeze(-1)).squeeze(-1))
 
 
 linalg = _Linalg()
