@@ -10,7 +10,7 @@
 // decoder concat), all Cout columns, a group of taps (one TMEM accumulator per tap: the dy
 // tile is loaded once per K step and reused by every tap) and a slice of the pixel range
 // (split-K).  Partial results are reduced into dW with red.global.add.f32.
-// Bias gradient (db[co] = sum_pix dy[pix][co]) rides along: the CTAs of job 0 issue one more MMA group
+// Bias gradient (db[co] = sum_pix dy[pix][co]) rides along: one job per pixel range (rotating) issues one more MMA group
 // per K step whose A operand is a constant all-ones tile, into a spare TMEM accumulator - the dy tile
 // is already in shared memory, so the separate column-sum pass over dy (1.25 ms / step) disappears.
 #include "common.cuh"
@@ -34,7 +34,7 @@ struct WgradParams {
   int chunk_c0[WG_MAX_CHUNKS];    // channel coordinate inside that tensor
   int chunk_ci[WG_MAX_CHUNKS];    // original ci of the chunk's first channel
   int chunk_cnt[WG_MAX_CHUNKS];   // valid channels in the chunk
-  // job (blockIdx.y) = (M tile, tap group)
+  // job (blockIdx.x) = (M tile, tap group)
   int job_mt[WG_MAX_JOBS], job_tap0[WG_MAX_JOBS], job_ntaps[WG_MAX_JOBS];
   int KW, pad_t, pad_l, stride_w, stride_h;
   int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
@@ -43,7 +43,7 @@ struct WgradParams {
   int Cin, Cout;
   int stages, stage_bytes, tmem_cols;
   float* dw;
-  float* db;                      // nullable: fused bias gradient (job 0 only)
+  float* db;                      // nullable: fused bias gradient (one job per pixel range)
   // Cin <= 64 (one chunk): the two 64-row halves of an accumulator hold two different TAPS of that chunk
   // instead of two channel chunks - no zero half, half the MMAs.  job_tap0 / job_ntaps then count accumulators.
   int pack2, taps;
@@ -51,6 +51,11 @@ struct WgradParams {
   // {64, TW, TH + 2} per chunk (the "slab") serves its three kh taps as descriptors at row offsets
   // kh * TW * 128 B (multiples of the 1024-byte swizzle atom) - half the L2 -> SM bytes of tap-by-tap loads.
   int slab, slab_bytes;
+  // 3x3 / stride 1 with Cin <= 64: pack2 fed from THREE slabs (one per kw, all in one CTA) instead of ten
+  // tap-by-tap boxes - half the L2 -> SM bytes per K step.  Accumulators: t = 0..2 pair (kh 0, kh 1) of kw = t
+  // (halves TW rows apart inside a slab), t = 3 pairs kh 2 of kw 0 / kw 1 (halves one slab apart), t = 4 holds
+  // kh 2 of kw 2 in its lower half (the upper half multiplies whatever follows in the stage and is discarded).
+  int slab2;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -71,7 +76,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     tc::fence_barrier_init();
   }
   if (warp == 4 && lane == 0) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
-  const bool do_bias = P.db != nullptr && blockIdx.y == 0;
+  // the bias gradient of a pixel range is computed by ONE of its jobs, rotating so the extra MMAs spread over the SMs
+  const bool do_bias = P.db != nullptr && blockIdx.x == (blockIdx.y % gridDim.x);
   if (do_bias) {
     // bf16 1.0 = 0x3f80; all-ones is invariant under the 128-byte swizzle
     for (int i = threadIdx.x; i < WG_ONES_BYTES / 16; i += WG_THREADS)
@@ -86,11 +92,13 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   tc::fence_after_sync();
   const uint32_t tmem_base = *tmem_base_slot;
 
-  const int job = blockIdx.y;
+  // job is the FAST grid index: the CTAs that walk the same pixel range (one per tap group / M tile) are
+  // scheduled together, so x and dy come from HBM once and from L2 for the other jobs
+  const int job = blockIdx.x;
   const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
-  const int k_begin = blockIdx.x * P.ktiles_per_split;
+  const int k_begin = blockIdx.y * P.ktiles_per_split;
   const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
-  const int a_bytes = P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
+  const int a_bytes = P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
   const int tx_bytes = a_bytes + P.n_chunks * WG_CHUNK_BYTES;
 
   if (warp == 4) {
@@ -103,7 +111,11 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         tc::mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
-        if (P.slab) {
+        if (P.slab2) {
+          for (int kw = 0; kw < 3; ++kw)
+            tc::tma_load_4d(base + (size_t)kw * P.slab_bytes, &tmX0, &full_bar[stage], P.chunk_c0[0],
+                            w0 + kw - P.pad_l, h0 - P.pad_t, n);
+        } else if (P.slab) {
           for (int c = 0; c < 2; ++c) {
             const int cm = P.chunk_map[mt * 2 + c];
             const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
@@ -138,9 +150,16 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         tc::fence_after_sync();
         uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
         uint32_t b_addr = base + (uint32_t)a_bytes;
+        // tap outermost: the K slices of one accumulator back to back (interleaving the accumulators was 14 % slower)
         for (int t = 0; t < ntaps; ++t) {
           uint32_t a_addr = P.slab ? base + (uint32_t)(t * P.TW * 128) : base + (uint32_t)(t * 2 * WG_CHUNK_BYTES);
-          const uint32_t a_lbo = P.slab ? (uint32_t)P.slab_bytes : (uint32_t)WG_CHUNK_BYTES;
+          uint32_t a_lbo = P.slab ? (uint32_t)P.slab_bytes : (uint32_t)WG_CHUNK_BYTES;
+          if (P.slab2) {
+            const uint32_t row = (uint32_t)(P.TW * 128);
+            if (t < 3) { a_addr = base + (uint32_t)(t * P.slab_bytes); a_lbo = row; }
+            else if (t == 3) { a_addr = base + 2 * row; a_lbo = (uint32_t)P.slab_bytes; }
+            else { a_addr = base + (uint32_t)(2 * P.slab_bytes) + 2 * row; a_lbo = row; }
+          }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             // 16 pixels (K) per MMA = 16 rows of 128 B = 2048 B
@@ -174,7 +193,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       int ci = P.chunk_ci[c] + rc;
       const bool vec4 = (P.Cout % 4) == 0;
       for (int t = 0; t < ntaps; ++t) {
-        const int tap = P.slab ? t * P.KW + tap0 : P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
+        int tap = P.slab ? t * P.KW + tap0 : P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
+        if (P.slab2) tap = t < 3 ? (row >> 6) * 3 + t : t == 3 ? 6 + (row >> 6) : 8 + (row >> 6);
         const bool valid = row_ok && tap < P.taps;
         float* dst_row = P.dw + ((size_t)(valid ? tap : 0) * P.Cin + (valid ? ci : 0)) * P.Cout;
         uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * P.n_mma);
@@ -274,6 +294,10 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
                ? 1 : 0;
   P.slab_bytes = (P.TH + 2) * P.TW * 128;
   if (P.slab) { tpp = 3; passes = 3; }
+  P.slab2 = (x_chunks == 1 && !getenv("OF_WG_NO_PACK2") && c->KH == 3 && c->KW == 3 && P.stride_w == 1 &&
+             P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && (5 + (c->db ? 1 : 0)) * P.n_mma <= 512 &&
+             !getenv("OF_WG_NO_SLAB2"))
+                ? 1 : 0;
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
   for (int s = 0; s < c->num_src; ++s) {
@@ -281,7 +305,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
     long long hs_ = view ? c->view_h_stride : (long long)c->W * c->x_stride[s];
     long long ns_ = view ? c->view_n_stride : (long long)c->H * c->W * c->x_stride[s];
     if (int r = of_tc_make_view_map(&tmX[s], c->x[s], c->x_c[s], ws_, hs_, ns_, c->N, c->H, c->W, P.TW,
-                                    P.slab ? P.TH + 2 : P.TH, P.stride_w, P.stride_h))
+                                    (P.slab || P.slab2) ? P.TH + 2 : P.TH, P.stride_w, P.stride_h))
       return r;
   }
   if (c->num_src == 1) tmX[1] = tmX[0];
@@ -314,6 +338,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
     passes = (units + tpp - 1) / tpp;
     tpp = (units + passes - 1) / passes;
   }
+  if (P.slab2) { tpp = 5; passes = 1; }
   int m_tiles = (nch + 1) / 2;
   int jobs = 0;
   for (int mt = 0; mt < m_tiles; ++mt)
@@ -325,19 +350,23 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
       P.job_mt[jobs] = mt; P.job_tap0[jobs] = t0; P.job_ntaps[jobs] = nt;
       ++jobs;
     }
-  int splits = (2 * OF_NUM_SMS + jobs - 1) / jobs;   // ~2 waves so uneven jobs balance
+  // ONE wave of one CTA per SM (never round up: 99 x 3 = 297 CTAs leaves one CTA for a wave of its own); a second
+  // wave only repeats the prologue and doubles the split-K atomics (measured 3-15 % slower)
+  int splits = OF_NUM_SMS / jobs;
+  if (const char* e = getenv("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
   if (splits > P.ktiles) splits = P.ktiles;
   if (splits < 1) splits = 1;
   P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
-  P.stage_bytes = (P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) + P.n_chunks * WG_CHUNK_BYTES;
+  P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
+                  P.n_chunks * WG_CHUNK_BYTES;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
-  dim3 grid(splits, jobs);
+  dim3 grid(jobs, splits);
   OF_CUDA(of_launch_pdl(conv_tc_wgrad_kernel, grid, dim3(WG_THREADS), smem, st, tmX[0], tmX[1], tmDY, P));
   if (int r = of_launch_check("conv_tc_wgrad_kernel")) return r;
   return 0;

@@ -204,6 +204,8 @@ WGRAD_CASES = [
     (1, 8, 16, 256, 3, 256, 1),
     (1, 16, 16, 96, 3, 64, 1),
     (2, 96, 128, 128, 3, 128, 1),    # long pixel reduction, several split-K slices
+    (1, 20, 40, 32, 3, 64, 1),       # Cin < 64, 8 x 8 pixel tiles: three-slab pack2 with zero-filled channels
+    (2, 12, 64, 64, 3, 16, 1),       # 32 x 2 pixel tiles, narrow Cout
 ]
 
 
