@@ -56,6 +56,13 @@ struct WgradParams {
   // (halves TW rows apart inside a slab), t = 3 pairs kh 2 of kw 0 / kw 1 (halves one slab apart), t = 4 holds
   // kh 2 of kw 2 in its lower half (the upper half multiplies whatever follows in the stage and is discarded).
   int slab2;
+  // 3x3 / stride 1 with Cout <= 64 ("N-stacked"): shift dy instead of x along kh.  dW[kh][kw] = sum_q x[q + (0, kw-1)]
+  // * dy[q - (kh-1, 0)] (x is zero outside the image, so q over the image rows is complete): the B operand is ONE dy
+  // slab {64, TW, TH + 2} whose three kh-shifted views are the three 64-column chunks of an N = 192 MMA (chunk j at
+  // +j rows = kh 2 - j), the A operand x boxes without halo.  A third of the MMA instructions, each 3x wider - these
+  // narrow layers are bound by the per-instruction cost, not by the math.  Cin <= 64: one job, accumulators
+  // (kw0 | kw1) and (kw2 | junk); otherwise a job is (M tile, kw) with one accumulator.
+  int nstack, nstack_one;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -98,8 +105,9 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
   const int k_begin = blockIdx.y * P.ktiles_per_split;
   const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
-  const int a_bytes = P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
-  const int tx_bytes = a_bytes + P.n_chunks * WG_CHUNK_BYTES;
+  const int a_bytes = P.nstack ? (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES
+                      : P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
+  const int tx_bytes = a_bytes + (P.nstack ? P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
 
   if (warp == 4) {
     if (lane == 0) {
@@ -111,6 +119,19 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         tc::mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
+        if (P.nstack) {
+          for (int c = 0; c < (P.nstack_one ? 3 : 2); ++c) {
+            const int chunk = P.nstack_one ? 0 : mt * 2 + c;
+            const int kw = P.nstack_one ? c : tap0;
+            const int cm = P.chunk_map[chunk];
+            const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
+            int cc = cm < 0 ? (1 << 20) : P.chunk_c0[chunk];
+            tc::tma_load_4d(base + (size_t)c * WG_CHUNK_BYTES, tm, &full_bar[stage], cc, w0 + kw - P.pad_l, h0, n);
+          }
+          tc::tma_load_4d(base + a_bytes, &tmDY, &full_bar[stage], 0, w0, h0 - 1, n);
+          if (++stage == P.stages) { stage = 0; phase ^= 1; }
+          continue;
+        }
         if (P.slab2) {
           for (int kw = 0; kw < 3; ++kw)
             tc::tma_load_4d(base + (size_t)kw * P.slab_bytes, &tmX0, &full_bar[stage], P.chunk_c0[0],
@@ -150,6 +171,30 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         tc::fence_after_sync();
         uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
         uint32_t b_addr = base + (uint32_t)a_bytes;
+        if (P.nstack) {
+          const uint32_t idesc_n = tc::idesc_bf16_f32(128, 192, 1, 1);
+          const uint32_t row = (uint32_t)(P.TW * 128);
+          for (int a = 0; a < ntaps; ++a) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              uint64_t adesc = tc::desc_sw128_mnmajor(base + (uint32_t)(a * 2 * WG_CHUNK_BYTES) + k * 2048, WG_CHUNK_BYTES);
+              uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, row);
+              tc::mma_bf16(tmem_base + (uint32_t)(a * 192), adesc, bdesc, idesc_n, (kt > k_begin || k > 0) ? 1u : 0u);
+            }
+          }
+          if (do_bias) {
+            const uint32_t idesc_b = tc::idesc_bf16_f32(128, 64, 1, 1);
+            const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + row + k * 2048, WG_CHUNK_BYTES);   // kh = 1: dy unshifted
+              tc::mma_bf16(tmem_base + (uint32_t)(ntaps * 192), odesc, bdesc, idesc_b, (kt > k_begin || k > 0) ? 1u : 0u);
+            }
+          }
+          tc::mma_commit(&empty_bar[stage]);
+          if (++stage == P.stages) { stage = 0; phase ^= 1; }
+          continue;
+        }
         // tap outermost: the K slices of one accumulator back to back (interleaving the accumulators was 14 % slower)
         for (int t = 0; t < ntaps; ++t) {
           uint32_t a_addr = P.slab ? base + (uint32_t)(t * P.TW * 128) : base + (uint32_t)(t * 2 * WG_CHUNK_BYTES);
@@ -188,11 +233,42 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       tc::mbar_wait(acc_full, 0);
       tc::fence_after_sync();
       int row = warp * 32 + lane;
+      if (P.nstack) {
+        const int chunk = P.nstack_one ? 0 : mt * 2 + (row >> 6), rcn = row & 63;
+        const bool rok = P.chunk_map[chunk] >= 0 && rcn < P.chunk_cnt[chunk];
+        const int cin = P.chunk_ci[chunk] + rcn;
+        for (int a = 0; a < ntaps; ++a) {
+          const int kw = P.nstack_one ? 2 * a + (row >> 6) : tap0;
+          const bool valid = rok && kw < 3;
+          const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * 192);
+          for (int c0 = 0; c0 < 192; c0 += 16) {
+            const int kh = 2 - (c0 >> 6), co0 = c0 & 63;
+            if (co0 >= P.n_valid) continue;                       // warp-uniform
+            __syncwarp();
+            uint32_t rr[16];
+            tc::tmem_ld16(taddr + (uint32_t)c0, rr);
+            tc::tmem_ld_wait();
+            if (!valid) continue;
+            float* dst = P.dw + ((size_t)(kh * 3 + kw) * P.Cin + cin) * P.Cout + co0;
+            const int nv = min(16, P.n_valid - co0);
+            if ((P.Cout % 4) == 0 && nv == 16) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                red_add_v4(dst + 4 * j, make_float4(__uint_as_float(rr[4 * j]), __uint_as_float(rr[4 * j + 1]),
+                                                    __uint_as_float(rr[4 * j + 2]), __uint_as_float(rr[4 * j + 3])));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < nv) red_add(dst + j, __uint_as_float(rr[j]));
+            }
+          }
+        }
+      }
       const int c = P.pack2 ? 0 : mt * 2 + (row >> 6), rc = row & 63;
       const bool row_ok = P.chunk_map[c] >= 0 && rc < P.chunk_cnt[c];
       int ci = P.chunk_ci[c] + rc;
       const bool vec4 = (P.Cout % 4) == 0;
-      for (int t = 0; t < ntaps; ++t) {
+      for (int t = 0; t < (P.nstack ? 0 : ntaps); ++t) {
         int tap = P.slab ? t * P.KW + tap0 : P.pack2 ? 2 * (tap0 + t) + (row >> 6) : tap0 + t;
         if (P.slab2) tap = t < 3 ? (row >> 6) * 3 + t : t == 3 ? 6 + (row >> 6) : 8 + (row >> 6);
         const bool valid = row_ok && tap < P.taps;
@@ -221,7 +297,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       }
       if (do_bias && warp == 0) {
         // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
-        uint32_t taddr = tmem_base + (uint32_t)(ntaps * P.n_mma);
+        uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? 192 : P.n_mma));
         for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
           __syncwarp();
           uint32_t rr[16];
@@ -298,6 +374,11 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
              P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && (5 + (c->db ? 1 : 0)) * P.n_mma <= 512 &&
              !getenv("OF_WG_NO_SLAB2"))
                 ? 1 : 0;
+  P.nstack = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view && P.n_chunks == 1 &&
+              P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_NSTACK"))
+                 ? 1 : 0;
+  P.nstack_one = (P.nstack && x_chunks == 1) ? 1 : 0;
+  if (P.nstack) { P.slab = 0; P.slab2 = 0; }
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
   for (int s = 0; s < c->num_src; ++s) {
@@ -309,7 +390,9 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
       return r;
   }
   if (c->num_src == 1) tmX[1] = tmX[0];
-  if (int r = of_tc_make_act_map(&tmDY, c->dy, c->dy_c, c->dy_stride, c->N, c->Ho, c->Wo, P.TW, P.TH, 1)) return r;
+  if (int r = of_tc_make_act_map(&tmDY, c->dy, c->dy_c, c->dy_stride, c->N, c->Ho, c->Wo, P.TW,
+                                 P.nstack ? P.TH + 2 : P.TH, 1))
+    return r;
 
   // list of 64-channel chunks over the sources (original ci offsets follow the concat order)
   int nch = 0;
@@ -329,7 +412,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
     attr_set = true;
   }
   P.taps = taps;
-  P.pack2 = (nch == 1 && taps > 1 && !getenv("OF_WG_NO_PACK2")) ? 1 : 0;
+  P.pack2 = (nch == 1 && taps > 1 && !P.nstack && !getenv("OF_WG_NO_PACK2")) ? 1 : 0;
   const int units = P.pack2 ? (taps + 1) / 2 : taps;       // accumulators needed per M tile
   if (P.pack2) {
     tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
@@ -341,6 +424,15 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (P.slab2) { tpp = 5; passes = 1; }
   int m_tiles = (nch + 1) / 2;
   int jobs = 0;
+  if (P.nstack) {
+    tpp = P.nstack_one ? 2 : 1;
+    for (int mt = 0; mt < m_tiles; ++mt)
+      for (int kw = 0; kw < (P.nstack_one ? 1 : 3); ++kw) {
+        OF_REQUIRE(jobs < WG_MAX_JOBS, OF_ERR_SHAPE, "too many wgrad jobs");
+        P.job_mt[jobs] = mt; P.job_tap0[jobs] = kw; P.job_ntaps[jobs] = tpp;
+        ++jobs;
+      }
+  } else
   for (int mt = 0; mt < m_tiles; ++mt)
     for (int p = 0; p < passes; ++p) {
       int t0 = P.slab ? p : p * tpp;                  // slab: the job's kw; its three taps are kh = 0..2
@@ -360,10 +452,12 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
+  if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.slab_bytes;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
+  if (P.nstack) cols = tpp * 192 + (c->db ? 64 : 0);
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
   dim3 grid(jobs, splits);

@@ -206,6 +206,7 @@ WGRAD_CASES = [
     (2, 96, 128, 128, 3, 128, 1),    # long pixel reduction, several split-K slices
     (1, 20, 40, 32, 3, 64, 1),       # Cin < 64, 8 x 8 pixel tiles: three-slab pack2 with zero-filled channels
     (2, 12, 64, 64, 3, 16, 1),       # 32 x 2 pixel tiles, narrow Cout
+    (1, 10, 24, 160, 3, 48, 1),      # N-stacked mode with three input chunks (second M tile half empty)
 ]
 
 
