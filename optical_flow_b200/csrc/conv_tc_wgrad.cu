@@ -56,12 +56,13 @@ struct WgradParams {
   // (halves TW rows apart inside a slab), t = 3 pairs kh 2 of kw 0 / kw 1 (halves one slab apart), t = 4 holds
   // kh 2 of kw 2 in its lower half (the upper half multiplies whatever follows in the stage and is discarded).
   int slab2;
-  // 3x3 / stride 1 with Cout <= 64 ("N-stacked"): shift dy instead of x along kh.  dW[kh][kw] = sum_q x[q + (0, kw-1)]
+  // 3x3 / stride 1 with Cout <= 128 ("N-stacked"): shift dy instead of x along kh.  dW[kh][kw] = sum_q x[q + (0, kw-1)]
   // * dy[q - (kh-1, 0)] (x is zero outside the image, so q over the image rows is complete): the B operand is ONE dy
   // slab {64, TW, TH + 2} whose three kh-shifted views are the three 64-column chunks of an N = 192 MMA (chunk j at
   // +j rows = kh 2 - j), the A operand x boxes without halo.  A third of the MMA instructions, each 3x wider - these
   // narrow layers are bound by the per-instruction cost, not by the math.  Cin <= 64: one job, accumulators
-  // (kw0 | kw1) and (kw2 | junk); otherwise a job is (M tile, kw) with one accumulator.
+  // (kw0 | kw1) and (kw2 | junk); otherwise a job is (M tile, kw) with one accumulator per 64-column dy chunk
+  // (Cout 96 / 128: two dy slabs, two N = 192 MMAs per K slice instead of three N = Cout ones: -12..15 %).
   int nstack, nstack_one;
 };
 
@@ -107,7 +108,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
   const int a_bytes = P.nstack ? (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES
                       : P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
-  const int tx_bytes = a_bytes + (P.nstack ? P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
+  const int tx_bytes = a_bytes + (P.nstack ? P.n_chunks * P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
 
   if (warp == 4) {
     if (lane == 0) {
@@ -128,7 +129,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             int cc = cm < 0 ? (1 << 20) : P.chunk_c0[chunk];
             tc::tma_load_4d(base + (size_t)c * WG_CHUNK_BYTES, tm, &full_bar[stage], cc, w0 + kw - P.pad_l, h0, n);
           }
-          tc::tma_load_4d(base + a_bytes, &tmDY, &full_bar[stage], 0, w0, h0 - 1, n);
+          for (int c = 0; c < P.n_chunks; ++c)
+            tc::tma_load_4d(base + a_bytes + (size_t)c * P.slab_bytes, &tmDY, &full_bar[stage], c * 64, w0, h0 - 1, n);
           if (++stage == P.stages) { stage = 0; phase ^= 1; }
           continue;
         }
@@ -174,21 +176,25 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         if (P.nstack) {
           const uint32_t idesc_n = tc::idesc_bf16_f32(128, 192, 1, 1);
           const uint32_t row = (uint32_t)(P.TW * 128);
-          for (int a = 0; a < ntaps; ++a) {
+          for (int a = 0; a < ntaps; ++a)
+            for (int c = 0; c < P.n_chunks; ++c) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              uint64_t adesc = tc::desc_sw128_mnmajor(base + (uint32_t)(a * 2 * WG_CHUNK_BYTES) + k * 2048, WG_CHUNK_BYTES);
-              uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, row);
-              tc::mma_bf16(tmem_base + (uint32_t)(a * 192), adesc, bdesc, idesc_n, (kt > k_begin || k > 0) ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) {
+                uint64_t adesc = tc::desc_sw128_mnmajor(base + (uint32_t)(a * 2 * WG_CHUNK_BYTES) + k * 2048, WG_CHUNK_BYTES);
+                uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + (uint32_t)(c * P.slab_bytes) + k * 2048, row);
+                tc::mma_bf16(tmem_base + (uint32_t)((a * P.n_chunks + c) * 192), adesc, bdesc, idesc_n,
+                             (kt > k_begin || k > 0) ? 1u : 0u);
+              }
             }
-          }
           if (do_bias) {
-            const uint32_t idesc_b = tc::idesc_bf16_f32(128, 64, 1, 1);
+            // kh = 1 (one row into the slab) is dy unshifted; the chunks are one slab apart
+            const uint32_t idesc_b = tc::idesc_bf16_f32(128, P.n_chunks * 64, 1, 1);
             const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + row + k * 2048, WG_CHUNK_BYTES);   // kh = 1: dy unshifted
-              tc::mma_bf16(tmem_base + (uint32_t)(ntaps * 192), odesc, bdesc, idesc_b, (kt > k_begin || k > 0) ? 1u : 0u);
+              uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + row + k * 2048, (uint32_t)P.slab_bytes);
+              tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_chunks * 192), odesc, bdesc, idesc_b,
+                           (kt > k_begin || k > 0) ? 1u : 0u);
             }
           }
           tc::mma_commit(&empty_bar[stage]);
@@ -240,9 +246,9 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         for (int a = 0; a < ntaps; ++a) {
           const int kw = P.nstack_one ? 2 * a + (row >> 6) : tap0;
           const bool valid = rok && kw < 3;
-          const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * 192);
-          for (int c0 = 0; c0 < 192; c0 += 16) {
-            const int kh = 2 - (c0 >> 6), co0 = c0 & 63;
+          const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * P.n_chunks * 192);
+          for (int c0 = 0; c0 < P.n_chunks * 192; c0 += 16) {
+            const int kh = 2 - ((c0 % 192) >> 6), co0 = (c0 / 192) * 64 + (c0 & 63);
             if (co0 >= P.n_valid) continue;                       // warp-uniform
             __syncwarp();
             uint32_t rr[16];
@@ -297,7 +303,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       }
       if (do_bias && warp == 0) {
         // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
-        uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? 192 : P.n_mma));
+        uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? P.n_chunks * 192 : P.n_mma));
         for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
           __syncwarp();
           uint32_t rr[16];
@@ -374,7 +380,8 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
              P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && (5 + (c->db ? 1 : 0)) * P.n_mma <= 512 &&
              !getenv("OF_WG_NO_SLAB2"))
                 ? 1 : 0;
-  P.nstack = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view && P.n_chunks == 1 &&
+  P.nstack = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view &&
+              (P.n_chunks == 1 || (P.n_chunks == 2 && x_chunks >= 2 && !getenv("OF_WG_NO_NSTACK2"))) &&
               P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_NSTACK"))
                  ? 1 : 0;
   P.nstack_one = (P.nstack && x_chunks == 1) ? 1 : 0;
@@ -452,12 +459,12 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
-  if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.slab_bytes;
+  if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
-  if (P.nstack) cols = tpp * 192 + (c->db ? 64 : 0);
+  if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
   dim3 grid(jobs, splits);
