@@ -44,6 +44,25 @@ __global__ void __launch_bounds__(256) copy_channels_kernel(const TS* __restrict
   }
 }
 
+// 4 channels per thread (float4 / 4 x bf16): every stride, count and base pointer a multiple of 4 elements
+template <typename TS, typename TD, bool ACC>
+__global__ void __launch_bounds__(256) copy_channels4_kernel(const TS* __restrict__ src, int src_stride,
+                                                             TD* __restrict__ dst, int dst_stride, int nch4,
+                                                             size_t npix) {
+  size_t total = npix * nch4;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    size_t pix = e / nch4;
+    int c = (int)(e - pix * nch4) * 4;
+    float4 v = ld4<TS>(src + pix * src_stride + c);
+    TD* d = dst + pix * dst_stride + c;
+    if (ACC) {
+      float4 o = ld4<TD>(d);
+      v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+    }
+    st4<TD>(d, v);
+  }
+}
+
 __global__ void __launch_bounds__(256) bn_fold_fwd_kernel(const float* __restrict__ w, const float* __restrict__ b,
                                                           const float* __restrict__ gamma,
                                                           const float* __restrict__ beta,
@@ -200,6 +219,24 @@ int of_copy_channels(const void* src, int src_stride, void* dst, int dst_stride,
   OF_REQUIRE(nch > 0 && src_stride >= nch && dst_stride >= nch, OF_ERR_SHAPE, "bad channel strides");
   OF_REQUIRE(of_valid_dtype(src_dtype) && of_valid_dtype(dst_dtype), OF_ERR_ARG, "bad dtype");
   cudaStream_t st = (cudaStream_t)stream;
+  const size_t ssz = src_dtype == OF_F32 ? 4 : 2, dsz = dst_dtype == OF_F32 ? 4 : 2;
+  if (nch % 4 == 0 && src_stride % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t)src % (4 * ssz) == 0 &&
+      (uintptr_t)dst % (4 * dsz) == 0) {
+    int grid4 = g_grid(npix * (nch / 4));
+#define GO4(TS, TD)                                                                                         \
+  do {                                                                                                      \
+    if (accumulate)                                                                                         \
+      copy_channels4_kernel<TS, TD, true><<<grid4, 256, 0, st>>>((const TS*)src, src_stride, (TD*)dst, dst_stride, nch / 4, npix); \
+    else                                                                                                    \
+      copy_channels4_kernel<TS, TD, false><<<grid4, 256, 0, st>>>((const TS*)src, src_stride, (TD*)dst, dst_stride, nch / 4, npix); \
+  } while (0)
+    if (src_dtype == OF_F32 && dst_dtype == OF_F32) GO4(float, float);
+    else if (src_dtype == OF_F32 && dst_dtype == OF_BF16) GO4(float, __nv_bfloat16);
+    else if (src_dtype == OF_BF16 && dst_dtype == OF_F32) GO4(__nv_bfloat16, float);
+    else GO4(__nv_bfloat16, __nv_bfloat16);
+#undef GO4
+    return of_launch_check("copy_channels4_kernel");
+  }
   int grid = g_grid(npix * nch);
 #define GO(TS, TD)                                                                                          \
   do {                                                                                                      \
