@@ -245,6 +245,10 @@ int of_flow_head_bwd(const void* x, const float* dy, const float* w, float* dw, 
  * dgrad is the stride-1 dgrad of this tensor. */
 int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,
                       void* stream);
+/* Same tensor, but only the non-zero quarter is written (out[2i,2j] = dy[i,j]): `out` is a buffer the caller
+ * zero-filled once and keeps for this layer, so the zeros of earlier steps are still in place. */
+int of_scatter_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,
+                         void* stream);
 /* db[c] = sum over pixels of dy[p, c] (dy has pixel stride dy_stride) */
 int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int dtype, void* stream);
 

@@ -77,6 +77,8 @@ PROTOTYPES = {
     "of_conv1_unpack_wgrad": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "of_zero_upsample2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, C.c_void_p]),
+    "of_scatter_upsample2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_void_p]),
     "of_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "of_version": (_i, []),
     "of_last_error": (C.c_char_p, []),

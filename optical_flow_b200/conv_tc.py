@@ -56,6 +56,7 @@ class PackCache:
         self.table = None         # device copy of the job table
         self.total_blocks = 0
         self.fresh = False
+        self.zero_upsampled = {}  # (layer key, shape) -> persistent zero-inserted gradient buffer (stride-2 dgrads)
 
     def get(self, w_hwio, segs, rows, cols, transpose):
         key = (w_hwio.data_ptr(), tuple(w_hwio.shape), tuple(tuple(s) for s in segs), rows, cols, bool(transpose))
@@ -170,8 +171,19 @@ def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torc
                   sign_out=sign_out)
 
 
-def zero_upsample2(dy, H, W):
+def zero_upsample2(dy, H, W, cache=None, key=None):
+    """Zero-inserted dy for a stride-2 dgrad.  With a cache (the network's PackCache) the buffer is allocated and
+    zero-filled once per layer (`key`) and a step only rewrites the non-zero quarter."""
     N, Ho, Wo, Cc = dy.shape
+    if cache is not None and key is not None:
+        bufs = cache.zero_upsampled
+        k = (key, N, H, W, Cc, dy.dtype)
+        out = bufs.get(k)
+        if out is None:
+            out = bufs[k] = torch.zeros((N, H, W, Cc), dtype=dy.dtype, device=dy.device)
+        L.check(L.load().of_scatter_upsample2(L.ptr(dy), L.ptr(out), N, Ho, Wo, H, W, Cc, L.dtype_code(dy),
+                                              L.stream_ptr()), "of_scatter_upsample2")
+        return out
     out = torch.empty((N, H, W, Cc), dtype=dy.dtype, device=dy.device)
     L.check(L.load().of_zero_upsample2(L.ptr(dy), L.ptr(out), N, Ho, Wo, H, W, Cc, L.dtype_code(dy), L.stream_ptr()),
             "of_zero_upsample2")
@@ -188,7 +200,7 @@ def conv2d_dgrad_tc(dz, w_hwio, in_hw, stride=1, seg=None, out_dtype=torch.bfloa
     _, pt, _ = F.same_pad(H, KH, stride)
     _, pl, _ = F.same_pad(W, KW, stride)
     if stride == 2:
-        dz = zero_upsample2(dz, H, W)
+        dz = zero_upsample2(dz, H, W, cache=cache, key=w_hwio.data_ptr())
     ci0, cnt = seg if seg is not None else (0, Cin)
     n_out = out_channels or cnt
     n_mma = _ceil(n_out, 16)

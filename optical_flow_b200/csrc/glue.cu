@@ -129,6 +129,23 @@ __global__ void __launch_bounds__(256) zero_upsample2_kernel(const T* __restrict
   }
 }
 
+// the non-zero quarter only: out[2i, 2j] = dy[i, j]; the caller keeps the other positions of `out` zero (a buffer it
+// zero-filled once and dedicates to this layer), so a step writes 1/4 of the tensor instead of all of it
+template <typename T>
+__global__ void __launch_bounds__(256) scatter_upsample2_kernel(const T* __restrict__ dy, T* __restrict__ out, int N,
+                                                                int Ho, int Wo, int H, int W, int C4) {
+  size_t total = (size_t)N * Ho * Wo * C4;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    int c = (int)(e % C4);
+    size_t r = e / C4;
+    int w = (int)(r % Wo); r /= Wo;
+    int h = (int)(r % Ho);
+    int n = (int)(r / Ho);
+    if (2 * h < H && 2 * w < W)
+      st4<T>(out + ((((size_t)n * H + 2 * h) * W + 2 * w) * C4 + c) * 4, ld4<T>(dy + e * 4));
+  }
+}
+
 // ---- stem (Cin = 3, 7x7 / 2) on tensor cores: packed image + weight (un)packing ------------------
 // out (2B, (H+6)/2, W+6, 2, 4) bf16: frame 1s then frame 2s; TF-SAME zero border (2 rows / 2 cols before, 4 after);
 // one 16-byte texel = the pixel of TWO consecutive image rows (row pair pr = rows 2 pr - 2, 2 pr - 1) x 4 channels
@@ -199,6 +216,20 @@ int of_zero_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, i
     zero_upsample2_kernel<__nv_bfloat16><<<g_grid(total), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)dy, (__nv_bfloat16*)out, N, Ho, Wo, H, W, C / 4);
   return of_launch_check("zero_upsample2_kernel");
+}
+
+int of_scatter_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H, int W, int C, int dtype,
+                         void* stream) {
+  OF_REQUIRE(dy && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(N > 0 && Ho > 0 && Wo > 0 && H > 0 && W > 0 && C > 0 && C % 4 == 0, OF_ERR_SHAPE, "bad dims");
+  OF_REQUIRE(of_valid_dtype(dtype), OF_ERR_ARG, "bad dtype");
+  size_t total = (size_t)N * Ho * Wo * (C / 4);
+  if (dtype == OF_F32)
+    scatter_upsample2_kernel<float><<<g_grid(total), 256, 0, (cudaStream_t)stream>>>((const float*)dy, (float*)out, N, Ho, Wo, H, W, C / 4);
+  else
+    scatter_upsample2_kernel<__nv_bfloat16><<<g_grid(total), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (__nv_bfloat16*)out, N, Ho, Wo, H, W, C / 4);
+  return of_launch_check("scatter_upsample2_kernel");
 }
 
 int of_split_image_pair(const float* imgs, void* out, int B, int H, int W, int out_dtype, void* stream) {
