@@ -51,8 +51,10 @@ struct Conv3Params {
   ConvEpi E;
 };
 
-template <bool COAL>
-__global__ void __launch_bounds__(T3_THREADS, 1)
+// MINB = 2: two CTAs per SM (narrow layers, <= 256 TMEM columns and half the rings each): the second CTA's TMA
+// stream and MMAs fill the first one's bubbles
+template <bool COAL, int MINB = 1>
+__global__ void __launch_bounds__(T3_THREADS, MINB)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ Conv3Params P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -432,6 +434,17 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     if (sscanf(e, "%d,%d", &a_, &b_) == 2 && a_ >= 1 && a_ <= T3_MAX_A && b_ >= 3 && b_ <= T3_MAX_B &&
         a_ * P.slab_bytes + b_ * P.btile_bytes <= budget) { P.na = a_; P.nb = b_; }
   }
+  // Two CTAs per SM for the narrow layers (measured at N8 192x640: 64->32 96 -> 64 us, 96->64 183 -> 153 us; 64->64
+  // and the Cout >= 96 layers do not gain): 4 * n_mma <= 256 TMEM columns each, rings cut to ~100 KB, 96 registers.
+  int two = 0;
+  {
+    const int kch = kb / 64;
+    int b_ = (100 * 1024 - stg_bytes - 2 * P.slab_bytes) / P.btile_bytes;
+    if (b_ > T3_MAX_B) b_ = T3_MAX_B;
+    const char* e = getenv("OF_T3_2CTA");                  // 0 = never, 1 = every layer with n_mma <= 64
+    const bool want = e ? (atoi(e) > 0 && c->n_mma <= 64) : (c->n_mma <= 32 || (c->n_mma <= 64 && kch >= 2));
+    if (want && !P.coal && b_ >= 3 && P.m_tiles > OF_NUM_SMS) { two = 1; P.na = 2; P.nb = b_; }
+  }
   if (P.nb < 3) return 0;
   int cols = 4 * c->n_mma;
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
@@ -465,9 +478,14 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   if (!attr_set) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set = true;
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
+  if (two) {
+    grid = P.m_tiles < 2 * OF_NUM_SMS ? P.m_tiles : 2 * OF_NUM_SMS;
+    OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+  } else
   if (P.coal) OF_CUDA(of_launch_pdl(conv_tc3_kernel<true>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   if (int r = of_launch_check("conv_tc3_kernel")) return r;

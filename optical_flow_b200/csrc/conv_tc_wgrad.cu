@@ -452,6 +452,10 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   // ONE wave of one CTA per SM (never round up: 99 x 3 = 297 CTAs leaves one CTA for a wave of its own); a second
   // wave only repeats the prologue and doubles the split-K atomics (measured 3-15 % slower)
   int splits = OF_NUM_SMS / jobs;
+  // N-stacked, several input chunks, Cout <= 64: 256 TMEM columns and a 28 KB stage - TWO CTAs fit an SM and fill
+  // each other's bubbles (96->64 at N8 192x640: 198 -> 150 us)
+  const bool two_per_sm = P.nstack && !P.nstack_one && P.n_chunks == 1 && !getenv("OF_WG_NO_2CTA");
+  if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
   if (const char* e = getenv("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
   if (splits > P.ktiles) splits = P.ktiles;
   if (splits < 1) splits = 1;
@@ -462,6 +466,8 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
+  if (two_per_sm && P.stages > 3) P.stages = 3;
+  if (const char* e = getenv("OF_WG_STAGES")) { int v = atoi(e); if (v >= 1 && v < P.stages) P.stages = v; }
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
   if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);
