@@ -425,10 +425,21 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   P.n_mma = c->n_mma; P.n_valid = c->n_valid;
   P.b_tile_bytes = ((c->n_mma * 128) + 1023) / 1024 * 1024;
   int stage_bytes = A_TILE_BYTES + P.b_tile_bytes;
-  P.stages = (200 * 1024) / stage_bytes;
-  if (P.stages > MAX_STAGES) P.stages = MAX_STAGES;
   int cols = 2 * c->n_mma;
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+  // several CTAs per SM where TMEM allows it (the kernel needs 58 registers): a second CTA's TMA stream and MMAs
+  // fill the bubbles of the first; the stage ring is split between them
+  int ctas = 512 / P.tmem_cols;
+  {
+    const char* e = getenv("OF_TC_CTAS");
+    const int cap = e ? atoi(e) : 2;
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    while (ctas > 1 && ((200 * 1024) / ctas) / stage_bytes < 3) --ctas;
+    if (P.m_tiles <= OF_NUM_SMS) ctas = 1;
+  }
+  P.stages = ((200 * 1024) / ctas) / stage_bytes;
+  if (P.stages > MAX_STAGES) P.stages = MAX_STAGES;
   P.out = c->out; P.out_dtype = c->out_dtype; P.out_stride = c->out_stride;
   P.bias = c->bias; P.act = c->act;
   P.add = c->add; P.add_dtype = c->add_dtype; P.add_stride = c->add_stride;
@@ -453,7 +464,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
+  int grid = P.m_tiles < ctas * OF_NUM_SMS ? P.m_tiles : ctas * OF_NUM_SMS;
   OF_CUDA(of_launch_pdl(conv_tc_kernel, dim3(grid), dim3(TC_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   return of_launch_check("conv_tc_kernel");
 }
