@@ -1,7 +1,7 @@
 """Literal NumPy restatement of the reference hot path (fp32 unless noted).
 
-TEST INFRASTRUCTURE ONLY - see oracle/__init__.py.  PARITY UNPINNED (no TF,
-no reference tests); every function cites the reference lines it follows.
+TEST INFRASTRUCTURE ONLY - see oracle/__init__.py (pinned to tests/golden/ops.npz: the
+reference's own Python run over a TF stand-in); every function cites the reference lines it follows.
 All citations are relative to the reference tree (xianlopez/optical_flow).
 
 Layout: NHWC float32, exactly like the reference.

@@ -1,7 +1,7 @@
 """NumPy restatement, part 2: resize, flow upscale, cost volume, the two
 pyramid losses (forward + hand-derived backward), Adam, TF SAME padding.
 
-TEST INFRASTRUCTURE ONLY - see oracle/__init__.py.  PARITY UNPINNED.
+TEST INFRASTRUCTURE ONLY - see oracle/__init__.py (pinned to tests/golden/ops.npz).
 """
 from __future__ import annotations
 

@@ -1,6 +1,6 @@
 """Independent torch-CPU autograd restatement of the reference hot path.
 
-TEST INFRASTRUCTURE ONLY - see oracle/__init__.py.  PARITY UNPINNED.
+TEST INFRASTRUCTURE ONLY - see oracle/__init__.py (pinned to tests/golden/*.npz).
 
 Second implementation for the two-implementation rule: every op
 is written with differentiable torch primitives so that autograd derives the
