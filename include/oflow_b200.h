@@ -273,6 +273,21 @@ int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const flo
                    float eps, const float* dw_folded, const float* db_folded, float* dw, float* db, float* dgamma,
                    float* dbeta, int K, int Cout, void* stream);
 
+/* All BN folds of a model in ONE launch each way.  jobs_device: device array of of_bn_job (one per conv + BN pair;
+ * pointers as in of_bn_fold_fwd / of_bn_fold_bwd, b / db nullable).  Forward: a job owns the blocks
+ * [block_begin, next job's block_begin), OF_BN_FWD_BLOCK elements of K*Cout each; backward: one block per output
+ * channel, block_begin = the running sum of Cout. */
+#define OF_BN_FWD_BLOCK 2048
+typedef struct {
+  const float* w; const float* b; const float* gamma; const float* beta; const float* mean; const float* var;
+  float* wf; float* bf;                                    /* forward outputs (folded weight / bias) */
+  const float* dwf; const float* dbf;                      /* backward inputs (gradients of the folded pair) */
+  float* dw; float* db; float* dgamma; float* dbeta;       /* backward outputs */
+  int K, Cout, fwd_block_begin, bwd_block_begin;
+} of_bn_job;
+int of_bn_fold_fwd_batch(const of_bn_job* jobs_device, int njobs, int total_blocks, float eps, void* stream);
+int of_bn_fold_bwd_batch(const of_bn_job* jobs_device, int njobs, int total_blocks, float eps, void* stream);
+
 /* ---- data path ------------------------------------------
  * data_reader.py:45-64 read_item + :36-41 batch assembly on the device: img1 / img2 = decoded uint8 BGR frames
  * (src_h, src_w, 3) in device memory; out = the item's (H, W, 6) f32 slice of the batch:

@@ -64,6 +64,15 @@ class PackJob(C.Structure):
                 ("block_begin", C.c_int), ("reserved", C.c_int)]
 
 
+class BnJob(C.Structure):
+    """of_bn_job (include/oflow_b200.h)."""
+    _fields_ = [(n, C.c_void_p) for n in ("w", "b", "gamma", "beta", "mean", "var", "wf", "bf", "dwf", "dbf", "dw", "db",
+                                          "dgamma", "dbeta")] + \
+               [("K", C.c_int), ("Cout", C.c_int), ("fwd_block_begin", C.c_int), ("bwd_block_begin", C.c_int)]
+
+
+OF_BN_FWD_BLOCK = 2048
+
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
 PROTOTYPES = {
     "of_conv_tc_run": (C.c_int, [C.POINTER(TcConv), C.c_void_p]),
@@ -124,6 +133,8 @@ PROTOTYPES = {
     "of_view_coords_bwd": (_i, [_fp9, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "of_make_transformation_matrix_fwd": (_i, [_vp, _i, _vp, _i, _vp]),
     "of_make_transformation_matrix_bwd": (_i, [_vp, _i, _vp, _vp, _i, _vp]),
+    "of_bn_fold_fwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
+    "of_bn_fold_bwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
     "of_comm_unique_id": (_i, [_vp]),
     "of_comm_init": (_i, [_vp, _i, _i, _pp]),

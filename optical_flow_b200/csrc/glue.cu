@@ -111,6 +111,50 @@ __global__ void __launch_bounds__(256) bn_fold_bwd_kernel(const float* __restric
   }
 }
 
+// ---- the same two folds for every conv + BN pair of the model, one launch each (26 tiny launches -> 2) ----
+__global__ void __launch_bounds__(256) bn_fold_fwd_batch_kernel(const of_bn_job* __restrict__ jobs, int njobs,
+                                                                float eps) {
+  int j = 0;
+  while (j + 1 < njobs && (int)blockIdx.x >= jobs[j + 1].fwd_block_begin) ++j;
+  const of_bn_job J = jobs[j];
+  const size_t total = (size_t)J.K * J.Cout;
+  const size_t e0 = (size_t)((int)blockIdx.x - J.fwd_block_begin) * OF_BN_FWD_BLOCK;
+  for (size_t e = e0 + threadIdx.x; e < e0 + OF_BN_FWD_BLOCK && e < total; e += 256) {
+    int co = (int)(e % J.Cout);
+    float s = J.gamma[co] / sqrtf(J.var[co] + eps);
+    J.wf[e] = J.w[e] * s;
+    if (e < (size_t)J.Cout) J.bf[co] = ((J.b ? J.b[co] : 0.f) - J.mean[co]) * s + J.beta[co];
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_fold_bwd_batch_kernel(const of_bn_job* __restrict__ jobs, int njobs,
+                                                                float eps) {
+  int j = 0;
+  while (j + 1 < njobs && (int)blockIdx.x >= jobs[j + 1].bwd_block_begin) ++j;
+  const of_bn_job J = jobs[j];
+  const int co = (int)blockIdx.x - J.bwd_block_begin, Cout = J.Cout;
+  float inv_std = 1.0f / sqrtf(J.var[co] + eps);
+  float s = J.gamma[co] * inv_std;
+  float acc = 0.f;
+  for (int k = threadIdx.x; k < J.K; k += blockDim.x) {
+    float g = J.dwf[(size_t)k * Cout + co];
+    acc += g * J.w[(size_t)k * Cout + co];
+    J.dw[(size_t)k * Cout + co] = g * s;
+  }
+  __shared__ float sm[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += sm[i];
+    float g_b = J.dbf[co];
+    J.dgamma[co] = (t + g_b * ((J.b ? J.b[co] : 0.f) - J.mean[co])) * inv_std;
+    J.dbeta[co] = g_b;
+    if (J.db) J.db[co] = g_b * s;
+  }
+}
+
 // zero-insertion x2 (stride-2 dgrad = stride-1 dgrad of the zero-upsampled dy)
 template <typename T>
 __global__ void __launch_bounds__(256) zero_upsample2_kernel(const T* __restrict__ dy, T* __restrict__ out, int N,
@@ -302,6 +346,18 @@ int of_bn_fold_bwd(const float* w, const float* b, const float* gamma, const flo
   bn_fold_bwd_kernel<<<Cout, 256, 0, (cudaStream_t)stream>>>(w, b, gamma, mean, var, eps, dw_folded, db_folded, dw,
                                                              db, dgamma, dbeta, K, Cout);
   return of_launch_check("bn_fold_bwd_kernel");
+}
+
+int of_bn_fold_fwd_batch(const of_bn_job* jobs_device, int njobs, int total_blocks, float eps, void* stream) {
+  OF_REQUIRE(jobs_device && njobs > 0 && total_blocks > 0, OF_ERR_ARG, "bad BN job table");
+  bn_fold_fwd_batch_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(jobs_device, njobs, eps);
+  return of_launch_check("bn_fold_fwd_batch_kernel");
+}
+
+int of_bn_fold_bwd_batch(const of_bn_job* jobs_device, int njobs, int total_blocks, float eps, void* stream) {
+  OF_REQUIRE(jobs_device && njobs > 0 && total_blocks > 0, OF_ERR_ARG, "bad BN job table");
+  bn_fold_bwd_batch_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(jobs_device, njobs, eps);
+  return of_launch_check("bn_fold_bwd_batch_kernel");
 }
 
 int of_pack_image_pair8(const float* imgs, void* out, int B, int H, int W, void* stream) {

@@ -135,12 +135,13 @@ class ConvLayer:
             net.backend.wgrad(self, self.x, dz, dwf, dbf)
             st = net.store
             b = self._p("/bias") if self.use_bias else None
-            L.check(L.load().of_bn_fold_bwd(
-                L.ptr(self._p("/kernel")), L.ptr(b), L.ptr(st.p[self.bn + "/gamma"]),
-                L.ptr(st.stats[self.bn + "/moving_mean"]), L.ptr(st.stats[self.bn + "/moving_variance"]), BN_EPS,
-                L.ptr(dwf), L.ptr(dbf), L.ptr(self._g("/kernel")), L.ptr(self._g("/bias")) if self.use_bias else None,
-                L.ptr(st.g[self.bn + "/gamma"]), L.ptr(st.g[self.bn + "/beta"]), K, self.cout, L.stream_ptr()),
-                "of_bn_fold_bwd")
+            if not getattr(net, "_bn_bwd_deferred", False):     # FlowNet.backward un-folds every layer in one launch
+                L.check(L.load().of_bn_fold_bwd(
+                    L.ptr(self._p("/kernel")), L.ptr(b), L.ptr(st.p[self.bn + "/gamma"]),
+                    L.ptr(st.stats[self.bn + "/moving_mean"]), L.ptr(st.stats[self.bn + "/moving_variance"]), BN_EPS,
+                    L.ptr(dwf), L.ptr(dbf), L.ptr(self._g("/kernel")), L.ptr(self._g("/bias")) if self.use_bias else None,
+                    L.ptr(st.g[self.bn + "/gamma"]), L.ptr(st.g[self.bn + "/beta"]), K, self.cout, L.stream_ptr()),
+                    "of_bn_fold_bwd")
         if not need_dx:
             return None
         if add is not None:
@@ -423,10 +424,51 @@ class FlowNet:
         if cache is None:
             return
         cache.invalidate()
+        table = self._bn_job_table()
+        if table is not None:
+            L.check(L.load().of_bn_fold_fwd_batch(L.ptr(table), self._bn_njobs, self._bn_fwd_blocks, BN_EPS,
+                                                  L.stream_ptr()), "of_bn_fold_fwd_batch")
         for layer in self.conv_layers:
-            layer.w_eff, layer.b_eff = layer.effective_weights()
+            if layer.bn is not None and table is not None:
+                layer.w_eff = self.buf(layer.name + ":wf", layer._p("/kernel").shape, torch.float32)
+                layer.b_eff = self.buf(layer.name + ":bf", (layer.cout,), torch.float32)
+            else:
+                layer.w_eff, layer.b_eff = layer.effective_weights()
             layer.weights_ready = True
         cache.refresh()
+
+    def _bn_job_table(self):
+        """Device table of of_bn_job, one per conv + BN pair (all buffers persistent): both folds of the whole
+        model are then one launch each.  Built once."""
+        if getattr(self, "_bn_table", None) is not None:
+            return self._bn_table
+        layers = [l for l in self.conv_layers if l.bn is not None]
+        if not layers:
+            return None
+        arr = (L.BnJob * len(layers))()
+        fb = bb = 0
+        st = self.store
+        for k, l in enumerate(layers):
+            w = l._p("/kernel")
+            K = l.k * l.k * l.cin
+            j = arr[k]
+            j.w, j.b = w.data_ptr(), (l._p("/bias").data_ptr() if l.use_bias else None)
+            j.gamma, j.beta = st.p[l.bn + "/gamma"].data_ptr(), st.p[l.bn + "/beta"].data_ptr()
+            j.mean, j.var = st.stats[l.bn + "/moving_mean"].data_ptr(), st.stats[l.bn + "/moving_variance"].data_ptr()
+            j.wf = self.buf(l.name + ":wf", w.shape, torch.float32).data_ptr()
+            j.bf = self.buf(l.name + ":bf", (l.cout,), torch.float32).data_ptr()
+            j.dwf = self.buf(l.name + ":dwf", w.shape, torch.float32).data_ptr()
+            j.dbf = self.buf(l.name + ":dbf", (l.cout,), torch.float32).data_ptr()
+            j.dw, j.db = l._g("/kernel").data_ptr(), (l._g("/bias").data_ptr() if l.use_bias else None)
+            j.dgamma, j.dbeta = st.g[l.bn + "/gamma"].data_ptr(), st.g[l.bn + "/beta"].data_ptr()
+            j.K, j.Cout, j.fwd_block_begin, j.bwd_block_begin = K, l.cout, fb, bb
+            fb += (K * l.cout + L.OF_BN_FWD_BLOCK - 1) // L.OF_BN_FWD_BLOCK
+            bb += l.cout
+        self._bn_njobs, self._bn_fwd_blocks, self._bn_bwd_blocks = len(layers), fb, bb
+        import ctypes
+        raw = torch.frombuffer(bytearray(ctypes.string_at(ctypes.addressof(arr), ctypes.sizeof(arr))), dtype=torch.uint8)
+        self._bn_table = raw.to(self.device)
+        return self._bn_table
 
     def backend_split(self, batch_imgs):
         if hasattr(self.backend, "split"):
@@ -440,6 +482,9 @@ class FlowNet:
     def backward(self, d_flows):
         """d_flows: [d_flow3, d_flow2, d_flow1, d_flow0] (finest first, like the outputs)."""
         B = self.B
+        # with a packed-weight back-end every BN fold is un-folded by ONE launch after the last wgrad
+        table = self._bn_job_table() if getattr(self.backend, "pack_cache", None) is not None else None
+        self._bn_bwd_deferred = table is not None
         d_by_level = [d_flows[3], d_flows[2], d_flows[1], d_flows[0]]
         d_enc = [None] * 4
         carry = None
@@ -456,7 +501,13 @@ class FlowNet:
             if d_f2.data_ptr() != de[B:].data_ptr():
                 _copy_channels(d_f2, 0, de[B:], 0, d_f2.shape[-1])
             d_enc[3 - lvl] = de
-        self.encoder.backward(d_enc)
+        try:
+            self.encoder.backward(d_enc)
+        finally:
+            self._bn_bwd_deferred = False
+        if table is not None:
+            L.check(L.load().of_bn_fold_bwd_batch(L.ptr(table), self._bn_njobs, self._bn_bwd_blocks, BN_EPS,
+                                                  L.stream_ptr()), "of_bn_fold_bwd_batch")
 
     # -- I/O (.npz with the reference's layer names) -------------
     def save_weights(self, path):
