@@ -25,14 +25,14 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const bool ch_ok = lane < Cin;
   const int ci = ch_ok ? lane : 0;
-  float wr[9][2], acc[9][2], bsum[2] = {0.f, 0.f};
+  // the two output channels ride in one packed fp32x2 FMA (sm_100 FFMA2): 18 instead of 36 FMAs per pixel
+  float2 wr[9], acc[9];
+  float bsum[2] = {0.f, 0.f};
 #pragma unroll
-  for (int t = 0; t < 9; ++t)
-#pragma unroll
-    for (int co = 0; co < 2; ++co) {
-      wr[t][co] = ch_ok ? __ldg(w + ((size_t)t * Cin + ci) * 2 + co) : 0.f;
-      acc[t][co] = 0.f;
-    }
+  for (int t = 0; t < 9; ++t) {
+    wr[t] = ch_ok ? __ldg(reinterpret_cast<const float2*>(w) + (size_t)t * Cin + ci) : make_float2(0.f, 0.f);
+    acc[t] = make_float2(0.f, 0.f);
+  }
   const int segs_x = (W + HD_SEG - 1) / HD_SEG;
   const long long nseg = (long long)N * H * segs_x;
   const float2* dy2 = reinterpret_cast<const float2*>(dy);
@@ -67,7 +67,8 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
 #pragma unroll
           for (int rr = 0; rr < 3; ++rr) c2[rr] = cn[k][rr];
           const float xv = xin[k];
-          float d = 0.f;
+          const float2 xv2 = make_float2(xv, xv);
+          float2 d2 = make_float2(0.f, 0.f);
           // tap (kh,kw) pairs with dy[q - (kh-1, kw-1)] = window[row 2-kh][col 2-kw]
 #pragma unroll
           for (int kh = 0; kh < 3; ++kh) {
@@ -76,12 +77,11 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
             for (int kw = 0; kw < 3; ++kw) {
               const float2 g = wc[2 - kw];
               const int t = kh * 3 + kw;
-              acc[t][0] = fmaf(xv, g.x, acc[t][0]);
-              acc[t][1] = fmaf(xv, g.y, acc[t][1]);
-              d = fmaf(wr[t][0], g.x, d);
-              d = fmaf(wr[t][1], g.y, d);
+              acc[t] = __ffma2_rn(xv2, g, acc[t]);
+              d2 = __ffma2_rn(wr[t], g, d2);
             }
           }
+          const float d = d2.x + d2.y;
           bsum[0] += c1[1].x; bsum[1] += c1[1].y;
           if (dz != nullptr && ch_ok) {
             float slope = 1.f;
@@ -99,8 +99,8 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
   float* mine = &red[warp][0][0];
 #pragma unroll
   for (int t = 0; t < 9; ++t) {
-    mine[(2 * t) * 32 + lane] = acc[t][0];
-    mine[(2 * t + 1) * 32 + lane] = acc[t][1];
+    mine[(2 * t) * 32 + lane] = acc[t].x;
+    mine[(2 * t + 1) * 32 + lane] = acc[t].y;
   }
   if (lane < 2) mine[18 * 32 + lane] = bsum[lane];
   __syncthreads();
