@@ -124,6 +124,35 @@ def test_tc_dgrad(cuda, cfg):
     assert rel_err(dz, ref2) <= 2 ** -7
 
 
+# more output tiles than SMs: the layers that run TWO CTAs per SM (conv_tc3 with n_mma <= 32 or several K chunks and
+# n_mma <= 64; the general kernel wherever two TMEM allocations fit) only take that path on a grid this large
+TWO_CTA_CASES = [
+    (8, 96, 128, 64, 3, 32, 1),      # conv_tc3<., 2>: n_mma = 32, 384 super-tiles
+    (4, 96, 128, 96, 3, 64, 1),      # conv_tc3<., 2>: two K chunks, n_mma = 64, 192 super-tiles
+    (8, 128, 128, 64, 3, 64, 2),     # conv_tc_kernel, stride 2: 256 tiles, 128 TMEM columns -> 2 CTAs / SM
+]
+
+
+@pytest.mark.parametrize("cfg", TWO_CTA_CASES)
+def test_tc_two_ctas_per_sm(cuda, cfg, monkeypatch):
+    """fprop, dgrad (+ mask epilogue) and sign-bit masks on grids large enough for the two-CTA variants; the
+    one-CTA launch of the same layer (OF_T3_2CTA=0 / OF_TC_CTAS=1) must give the same bits."""
+    from optical_flow_b200 import conv_tc, _lib as L
+    test_tc_fprop(cuda, cfg)
+    test_tc_dgrad(cuda, cfg)
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 11)
+    xd, wd, bd = torch.tensor(x, device=cuda).bfloat16(), torch.tensor(w, device=cuda), torch.tensor(b, device=cuda)
+    two = conv_tc.conv2d_fprop_tc(xd, wd, bd, stride=s, act=L.OF_ACT_LEAKY)
+    monkeypatch.setenv("OF_T3_2CTA", "0")
+    monkeypatch.setenv("OF_TC_CTAS", "1")
+    one = conv_tc.conv2d_fprop_tc(xd, wd, bd, stride=s, act=L.OF_ACT_LEAKY)
+    assert torch.equal(one, two)
+    if s == 1:
+        monkeypatch.delenv("OF_T3_2CTA")
+        test_tc3_sign_bit_mask(cuda, cfg)
+
+
 @pytest.mark.parametrize("cfg", [(2, 24, 32, 64, 3, 64, 1), (1, 16, 48, 128, 3, 96, 1), (1, 9, 13, 64, 3, 32, 1)])
 def test_tc3_staged_epilogue_variant(cuda, cfg, monkeypatch):
     """conv_tc3.cu's optional staged (coalesced) epilogue, OF_T3_COAL=1: same results as the default."""
