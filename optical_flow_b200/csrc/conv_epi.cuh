@@ -78,6 +78,13 @@ struct ConvEpi {
 };
 #define OF_MASK_BITS 2   // mask_dtype: `mask` is such a sign-bit buffer (conv_tc3 only)
 
+// 32 bytes in one instruction = one full L2 sector (p 32-byte aligned)
+__device__ __forceinline__ void st_global_256(void* p, const uint32_t (&pk)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]),
+               "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+               : "memory");
+}
+
 struct ConvEpi;
 __device__ __forceinline__ void store16(const ConvEpi& E, size_t pix, int c0, const float (&v)[16]);
 
@@ -117,8 +124,12 @@ __device__ __forceinline__ void epilogue_store16(const ConvEpi& E, size_t pix, i
         __nv_bfloat162 t = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
         pk[j] = *reinterpret_cast<uint32_t*>(&t);
       }
-      reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-      reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+        st_global_256(o, pk);
+      } else {
+        reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      }
     } else {
 #pragma unroll
       for (int j = 0; j < 16; ++j) if (j < nv) o[j] = __float2bfloat16_rn(v[j]);
@@ -148,12 +159,26 @@ __device__ __forceinline__ void store16(const ConvEpi& E, size_t pix, int c0, co
       __nv_bfloat162 t = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
       pk[j] = *reinterpret_cast<uint32_t*>(&t);
     }
-    reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-    reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+      // one 256-bit store = one full 32-byte L2 sector (two 16-byte stores are two partial-sector writes: the conv
+      // kernels are L2-slice-throughput bound, and the output stores were 17 % of a 128->128 layer's time)
+      st_global_256(o, pk);
+    } else {
+      reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
   } else {
     float* o = reinterpret_cast<float*>(E.out) + pix * E.out_stride + c0;
+    if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+      uint32_t lo[8], hi[8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-      reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      for (int j = 0; j < 8; ++j) { lo[j] = __float_as_uint(v[j]); hi[j] = __float_as_uint(v[8 + j]); }
+      st_global_256(o, lo);
+      st_global_256(o + 8, hi);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
   }
 }

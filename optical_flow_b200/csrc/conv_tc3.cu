@@ -111,15 +111,25 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           for (int kc = 0; kc < P.kchunks[s]; ++kc) {
             for (int kw = 0; kw < 3; ++kw) {
               tc::mbar_wait(&a_empty[as], aph ^ 1);
+              if ((P.dbg & 32) && tile != (int)blockIdx.x) {
+                tc::mbar_arrive(&a_full[as]);         // profiling only: activation slabs "free"
+              } else {
               tc::mbar_expect_tx(&a_full[as], (uint32_t)P.slab_bytes);
               tc::tma_load_4d(a_ring + (size_t)as * P.slab_bytes, tmA, &a_full[as], kc * 64,
                               w0 + P.sign * (kw - P.pad_l), h0 + slab_dh, n);
+              }
               if (++as == P.na) { as = 0; aph ^= 1; }
               for (int kh = 0; kh < 3; ++kh) {
                 tc::mbar_wait(&b_empty[bs], bph ^ 1);
+                if ((P.dbg & 8) && tile != (int)blockIdx.x) {
+                  tc::mbar_arrive(&b_full[bs]);       // profiling only: weight tiles "free" after the first output tile
+                } else if ((P.dbg & 16) && tile != (int)blockIdx.x && kh > 0) {
+                  tc::mbar_arrive(&b_full[bs]);       // profiling only: a third of the weight traffic
+                } else {
                 tc::mbar_expect_tx(&b_full[bs], (uint32_t)(P.n_mma * 128));
                 tc::tma_load_3d(b_ring + (size_t)bs * P.btile_bytes, &tmB, &b_full[bs], P.kbase[s] + kc * 64, 0,
                                 kh * 3 + kw);
+                }
                 if (++bs == P.nb) { bs = 0; bph ^= 1; }
               }
             }
@@ -315,7 +325,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 #pragma unroll
               for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], P.E.mask_act);
             }
-            store16(P.E, pix, c0, v);
+            // profiling only (dbg 64): all the epilogue math, no global store
+            if (!(P.dbg & 64) || v[0] + v[7] + v[15] == 1.2345e-30f) store16(P.E, pix, c0, v);
           } else {
             epilogue_store16(P.E, pix, c0, rr[slot]);    // ragged channel tail / unaligned strides: generic path
           }
