@@ -21,6 +21,13 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 
+// 32 bytes in one instruction = one full L2 sector (p 32-byte aligned)
+__device__ __forceinline__ void st256(void* p, const uint32_t (&pk)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]),
+               "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+               : "memory");
+}
+
 #define CT_THREADS 320
 #define CT_M 128
 #define CT_NB 144
@@ -245,8 +252,12 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
             pk[j] = *reinterpret_cast<uint32_t*>(&t2);
           }
           uint4* op = reinterpret_cast<uint4*>(P.out + off + c0);
-          op[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          op[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          if ((reinterpret_cast<uintptr_t>(op) & 31) == 0) {
+            st256(op, pk);                               // one full 32-byte L2 sector per instruction
+          } else {
+            op[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            op[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          }
         }
       }
       tc::fence_before_sync();
@@ -407,7 +418,16 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
         __nv_bfloat16* o = P.out + (((size_t)b * P.H + y) * P.W + x) * P.cv_stride;
         uint4* o4 = reinterpret_cast<uint4*>(o);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) o4[k] = make_uint4(ow[4 * k], ow[4 * k + 1], ow[4 * k + 2], ow[4 * k + 3]);
+        for (int k = 0; k < 6; k += 2) {
+          if ((reinterpret_cast<uintptr_t>(o4) & 31) == 0) {
+            const uint32_t w8[8] = {ow[4 * k], ow[4 * k + 1], ow[4 * k + 2], ow[4 * k + 3],
+                                    ow[4 * k + 4], ow[4 * k + 5], ow[4 * k + 6], ow[4 * k + 7]};
+            st256(o4 + k, w8);
+          } else {
+            o4[k] = make_uint4(ow[4 * k], ow[4 * k + 1], ow[4 * k + 2], ow[4 * k + 3]);
+            o4[k + 1] = make_uint4(ow[4 * k + 4], ow[4 * k + 5], ow[4 * k + 6], ow[4 * k + 7]);
+          }
+        }
         *reinterpret_cast<uint16_t*>(o + 48) = (uint16_t)(ow[24] & 0xffffu);
       }
     }
