@@ -85,6 +85,13 @@ __device__ __forceinline__ void st_global_256(void* p, const uint32_t (&pk)[8]) 
                : "memory");
 }
 
+// 32 bytes in one load (read-only path): two uint4 halves of one L2 sector (p 32-byte aligned)
+__device__ __forceinline__ void ld_global_256(const void* p, uint4& a, uint4& b) {
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+               : "l"(p));
+}
+
 struct ConvEpi;
 __device__ __forceinline__ void store16(const ConvEpi& E, size_t pix, int c0, const float (&v)[16]);
 

@@ -242,15 +242,23 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               const int nq = (COAL || P.E.add_dtype == OF_BF16) ? 2 : 4;
               const uint4* qd = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.add) +
                                                                (pix * P.E.add_stride + c * 16) * (nq == 2 ? 2 : 4));
+              if (nq == 2 && (reinterpret_cast<uintptr_t>(qd) & 31) == 0) {
+                ld_global_256(qd, araw[slot][0], araw[slot][1]);      // one full sector per request
+              } else {
 #pragma unroll
-              for (int k = 0; k < (COAL ? 2 : 4); ++k) if (k < nq) araw[slot][k] = __ldg(qd + k);
+                for (int k = 0; k < (COAL ? 2 : 4); ++k) if (k < nq) araw[slot][k] = __ldg(qd + k);
+              }
             }
             if (!COAL && P.E.mask && !mask_bits) {
               const int nq = P.E.mask_dtype == OF_BF16 ? 2 : 4;
               const uint4* qd = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(P.E.mask) +
                                                                (pix * P.E.mask_stride + c * 16) * (P.E.mask_dtype == OF_BF16 ? 2 : 4));
+              if (nq == 2 && (reinterpret_cast<uintptr_t>(qd) & 31) == 0) {
+                ld_global_256(qd, mraw[slot][0], mraw[slot][1]);
+              } else {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) if (k < nq) mraw[slot][k] = __ldg(qd + k);
+                for (int k = 0; k < 4; ++k) if (k < nq) mraw[slot][k] = __ldg(qd + k);
+              }
             }
           }
         };

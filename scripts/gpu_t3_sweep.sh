@@ -1,2 +1,2 @@
-python scripts/bench_conv_layer.py 2>&1
-python -m pytest tests/test_gpu_conv_tc.py -x -q -m gpu 2>&1 | tail -2
+python scripts/prof_conv_pair.py
+python -m pytest tests -x -q -m gpu 2>&1 | tail -2
