@@ -173,12 +173,20 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
           const int xa = x0 - 3 + tb, xb = xa + 128;
           const bool oka = row_ok && xa >= 0 && xa < P.W;
           const bool okb = row_ok && tb < 6 && xb < P.W;
-          const uint32_t* pa = reinterpret_cast<const uint32_t*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (oka ? xa : 0)) * P.cv_stride) + wofs;
-          const uint32_t* pb = reinterpret_cast<const uint32_t*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (okb ? xb : 0)) * P.cv_stride) + wofs;
+          // the 4-word window starts at word wofs of the pixel's 128-byte row: one or two 16-byte chunks instead of
+          // four 4-byte loads (every request is a sector operation in L2, and this kernel is L2-bound)
+          const int q0 = wofs >> 2, sh = wofs & 3;
+          const uint4* pa = reinterpret_cast<const uint4*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (oka ? xa : 0)) * P.cv_stride) + q0;
+          const uint4* pb = reinterpret_cast<const uint4*>(P.d_cv + (((size_t)b * P.H + (row_ok ? ys : 0)) * P.W + (okb ? xb : 0)) * P.cv_stride) + q0;
+          const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+          const uint4 alo = oka ? __ldg(pa) : z4, ahi = (oka && sh) ? __ldg(pa + 1) : z4;
+          const uint4 blo = okb ? __ldg(pb) : z4, bhi = (okb && sh) ? __ldg(pb + 1) : z4;
+          const uint32_t ta[8] = {alo.x, alo.y, alo.z, alo.w, ahi.x, ahi.y, ahi.z, ahi.w};
+          const uint32_t tb8[8] = {blo.x, blo.y, blo.z, blo.w, bhi.x, bhi.y, bhi.z, bhi.w};
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            wa[i][q] = oka ? __ldg(pa + q) : 0u;
-            wb[i][q] = okb ? __ldg(pb + q) : 0u;
+            wa[i][q] = ta[sh + q];
+            wb[i][q] = tb8[sh + q];
           }
         }
       }
