@@ -367,7 +367,7 @@ def bench_loss(args, dev, world, rank):
     fl_bytes = sum(f.numel() * 4 for f in h_flows)
     e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
            "h2d_bytes_per_step": h_imgs.numel() * 4 + fl_bytes, "d2h_bytes_per_step": fl_bytes + 4}
-    return {"metric": "image-pairs/s through fused warp+loss (fwd + d_flow), 384x1280", "value": value,
+    return {"metric": "image-pairs/s through fused warp+loss (fwd + d_flow), %dx%d" % (H, W), "value": value,
             "unit": "image-pairs/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": per, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
