@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
   const int grp = threadIdx.x / TPP;       // pixel slot within the pass
   constexpr int PIX_PER_PASS = 256 / TPP;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    float4 racc[4];                                   // RUN: pending contribution per tap slot
+    float4 racc[4][VEC == 8 ? 2 : 1];                 // RUN: pending contribution per tap slot
     size_t raddr[4];
     bool rvalid[4] = {false, false, false, false};
     for (int p0 = 0; p0 < TILE * TILE; p0 += PIX_PER_PASS) {
@@ -257,7 +257,49 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
         for (int v = sub; v < CV; v += TPP) {
           if (!valid) continue;
           int ch = v * VEC;
-          if (VEC == 4) {
+          if constexpr (VEC == 8) {
+            // bf16 features and bf16 incoming gradient, 16-byte accesses: 8 threads per 64-channel pixel
+            float g[8], v00[8], v01[8], v10[8], v11[8];
+            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(d_out) + pix * C + ch, g);
+            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o00 + ch, v00);
+            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o01 + ch, v01);
+            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o10 + ch, v10);
+            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o11 + ch, v11);
+            // same summation order as the VEC == 4 path over the two 4-channel halves
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int k = 4 * h;
+              d0 += g[k] * (t.ay * (v10[k] - v00[k]) + t.by * (v11[k] - v01[k])) +
+                    g[k + 1] * (t.ay * (v10[k + 1] - v00[k + 1]) + t.by * (v11[k + 1] - v01[k + 1])) +
+                    g[k + 2] * (t.ay * (v10[k + 2] - v00[k + 2]) + t.by * (v11[k + 2] - v01[k + 2])) +
+                    g[k + 3] * (t.ay * (v10[k + 3] - v00[k + 3]) + t.by * (v11[k + 3] - v01[k + 3]));
+              d1 += g[k] * (t.ax * (v01[k] - v00[k]) + t.bx * (v11[k] - v10[k])) +
+                    g[k + 1] * (t.ax * (v01[k + 1] - v00[k + 1]) + t.bx * (v11[k + 1] - v10[k + 1])) +
+                    g[k + 2] * (t.ax * (v01[k + 2] - v00[k + 2]) + t.bx * (v11[k + 2] - v10[k + 2])) +
+                    g[k + 3] * (t.ax * (v01[k + 3] - v00[k + 3]) + t.bx * (v11[k + 3] - v10[k + 3]));
+            }
+            if (d_in != nullptr) {
+              const size_t offs[4] = {o00 + ch, o01 + ch, o10 + ch, o11 + ch};
+              const float ws[4] = {w00, w01, w10, w11};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float4 lo = make_float4(ws[k] * g[0], ws[k] * g[1], ws[k] * g[2], ws[k] * g[3]);
+                const float4 hi = make_float4(ws[k] * g[4], ws[k] * g[5], ws[k] * g[6], ws[k] * g[7]);
+                if (RUN) {
+                  if (rvalid[k] && raddr[k] == offs[k]) {
+                    racc[k][0].x += lo.x; racc[k][0].y += lo.y; racc[k][0].z += lo.z; racc[k][0].w += lo.w;
+                    racc[k][1].x += hi.x; racc[k][1].y += hi.y; racc[k][1].z += hi.z; racc[k][1].w += hi.w;
+                  } else {
+                    if (rvalid[k]) { red_add_v4(d_in + raddr[k], racc[k][0]); red_add_v4(d_in + raddr[k] + 4, racc[k][1]); }
+                    racc[k][0] = lo; racc[k][1] = hi; raddr[k] = offs[k]; rvalid[k] = true;
+                  }
+                } else {
+                  red_add_v4(d_in + offs[k], lo);
+                  red_add_v4(d_in + offs[k] + 4, hi);
+                }
+              }
+            }
+          } else if (VEC == 4) {
             float4 g = ld4<G>(d_out + pix * C + ch);
             float4 v00 = ld4<T>(in + o00 + ch), v01 = ld4<T>(in + o01 + ch);
             float4 v10 = ld4<T>(in + o10 + ch), v11 = ld4<T>(in + o11 + ch);
@@ -277,10 +319,10 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
                 for (int k = 0; k < 4; ++k) {
                   const float4 val = make_float4(ws[k] * g.x, ws[k] * g.y, ws[k] * g.z, ws[k] * g.w);
                   if (rvalid[k] && raddr[k] == offs[k]) {
-                    racc[k].x += val.x; racc[k].y += val.y; racc[k].z += val.z; racc[k].w += val.w;
+                    racc[k][0].x += val.x; racc[k][0].y += val.y; racc[k][0].z += val.z; racc[k][0].w += val.w;
                   } else {
-                    if (rvalid[k]) red_add_v4(d_in + raddr[k], racc[k]);
-                    racc[k] = val; raddr[k] = offs[k]; rvalid[k] = true;
+                    if (rvalid[k]) red_add_v4(d_in + raddr[k], racc[k][0]);
+                    racc[k][0] = val; raddr[k] = offs[k]; rvalid[k] = true;
                   }
                 }
               } else {
@@ -317,7 +359,10 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
     if (RUN) {
 #pragma unroll
       for (int k = 0; k < 4; ++k)
-        if (rvalid[k]) red_add_v4(d_in + raddr[k], racc[k]);
+        if (rvalid[k]) {
+          red_add_v4(d_in + raddr[k], racc[k][0]);
+          if constexpr (VEC == 8) red_add_v4(d_in + raddr[k] + 4, racc[k][1]);
+        }
     }
   }
 }
@@ -359,6 +404,14 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
   sample_bwd_kernel<T, 4, TPP, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
                                                                    d_coords, B, H, W, C)
   const bool run = SRC == SRC_REF_IJ && d_in != nullptr && !getenv("OF_WARP_NO_RUN");
+  // bf16 features + bf16 gradient, C = 64 / 128: 16-byte accesses, 8 / 16 threads per pixel
+  if (sizeof(T) == 2 && sizeof(G) == 2 && run && (C == 64 || C == 128) && !getenv("OF_WARP_NO_VEC8") &&
+      ((((uintptr_t)in | (uintptr_t)d_out) & 15) == 0)) {
+    if (C == 64)
+      sample_bwd_kernel<T, 8, 8, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
+    else
+      sample_bwd_kernel<T, 8, 16, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
+  } else
   if (C % 4 == 0) {
     int cv = C / 4;
     if (run && cv == 32) LRUN(32);

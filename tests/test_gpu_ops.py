@@ -300,7 +300,9 @@ def test_warp_features_bwd_bf16_incoming_gradient(cuda):
         a2, b2 = F.warp_features_bwd(flow, feats, g16.float(), mode=mode)
         # scatter order differs run to run (atomics): compare with an fp32 summation bound
         assert (a1 - a2).abs().max().item() <= 1e-5 * a2.abs().max().item()
-        assert torch.equal(b1, b2)
+        # the bf16-gradient call takes the 16-byte path (8 channels per thread): same products, another fp32
+        # summation order over the channels
+        assert (b1 - b2).abs().max().item() <= 1e-5 * b2.abs().max().item()
 
 
 @pytest.mark.parametrize("dtype", ["f32", "bf16"])
