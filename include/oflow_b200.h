@@ -333,6 +333,11 @@ int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n,
                  int step, float lr, float beta1, float beta2, float eps,
                  float grad_scale, void* stream);
 
+/* Opt-in L2 regulariser: the reference declares kernel_regularizer / bias_regularizer = l2(1e-4)
+ * on the encoder convs (model.py:7,13; resnet/models.py:5,18,23) but train.py never adds model.losses, so the default
+ * step does not call this.  Keras l2(l): grad[i] += 2 l w[i]; *loss (nullable, f32 scalar) += l * sum(w^2). */
+int of_l2_regularizer(const float* w, float* grad, size_t n, float l2, float* loss, void* stream);
+
 /* ---- collectives (NCCL over NVLink; nothing in the reference) --------------
  * One communicator per process (rank == GPU).  unique_id is the 128-byte
  * ncclUniqueId produced by of_comm_unique_id() on rank 0 and shipped to the

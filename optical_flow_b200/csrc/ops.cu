@@ -214,7 +214,39 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// ---- opt-in L2 regulariser (model.py:7,13 / resnet/models.py:5,18,23: declared with l2(1e-4) on the encoder convs'
+// kernels and biases, but train.py never adds model.losses - SURVEY F6; off by default) ----------------------------
+// Keras l2(l): penalty = l * sum(w^2)  ->  grad += 2 l w, loss += l * sum(w^2)
+__global__ void __launch_bounds__(256) l2_regularizer_kernel(const float* __restrict__ w, float* __restrict__ grad,
+                                                             size_t n, float l2, float* __restrict__ loss) {
+  float acc = 0.f;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const float v = w[e];
+    grad[e] += 2.0f * l2 * v;
+    acc += v * v;
+  }
+  if (loss == nullptr) return;
+  __shared__ float sm[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += sm[i];
+    atomicAdd(loss, l2 * t);
+  }
+}
+
 extern "C" {
+
+int of_l2_regularizer(const float* w, float* grad, size_t n, float l2, float* loss, void* stream) {
+  OF_REQUIRE(w && grad, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(n > 0, OF_ERR_SHAPE, "empty tensor");
+  size_t blocks = (n + 255) / 256;
+  if (blocks > (size_t)OF_NUM_SMS * 4) blocks = (size_t)OF_NUM_SMS * 4;
+  l2_regularizer_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(w, grad, n, l2, loss);
+  return of_launch_check("l2_regularizer_kernel");
+}
 
 int of_resize_bilinear(const float* in, float* out, int B, int H, int W, int C, int out_h, int out_w,
                        void* stream) {

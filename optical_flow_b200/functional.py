@@ -307,6 +307,14 @@ def adam_step(param, grad, m, v, step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-7
                                   L.stream_ptr()), "of_adam_step")
 
 
+def l2_regularizer(param, grad, l2, loss=None):
+    """Keras ``l2(l)`` on one tensor (opt-in): grad += 2 l w; loss (0-d / 1-element f32 tensor) += l sum(w^2)."""
+    assert param.dtype == grad.dtype == torch.float32 and param.numel() == grad.numel()
+    assert param.is_contiguous() and grad.is_contiguous()
+    L.check(L.load().of_l2_regularizer(L.ptr(param), L.ptr(grad), param.numel(), float(l2), L.ptr(loss), L.stream_ptr()),
+            "of_l2_regularizer")
+
+
 # ------------------------------------------- depth / pose re-projection (8f rank 3) --
 
 def _f32(shape, like):

@@ -26,11 +26,22 @@ nepochs = 20                # train.py:25
 learning_rate = 1e-4        # train.py:34
 
 
+def regularized_parameters(specs):
+    """Names of the tensors the reference attaches l2(l2_reg) to: kernel and bias of the stem (model.py:12-13) and of
+    every residual block's conv1 / conv2 (resnet/models.py:17-23); not the shortcuts, BN or the decoder."""
+    return [n for n in specs
+            if (n.startswith("conv1/") or n.split("/")[0].endswith(("_conv1", "_conv2"))) and not n.startswith("flow")
+            and n.endswith(("/kernel", "/bias"))]
+
+
 class Trainer:
     def __init__(self, height=img_height, width=img_width, pretrained_weights_path=None, lr=learning_rate,
-                 conv_mode="bf16", warp_mode="ref_ij", comm=None, seed=42):
+                 conv_mode="bf16", warp_mode="ref_ij", comm=None, seed=42, apply_l2=False, l2_reg=1e-4):
         """``comm``: None (single replica) or a parallel.CAbiComm / parallel.TorchDistComm; every
-        replica must be built with the same ``seed`` so the weights start identical."""
+        replica must be built with the same ``seed`` so the weights start identical.
+        ``apply_l2`` (opt-in, default off = the reference's behaviour): add the L2 penalty the reference
+        DECLARES on the encoder convs' kernels and biases (model.py:7,13; resnet/models.py:5,18,23) but never adds to
+        its loss (train.py:50-55 ignores model.losses)."""
         self.flow_net = build_flow_net(height, width, pretrained_weights_path, conv_mode=conv_mode,
                                        warp_mode=warp_mode, seed=seed)
         self.loss_layer = LossLayer(warp_mode=warp_mode)
@@ -38,6 +49,7 @@ class Trainer:
         self.step = 0
         self.comm = comm
         self.world_size = comm.world_size if comm is not None else 1
+        self.apply_l2, self.l2_reg = bool(apply_l2), float(l2_reg)
 
     @property
     def trainable_weights(self):
@@ -48,6 +60,10 @@ class Trainer:
         flows = self.flow_net(batch_imgs)
         loss_value = self.loss_layer(batch_imgs, flows)            # also yields d loss / d flow_s
         self.flow_net.backward(self.loss_layer.d_flows)
+        if self.apply_l2:
+            st = self.flow_net.store
+            for name in regularized_parameters(st.specs):
+                F.l2_regularizer(st.p[name], st.g[name], self.l2_reg, loss_value)
         return loss_value, flows
 
     def apply_gradients(self):

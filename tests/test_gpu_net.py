@@ -127,3 +127,32 @@ def test_save_load_weights_roundtrip(cuda, tmp_path):
     assert not torch.equal(net.store.flat, net2.store.flat)
     net2.load_weights(path)
     assert torch.equal(net.store.flat, net2.store.flat)
+
+
+def test_opt_in_l2_regularizer(cuda, small_case):
+    """off by default (the reference never adds model.losses); with apply_l2 the penalty the
+    reference DECLARES (l2(1e-4) on the encoder convs' kernels and biases) adds exactly 2*l*w to those gradients,
+    nothing elsewhere, and l*sum(w^2) to the loss."""
+    from optical_flow_b200.train import Trainer, regularized_parameters
+    imgs = torch.tensor(small_case["imgs"], device=cuda)
+    out = {}
+    for flag in (False, True):
+        tr = Trainer(small_case["H"], small_case["W"], None, conv_mode="fp32", apply_l2=flag)
+        tr.flow_net.store.load_numpy(small_case["params"], small_case["stats"])
+        loss_value, _ = tr.forward_backward(imgs)
+        out[flag] = (loss_value.item(), {n: tr.flow_net.store.g[n].detach().cpu().numpy().copy() for n in tr.flow_net.store.specs})
+    names = set(regularized_parameters(small_case["params"].keys()))
+    assert len(names) == 26 and "conv1/kernel" in names and "layer3_block_1_shortcut/kernel" not in names
+    assert not any(n.startswith("flow") or "_bn" in n for n in names)
+    penalty = 0.0
+    for n, g0 in out[False][1].items():
+        g1 = out[True][1][n]
+        w = small_case["params"][n]
+        if n in names:
+            penalty += 1e-4 * float((w.astype(np.float64) ** 2).sum())
+            exp = g0 + np.float32(2e-4) * w
+            assert np.abs(g1 - exp).max() <= 1e-6 * max(np.abs(exp).max(), 1e-30) + 1e-9, n
+        else:
+            # atomics-free fp32 path: the untouched gradients are reproduced by the second run
+            assert np.abs(g1 - g0).max() <= 1e-5 * max(np.abs(g0).max(), 1e-30), n
+    assert abs((out[True][0] - out[False][0]) - penalty) <= 1e-4 * penalty + 1e-6
