@@ -454,7 +454,10 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int splits = OF_NUM_SMS / jobs;
   // N-stacked, several input chunks, Cout <= 64: 256 TMEM columns and a 28 KB stage - TWO CTAs fit an SM and fill
   // each other's bubbles (96->64 at N8 192x640: 198 -> 150 us)
-  const bool two_per_sm = P.nstack && !P.nstack_one && P.n_chunks == 1 && !getenv("OF_WG_NO_2CTA");
+  // (also the stem's strided-view wgrad: its overlapping-window boxes fill shared memory at ~20 B/clk per CTA)
+  const int acc_cols = P.nstack ? tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0) : (tpp + (c->db ? 1 : 0)) * P.n_mma;
+  const bool two_per_sm = ((P.nstack && !P.nstack_one && P.n_chunks == 1) || (view && acc_cols <= 256)) &&
+                          !getenv("OF_WG_NO_2CTA");
   if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
   if (const char* e = getenv("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
   if (splits > P.ktiles) splits = P.ktiles;
@@ -466,7 +469,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
-  if (two_per_sm && P.stages > 3) P.stages = 3;
+  if (two_per_sm) { int cap = (100 * 1024) / P.stage_bytes; if (cap < 2) cap = 2; if (P.stages > cap) P.stages = cap; }
   if (const char* e = getenv("OF_WG_STAGES")) { int v = atoi(e); if (v >= 1 && v < P.stages) P.stages = v; }
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
