@@ -64,6 +64,8 @@ struct WgradParams {
   // (kw0 | kw1) and (kw2 | junk); otherwise a job is (M tile, kw) with one accumulator per 64-column dy chunk
   // (Cout 96 / 128: two dy slabs, two N = 192 MMAs per K slice instead of three N = Cout ones: -12..15 %).
   int nstack, nstack_one;
+  // nstack_one split over two jobs ((kw0 | kw1) and (kw2 | junk)): 256 TMEM columns each, so TWO CTAs fit an SM
+  int one_split;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -106,7 +108,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
   const int k_begin = blockIdx.y * P.ktiles_per_split;
   const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
-  const int a_bytes = P.nstack ? (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES
+  const int a_bytes = P.nstack ? (P.nstack_one ? (P.one_split ? (tap0 == 0 ? 2 : 1) : 3) : 2) * WG_CHUNK_BYTES
                       : P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
   const int tx_bytes = a_bytes + (P.nstack ? P.n_chunks * P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
 
@@ -121,9 +123,10 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
         if (P.nstack) {
-          for (int c = 0; c < (P.nstack_one ? 3 : 2); ++c) {
+          const int nbox = P.nstack_one ? (P.one_split ? (tap0 == 0 ? 2 : 1) : 3) : 2;
+          for (int c = 0; c < nbox; ++c) {
             const int chunk = P.nstack_one ? 0 : mt * 2 + c;
-            const int kw = P.nstack_one ? c : tap0;
+            const int kw = P.nstack_one ? (P.one_split ? tap0 + c : c) : tap0;
             const int cm = P.chunk_map[chunk];
             const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
             int cc = cm < 0 ? (1 << 20) : P.chunk_c0[chunk];
@@ -244,7 +247,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         const bool rok = P.chunk_map[chunk] >= 0 && rcn < P.chunk_cnt[chunk];
         const int cin = P.chunk_ci[chunk] + rcn;
         for (int a = 0; a < ntaps; ++a) {
-          const int kw = P.nstack_one ? 2 * a + (row >> 6) : tap0;
+          const int kw = P.nstack_one ? (P.one_split ? tap0 : 2 * a) + (row >> 6) : tap0;
           const bool valid = rok && kw < 3;
           const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * P.n_chunks * 192);
           for (int c0 = 0; c0 < P.n_chunks * 192; c0 += 16) {
@@ -385,6 +388,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
               P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_NSTACK"))
                  ? 1 : 0;
   P.nstack_one = (P.nstack && x_chunks == 1) ? 1 : 0;
+  P.one_split = (P.nstack_one && P.n_chunks == 1 && !getenv("OF_WG_NO_ONE_SPLIT")) ? 1 : 0;
   if (P.nstack) { P.slab = 0; P.slab2 = 0; }
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
@@ -432,9 +436,9 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int m_tiles = (nch + 1) / 2;
   int jobs = 0;
   if (P.nstack) {
-    tpp = P.nstack_one ? 2 : 1;
+    tpp = (P.nstack_one && !P.one_split) ? 2 : 1;
     for (int mt = 0; mt < m_tiles; ++mt)
-      for (int kw = 0; kw < (P.nstack_one ? 1 : 3); ++kw) {
+      for (int kw = 0; kw < (P.nstack_one ? (P.one_split ? 4 : 1) : 3); kw += (P.one_split ? 2 : 1)) {
         OF_REQUIRE(jobs < WG_MAX_JOBS, OF_ERR_SHAPE, "too many wgrad jobs");
         P.job_mt[jobs] = mt; P.job_tap0[jobs] = kw; P.job_ntaps[jobs] = tpp;
         ++jobs;
@@ -456,7 +460,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   // each other's bubbles (96->64 at N8 192x640: 198 -> 150 us)
   // (also the stem's strided-view wgrad: its overlapping-window boxes fill shared memory at ~20 B/clk per CTA)
   const int acc_cols = P.nstack ? tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0) : (tpp + (c->db ? 1 : 0)) * P.n_mma;
-  const bool two_per_sm = ((P.nstack && !P.nstack_one && P.n_chunks == 1) || (view && acc_cols <= 256)) &&
+  const bool two_per_sm = ((P.nstack && (!P.nstack_one || P.one_split) && P.n_chunks == 1) || (view && acc_cols <= 256)) &&
                           !getenv("OF_WG_NO_2CTA");
   if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
   if (const char* e = getenv("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
@@ -466,7 +470,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
-  if (P.nstack) P.stage_bytes = (P.nstack_one ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
+  if (P.nstack) P.stage_bytes = ((P.nstack_one && !P.one_split) ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   if (two_per_sm) { int cap = (100 * 1024) / P.stage_bytes; if (cap < 2) cap = 2; if (P.stages > cap) P.stages = cap; }
