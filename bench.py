@@ -102,6 +102,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def mark(self):
+        """Start of the timed region: the sampler was started during the warm-up (nvidia-smi needs a few hundred
+        ms before its first line - longer than a 0.2 s timed region); only rows from here on are reported."""
+        self.rows = []
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -112,7 +117,8 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm),
+                "window": "timed region + the e2e timed region that follows it (same step, under load)"}
 
 
 # ------------------------------------------------------------------ CPU baselines --
@@ -334,11 +340,11 @@ def bench_loss(args, dev, world, rank):
             graph.replay()
 
     steps = max(args.steps // nsets, 1) * nsets
-    run_timed(nsets * 3)
     clocks = ClockSampler(dev.index or 0)
     clocks.start()
+    run_timed(nsets * 3)
+    clocks.mark()
     ms = _timed(torch, dist, world, run_timed, steps)
-    ck = clocks.stop()
     per = ms / steps
     value = world * B / (per * 1e-3)
     alg = loss_algorithmic_bytes(B, H, W)
@@ -364,6 +370,7 @@ def bench_loss(args, dev, world, rank):
 
     run_e2e(2)
     ms_e = _timed(torch, dist, world, run_e2e, args.steps)
+    ck = clocks.stop()
     fl_bytes = sum(f.numel() * 4 for f in h_flows)
     e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
            "h2d_bytes_per_step": h_imgs.numel() * 4 + fl_bytes, "d2h_bytes_per_step": fl_bytes + 4}
@@ -430,12 +437,12 @@ def bench_train(args, dev, world, rank):
         for i in range(n):
             loss, _ = tr.train_step(batches[i % nsets], i)
 
-    run(max(args.warmup, 3))
-    launches_before = L.load().of_launch_count()
     clocks = ClockSampler(dev.index or 0)
     clocks.start()
+    run(max(args.warmup, 3))
+    launches_before = L.load().of_launch_count()
+    clocks.mark()
     ms = _timed(torch, dist, world, run, args.steps)
-    ck = clocks.stop()
     launches = L.load().of_launch_count() - launches_before
     per = ms / args.steps
     value = world * B / (per * 1e-3)
@@ -457,6 +464,7 @@ def bench_train(args, dev, world, rank):
 
     run_e2e(2)
     ms_e = _timed(torch, dist, world, run_e2e, args.steps)
+    ck = clocks.stop()
     d_in = batches[0]
     e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
            "h2d_bytes_per_step": d_in.numel() * 4, "d2h_bytes_per_step": 4}
