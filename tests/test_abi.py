@@ -55,3 +55,16 @@ def test_no_product_import_of_oracle():
             if f.endswith(".py"):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), os.path.join(dirpath, f)
+
+
+def test_regularized_parameter_names_follow_the_reference():
+    """Host logic of the opt-in L2 term: the reference attaches l2(1e-4) to kernel AND bias of the stem (model.py:12-13)
+    and of each residual block's conv1 / conv2 (resnet/models.py:17-23) - 13 convs, not the shortcuts, BN or decoder."""
+    from optical_flow_b200.params import decoder_param_specs, encoder_param_specs
+    from optical_flow_b200.train import regularized_parameters
+    specs = dict(encoder_param_specs())
+    specs.update(decoder_param_specs())
+    names = regularized_parameters(specs)
+    assert len(names) == 26 and len(set(names)) == 26
+    assert {"conv1/kernel", "conv1/bias", "layer4_block_2_conv2/kernel", "layer3_block_1_conv1/bias"} <= set(names)
+    assert not any("shortcut" in n or "_bn" in n or n.startswith(("flow", "layer1_bn")) for n in names)
