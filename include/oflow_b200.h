@@ -333,6 +333,29 @@ int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n,
                  int step, float lr, float beta1, float beta2, float eps,
                  float grad_scale, void* stream);
 
+/* ---- training-mode BatchNormalization (OPT-IN) --------------
+ * The reference's step runs layers.BatchNormalization (model.py:14; resnet/models.py:19,24) in inference mode
+ * (SURVEY F5), which is what of_bn_fold_* implement; these four passes are the batch-statistics variant.
+ * x / y / dy / dx: (npix, C) NHWC rows, dtype f32 or bf16, C % 4 == 0 and C / 4 dividing 256; all statistics f32.
+ *   stats:       sum[c] = sum_p x, sumsq[c] = sum_p x^2 (zeroed by the callee).  For cross-replica (sync) BN the
+ *                caller all-reduces both buffers and passes the GLOBAL count below.
+ *   apply:       mean = sum / count, var = sumsq / count - mean^2 (biased); y = act(gamma (x - mean) / sqrt(var + eps)
+ *                + beta); moving_* (nullable pair) <- moving * momentum + batch * (1 - momentum), the variance
+ *                unbiased (count / (count - 1)) like TF's fused kernel.  Keras defaults: eps 1e-3, momentum 0.99.
+ *   bwd_reduce:  dy' = dy * act'(y); dsum[c] = sum_p dy' (= dbeta), dsum_xhat[c] = sum_p dy' * xhat (= dgamma)
+ *                (zeroed by the callee; all-reduce them as well for sync BN).
+ *   bwd_apply:   dx = gamma / sqrt(var + eps) * (dy' - dsum / count - xhat * dsum_xhat / count). */
+int of_bn_train_stats(const void* x, float* sum, float* sumsq, size_t npix, int C, int dtype, void* stream);
+int of_bn_train_apply(const void* x, const float* sum, const float* sumsq, float count, const float* gamma,
+                      const float* beta, float eps, int act, void* y, float* moving_mean, float* moving_var,
+                      float momentum, size_t npix, int C, int dtype, void* stream);
+int of_bn_train_bwd_reduce(const void* x, const void* y, const void* dy, const float* sum, const float* sumsq,
+                           float count, float eps, int act, float* dsum, float* dsum_xhat, size_t npix, int C,
+                           int dtype, void* stream);
+int of_bn_train_bwd_apply(const void* x, const void* y, const void* dy, const float* sum, const float* sumsq,
+                          float count, const float* gamma, float eps, int act, const float* dsum,
+                          const float* dsum_xhat, void* dx, size_t npix, int C, int dtype, void* stream);
+
 /* Opt-in L2 regulariser: the reference declares kernel_regularizer / bias_regularizer = l2(1e-4)
  * on the encoder convs (model.py:7,13; resnet/models.py:5,18,23) but train.py never adds model.losses, so the default
  * step does not call this.  Keras l2(l): grad[i] += 2 l w[i]; *loss (nullable, f32 scalar) += l * sum(w^2). */

@@ -136,6 +136,10 @@ PROTOTYPES = {
     "of_bn_fold_fwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_bn_fold_bwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
+    "of_bn_train_stats": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),
+    "of_bn_train_apply": (_i, [_vp, _vp, _vp, _f, _vp, _vp, _f, _i, _vp, _vp, _vp, _f, _sz, _i, _i, _vp]),
+    "of_bn_train_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _sz, _i, _i, _vp]),
+    "of_bn_train_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _i, _i, _vp]),
     "of_l2_regularizer": (_i, [_vp, _vp, _sz, _f, _vp, _vp]),
     "of_comm_unique_id": (_i, [_vp]),
     "of_comm_init": (_i, [_vp, _i, _i, _pp]),

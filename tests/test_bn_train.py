@@ -1,0 +1,122 @@
+"""Training-mode BatchNormalization (opt-in): the four CUDA passes against torch-CPU
+F.batch_norm(training=True) + autograd (the semantics of Keras' BatchNormalization(training=True): biased batch
+variance in the normalisation, momentum 0.99, epsilon 1e-3), and the cross-replica form against the full batch."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def reference(x, gamma, beta, g, act, eps=1e-3):
+    xt = torch.tensor(x, dtype=torch.float64, requires_grad=True)
+    gt = torch.tensor(gamma, dtype=torch.float64, requires_grad=True)
+    bt = torch.tensor(beta, dtype=torch.float64, requires_grad=True)
+    y = torch.nn.functional.batch_norm(xt.permute(0, 3, 1, 2), None, None, gt, bt, True, 0.0, eps).permute(0, 2, 3, 1)
+    if act == 1:
+        y = torch.relu(y)
+    elif act == 2:
+        y = torch.nn.functional.leaky_relu(y, 0.3)
+    y.backward(torch.tensor(g, dtype=torch.float64))
+    return y.detach().numpy(), xt.grad.numpy(), gt.grad.numpy(), bt.grad.numpy()
+
+
+def close(a, b, tol):
+    a = a.detach().float().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+    err = np.abs(a.astype(np.float64) - b).max()
+    assert err <= tol * max(np.abs(b).max(), 1e-30), (err, np.abs(b).max())
+
+
+@pytest.mark.parametrize("shape,act", [((2, 6, 10, 64), 1), ((3, 17, 9, 128), 0), ((1, 5, 7, 256), 2), ((16, 96, 320, 64), 1)])
+def test_bn_train_fwd_bwd_fp32(cuda, shape, act):
+    from optical_flow_b200.resnet.batchnorm import BatchNormalizationTraining
+    r = np.random.default_rng(sum(shape))
+    x = (r.standard_normal(shape) * 1.7 + 0.4).astype(np.float32)
+    g = r.standard_normal(shape).astype(np.float32)
+    C = shape[-1]
+    gamma, beta = (1 + 0.2 * r.standard_normal(C)).astype(np.float32), (0.1 * r.standard_normal(C)).astype(np.float32)
+    bn = BatchNormalizationTraining(C, act=act, device=cuda)
+    bn.gamma.copy_(torch.tensor(gamma)); bn.beta.copy_(torch.tensor(beta))
+    y = bn(torch.tensor(x, device=cuda))
+    dx = bn.backward(torch.tensor(g, device=cuda))
+    ey, edx, eg, eb = reference(x, gamma, beta, g, act)
+    close(y, ey, 2e-5)
+    close(dx, edx, 1e-4)
+    close(bn.d_gamma, eg, 1e-4)
+    close(bn.d_beta, eb, 1e-4)
+    # moving statistics: one Keras update from (0, 1) with momentum 0.99, unbiased batch variance (fused kernel)
+    n = x.size // C
+    m, v = x.reshape(-1, C).astype(np.float64).mean(0), x.reshape(-1, C).astype(np.float64).var(0)
+    close(bn.moving_mean, 0.01 * m, 1e-4)
+    close(bn.moving_variance, 0.99 + 0.01 * v * n / (n - 1), 1e-4)
+
+
+def test_bn_train_bf16(cuda):
+    from optical_flow_b200.resnet.batchnorm import BatchNormalizationTraining
+    r = np.random.default_rng(5)
+    shape = (2, 12, 20, 64)
+    x = torch.tensor(r.standard_normal(shape).astype(np.float32)).bfloat16()
+    g = torch.tensor(r.standard_normal(shape).astype(np.float32)).bfloat16()
+    bn = BatchNormalizationTraining(64, act=1, device=cuda)
+    y = bn(x.to(cuda))
+    dx = bn.backward(g.to(cuda))
+    ey, edx, eg, eb = reference(x.float().numpy(), np.ones(64, np.float32), np.zeros(64, np.float32), g.float().numpy(), 1)
+    close(y, ey, 2 ** -7)
+    close(dx, edx, 2 ** -6)
+    close(bn.d_gamma, eg, 2e-2)
+
+
+class _TwoReplicaSum:
+    """Stand-in communicator for two replicas living in one process: the 'all-reduce' adds the other replica's
+    buffer (captured from a first pass)."""
+    world_size = 2
+
+    def __init__(self):
+        self.other = []      # buffers of the other replica, in call order
+        self.k = 0
+
+    def allreduce_sum_(self, t):
+        t.add_(self.other[self.k])
+        self.k += 1
+
+
+def test_bn_train_cross_replica_equals_full_batch(cuda):
+    """SURVEY 8c (12) for sync BN: two replicas with half the batch each, statistics and gradient sums exchanged,
+    give the full-batch output and gradients."""
+    from optical_flow_b200.resnet.batchnorm import BatchNormalizationTraining
+    r = np.random.default_rng(9)
+    shape = (4, 10, 12, 64)
+    x = (r.standard_normal(shape) + 0.3).astype(np.float32)
+    g = r.standard_normal(shape).astype(np.float32)
+    ey, edx, eg, eb = reference(x, np.ones(64, np.float32), np.zeros(64, np.float32), g, 1)
+    halves = [(torch.tensor(x[:2], device=cuda), torch.tensor(g[:2], device=cuda)),
+              (torch.tensor(x[2:], device=cuda), torch.tensor(g[2:], device=cuda))]
+    # pass 1: each replica alone, to capture the buffers its peer would contribute
+    local = []
+    for xh, gh in halves:
+        bn = BatchNormalizationTraining(64, act=1, device=cuda)
+        bn(xh)
+        local.append(bn._stats.clone())
+    outs = []
+    for k, (xh, gh) in enumerate(halves):
+        comm = _TwoReplicaSum()
+        bn = BatchNormalizationTraining(64, act=1, device=cuda, comm=comm)
+        comm.other = [local[1 - k]]
+        y = bn(xh)
+        outs.append((bn, y, gh, comm))
+    # gradient sums of each replica (computed with the GLOBAL statistics), then exchanged
+    sums = []
+    for bn, y, gh, comm in outs:
+        probe = BatchNormalizationTraining(64, act=1, device=cuda)
+        probe._stats.copy_(bn._stats); probe._saved = bn._saved
+        saved_comm, probe.comm = probe.comm, None
+        probe.backward(gh)
+        sums.append((probe.d_beta.clone(), probe.d_gamma.clone()))
+    for k, (bn, y, gh, comm) in enumerate(outs):
+        comm.other = [local[1 - k], sums[1 - k][0], sums[1 - k][1]]
+        comm.k = 1
+        dx = bn.backward(gh)
+        close(y, ey[2 * k:2 * k + 2], 2e-5)
+        close(dx, edx[2 * k:2 * k + 2], 1e-4)
+        close(bn.d_gamma, eg, 1e-4)
+        close(bn.d_beta, eb, 1e-4)
