@@ -44,6 +44,10 @@ int of_version(void);
 const char* of_last_error(void);
 /* number of CUDA kernels this library has launched in this process (bench evidence) */
 unsigned long long of_launch_count(void);
+/* Select a kernel variant by name (e.g. "OF_CV_NO_TC" = "1": SIMT cost volume instead of the tcgen05 one;
+ * "OF_LOSS_GENERIC": direct-gather loss kernel).  value NULL unsets.  Process-wide, not thread-safe against
+ * concurrent launches; meant for tests and tuning scripts.  The shipped library reads NO environment variables. */
+int of_set_option(const char* name, const char* value);
 
 /* ---- sampler ------------------------------------------------------------
  * transformations.py:85-129 bilinear_interpolation (+ :70-81 gather).
@@ -337,23 +341,30 @@ int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n,
  * The reference's step runs layers.BatchNormalization (model.py:14; resnet/models.py:19,24) in inference mode
  * (SURVEY F5), which is what of_bn_fold_* implement; these four passes are the batch-statistics variant.
  * x / y / dy / dx: (npix, C) NHWC rows, dtype f32 or bf16, C % 4 == 0 and C / 4 dividing 256; all statistics f32.
- *   stats:       sum[c] = sum_p x, sumsq[c] = sum_p x^2 (zeroed by the callee).  For cross-replica (sync) BN the
- *                caller all-reduces both buffers and passes the GLOBAL count below.
- *   apply:       mean = sum / count, var = sumsq / count - mean^2 (biased); y = act(gamma (x - mean) / sqrt(var + eps)
- *                + beta); moving_* (nullable pair) <- moving * momentum + batch * (1 - momentum), the variance
- *                unbiased (count / (count - 1)) like TF's fused kernel.  Keras defaults: eps 1e-3, momentum 0.99.
+ *   Every function takes `shift` (nullable = 0), a per-channel offset the sums are taken about; the layer passes a
+ *   snapshot of its moving mean (identical on every replica), which removes the E[x^2] - E[x]^2 cancellation.
+ *   stats:       sum[c] = sum_p (x - shift), sumsq[c] = sum_p (x - shift)^2.  Deterministic: per-CTA partials in
+ *                `workspace` (of_bn_train_workspace_bytes(C), 16-byte aligned) are added in a fixed order by the last
+ *                CTA - no floating-point atomics.  For cross-replica (sync) BN the caller all-reduces both buffers and
+ *                passes the GLOBAL count below.
+ *   apply:       mean = shift + sum / count, var = sumsq / count - (sum / count)^2 (biased); y = act(gamma (x - mean) /
+ *                sqrt(var + eps) + beta); moving_* (nullable pair) <- moving * momentum + batch * (1 - momentum), the
+ *                variance unbiased (count / (count - 1)) like TF's fused kernel.  Keras defaults: eps 1e-3, momentum 0.99.
+ *                `shift` must not alias moving_mean.
  *   bwd_reduce:  dy' = dy * act'(y); dsum[c] = sum_p dy' (= dbeta), dsum_xhat[c] = sum_p dy' * xhat (= dgamma)
- *                (zeroed by the callee; all-reduce them as well for sync BN).
+ *                (same deterministic two-stage sum; all-reduce them as well for sync BN).
  *   bwd_apply:   dx = gamma / sqrt(var + eps) * (dy' - dsum / count - xhat * dsum_xhat / count). */
-int of_bn_train_stats(const void* x, float* sum, float* sumsq, size_t npix, int C, int dtype, void* stream);
-int of_bn_train_apply(const void* x, const float* sum, const float* sumsq, float count, const float* gamma,
-                      const float* beta, float eps, int act, void* y, float* moving_mean, float* moving_var,
-                      float momentum, size_t npix, int C, int dtype, void* stream);
+size_t of_bn_train_workspace_bytes(int C);
+int of_bn_train_stats(const void* x, const float* shift, float* sum, float* sumsq, size_t npix, int C, int dtype,
+                      void* workspace, void* stream);
+int of_bn_train_apply(const void* x, const float* sum, const float* sumsq, const float* shift, float count,
+                      const float* gamma, const float* beta, float eps, int act, void* y, float* moving_mean,
+                      float* moving_var, float momentum, size_t npix, int C, int dtype, void* stream);
 int of_bn_train_bwd_reduce(const void* x, const void* y, const void* dy, const float* sum, const float* sumsq,
-                           float count, float eps, int act, float* dsum, float* dsum_xhat, size_t npix, int C,
-                           int dtype, void* stream);
+                           const float* shift, float count, float eps, int act, float* dsum, float* dsum_xhat,
+                           size_t npix, int C, int dtype, void* workspace, void* stream);
 int of_bn_train_bwd_apply(const void* x, const void* y, const void* dy, const float* sum, const float* sumsq,
-                          float count, const float* gamma, float eps, int act, const float* dsum,
+                          const float* shift, float count, const float* gamma, float eps, int act, const float* dsum,
                           const float* dsum_xhat, void* dx, size_t npix, int C, int dtype, void* stream);
 
 /* Opt-in L2 regulariser: the reference declares kernel_regularizer / bias_regularizer = l2(1e-4)

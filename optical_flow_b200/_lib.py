@@ -12,7 +12,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liboflow_b200.so")
+# OF_PROFILE_LIB=1 selects the -DOF_PROFILE_HOOKS build (scripts/ only; tests, smoke and bench use the shipped library)
+LIB_PATH = os.path.join(_HERE, "liboflow_b200_prof.so" if os.environ.get("OF_PROFILE_LIB") == "1" else "liboflow_b200.so")
 
 OF_F32, OF_BF16 = 0, 1
 OF_MASK_BITS = 2      # of_tc_conv.mask_dtype: sign-bit mask written by a conv_tc3 fprop (sign_out)
@@ -92,6 +93,7 @@ PROTOTYPES = {
     "of_version": (_i, []),
     "of_last_error": (C.c_char_p, []),
     "of_launch_count": (C.c_ulonglong, []),
+    "of_set_option": (C.c_int, [C.c_char_p, C.c_char_p]),
     "of_bilinear_sample_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_bilinear_sample_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_warp_features_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
@@ -136,10 +138,11 @@ PROTOTYPES = {
     "of_bn_fold_fwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_bn_fold_bwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
-    "of_bn_train_stats": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),
-    "of_bn_train_apply": (_i, [_vp, _vp, _vp, _f, _vp, _vp, _f, _i, _vp, _vp, _vp, _f, _sz, _i, _i, _vp]),
-    "of_bn_train_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _sz, _i, _i, _vp]),
-    "of_bn_train_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _i, _i, _vp]),
+    "of_bn_train_workspace_bytes": (_sz, [_i]),
+    "of_bn_train_stats": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _i, _vp, _vp]),
+    "of_bn_train_apply": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _f, _i, _vp, _vp, _vp, _f, _sz, _i, _i, _vp]),
+    "of_bn_train_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _sz, _i, _i, _vp, _vp]),
+    "of_bn_train_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _i, _i, _vp]),
     "of_l2_regularizer": (_i, [_vp, _vp, _sz, _f, _vp, _vp]),
     "of_comm_unique_id": (_i, [_vp]),
     "of_comm_init": (_i, [_vp, _i, _i, _pp]),
@@ -167,6 +170,22 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+class option:
+    """``with option("OF_CV_NO_TC", "1"): ...`` - select a kernel variant for the duration of the block
+    (of_set_option; the library reads no environment variables)."""
+
+    def __init__(self, name, value="1"):
+        self.name, self.value = name.encode(), None if value is None else str(value).encode()
+
+    def __enter__(self):
+        check(load().of_set_option(self.name, self.value), "of_set_option")
+        return self
+
+    def __exit__(self, *exc):
+        load().of_set_option(self.name, None)
+        return False
 
 
 def check(rc: int, what: str = ""):

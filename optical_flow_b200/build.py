@@ -15,6 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "liboflow_b200.so")
+LIB_PROF = os.path.join(HERE, "liboflow_b200_prof.so")      # -DOF_PROFILE_HOOKS build (profiling scripts only)
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 NVCC_FLAGS = [
@@ -46,22 +47,27 @@ def _deps_mtime():
     return m
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(BUILD, exist_ok=True)
+def build_library(force: bool = False, verbose: bool = False, profile_hooks: bool = False) -> str:
+    """profile_hooks: build liboflow_b200_prof.so with -DOF_PROFILE_HOOKS (environment-variable tuning knobs and the
+    "skip part of the kernel" debug paths; see csrc/common.cuh).  The shipped library has none of them."""
+    build_dir = BUILD + ("_prof" if profile_hooks else "")
+    lib_path = LIB_PROF if profile_hooks else LIB
+    extra = ["-DOF_PROFILE_HOOKS"] if profile_hooks else []
+    os.makedirs(build_dir, exist_ok=True)
     nvcc = _nvcc()
     hdr_m = _deps_mtime()
     jobs = []
     objs = []
     for src in _sources():
         s = os.path.join(CSRC, src)
-        o = os.path.join(BUILD, src[:-3] + ".o")
+        o = os.path.join(build_dir, src[:-3] + ".o")
         objs.append(o)
         if force or not os.path.exists(o) or os.path.getmtime(o) < max(os.path.getmtime(s), hdr_m):
             jobs.append((s, o))
 
     def compile_one(job):
         s, o = job
-        cmd = [nvcc] + NVCC_FLAGS + ["-I", INCLUDE, "-c", s, "-o", o]
+        cmd = [nvcc] + NVCC_FLAGS + extra + ["-I", INCLUDE, "-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = o[:-2] + ".ptxas.log"
         with open(log, "w") as f:
@@ -75,13 +81,13 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
             for s in ex.map(compile_one, jobs):
                 if verbose:
                     print("compiled", os.path.basename(s))
-    if jobs or not os.path.exists(LIB):
-        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart", "-ldl"]
+    if jobs or not os.path.exists(lib_path):
+        cmd = [nvcc, "-shared", "-o", lib_path] + objs + ["-lcudart", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
-    return LIB
+    return lib_path
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose=True))
+    print(build_library(force="--force" in sys.argv, verbose=True, profile_hooks="--profile-hooks" in sys.argv))

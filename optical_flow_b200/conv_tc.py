@@ -238,7 +238,7 @@ def conv2d_wgrad_tc(x, dz, ksize, stride=1, dw=None, db=None, need_bias_grad=Tru
     if need_bias_grad and db is None:
         db = torch.empty((Cout,), dtype=torch.float32, device=dz.device)
     # bias gradient fused into the wgrad launch (ones-operand MMA) when a TMEM accumulator is spare
-    fuse_db = need_bias_grad and (Cout + 15) // 16 * 16 <= 128 and not os.environ.get("OF_WG_NO_BIAS")
+    fuse_db = need_bias_grad and (Cout + 15) // 16 * 16 <= 128
     if fuse_db:
         d.db = db.data_ptr()
     L.check(L.load().of_conv_tc_wgrad(C.byref(d), L.stream_ptr()), "of_conv_tc_wgrad")

@@ -32,6 +32,27 @@ void of_set_error(const char* fmt, ...);
 
 void of_count_launch(void);
 
+// ---- profiling / tuning hooks ------------------------------------------------------------------
+// Kernel-variant knobs (OF_T3_*, OF_LF_*, OF_WG_*, OF_CV_NO_TC, OF_LOSS_GENERIC, OF_NO_PDL, ...) are read from a
+// process-wide option table that only an explicit of_set_option(name, value) call fills (the tests use it to
+// compare two variants of a kernel); the table is empty by default, so the launch paths do no getenv and a stray
+// ENVIRONMENT variable changes nothing.  Environment variables are honoured, and the "skip this part of the
+// kernel" debug paths (P.dbg) exist, ONLY in a library built with -DOF_PROFILE_HOOKS (python -m
+// optical_flow_b200.build --profile-hooks -> liboflow_b200_prof.so); in the shipped library OF_DBG(P) is a
+// constant 0 and those branches are compiled out.
+#include <stdlib.h>
+const char* of_option_get(const char* name);
+#ifdef OF_PROFILE_HOOKS
+static inline const char* of_tune_env(const char* name) {
+  const char* v = of_option_get(name);
+  return v ? v : getenv(name);
+}
+#define OF_DBG(P) ((P).dbg)
+#else
+static inline const char* of_tune_env(const char* name) { return of_option_get(name); }
+#define OF_DBG(P) 0
+#endif
+
 // ---- programmatic dependent launch (PDL) ----------------------------------------------------------
 // The tensor-core kernels are launched with programmatic stream serialization: the next kernel's CTAs may
 // become resident (barrier init, TMEM allocation, tensor-map prefetch) while the previous kernel drains.
@@ -48,7 +69,7 @@ static inline cudaError_t of_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = getenv("OF_NO_PDL") ? 0 : 1;
+  at[0].val.programmaticStreamSerializationAllowed = of_tune_env("OF_NO_PDL") ? 0 : 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }

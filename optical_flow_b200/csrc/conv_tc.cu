@@ -431,7 +431,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   // fill the bubbles of the first; the stage ring is split between them
   int ctas = 512 / P.tmem_cols;
   {
-    const char* e = getenv("OF_TC_CTAS");
+    const char* e = of_tune_env("OF_TC_CTAS");
     const int cap = e ? atoi(e) : 2;
     if (ctas > cap) ctas = cap;
     if (ctas < 1) ctas = 1;

@@ -111,7 +111,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           for (int kc = 0; kc < P.kchunks[s]; ++kc) {
             for (int kw = 0; kw < 3; ++kw) {
               tc::mbar_wait(&a_empty[as], aph ^ 1);
-              if ((P.dbg & 32) && tile != (int)blockIdx.x) {
+              if ((OF_DBG(P) & 32) && tile != (int)blockIdx.x) {
                 tc::mbar_arrive(&a_full[as]);         // profiling only: activation slabs "free"
               } else {
               tc::mbar_expect_tx(&a_full[as], (uint32_t)P.slab_bytes);
@@ -121,9 +121,9 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               if (++as == P.na) { as = 0; aph ^= 1; }
               for (int kh = 0; kh < 3; ++kh) {
                 tc::mbar_wait(&b_empty[bs], bph ^ 1);
-                if ((P.dbg & 8) && tile != (int)blockIdx.x) {
+                if ((OF_DBG(P) & 8) && tile != (int)blockIdx.x) {
                   tc::mbar_arrive(&b_full[bs]);       // profiling only: weight tiles "free" after the first output tile
-                } else if ((P.dbg & 16) && tile != (int)blockIdx.x && kh > 0) {
+                } else if ((OF_DBG(P) & 16) && tile != (int)blockIdx.x && kh > 0) {
                   tc::mbar_arrive(&b_full[bs]);       // profiling only: a third of the weight traffic
                 } else {
                 tc::mbar_expect_tx(&b_full[bs], (uint32_t)(P.n_mma * 128));
@@ -192,7 +192,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       int th_i = r % P.tiles_h; int n = r / P.tiles_h;
       const int h_base = th_i * SH + hh * P.TH, w_base = tw_i * P.TW;
       const int ph = h_base + (row >> P.tw_shift), pw = w_base + (row & (P.TW - 1));
-      const bool valid = ph < P.Ho && pw < P.Wo && !(P.dbg & 1);
+      const bool valid = ph < P.Ho && pw < P.Wo && !(OF_DBG(P) & 1);
       const size_t pix = ((size_t)n * P.Ho + ph) * P.Wo + pw;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((buf * 2 + hh) * P.n_mma);
 
@@ -201,7 +201,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         int rr_ = q * 32 + i * 4 + r_sub;
         int ch_ = h_base + (rr_ >> P.tw_shift), cw_ = w_base + (rr_ & (P.TW - 1));
         cpix = ((size_t)n * P.Ho + ch_) * P.Wo + cw_;
-        return ch_ < P.Ho && cw_ < P.Wo && !(P.dbg & 1);
+        return ch_ < P.Ho && cw_ < P.Wo && !(OF_DBG(P) & 1);
       };
       uint4 mreg[8];
       auto load_mask = [&](int g) {                     // coalesced: 4 pixel rows x 128 B per instruction
@@ -215,7 +215,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                        : make_uint4(0, 0, 0, 0);
         }
       };
-      if (mask_coal && !(P.dbg & 2)) load_mask(0);       // in flight while the accumulator is still being produced
+      if (mask_coal && !(OF_DBG(P) & 2)) load_mask(0);       // in flight while the accumulator is still being produced
       // sign-bit activation mask (16 B / pixel, written by the producing layer's fprop): one load per row
       const bool mask_bits = !COAL && P.E.mask != nullptr && P.E.mask_dtype == OF_MASK_BITS;
       uint64_t mb_lo = 0, mb_hi = 0, sb_lo = 0, sb_hi = 0;
@@ -227,7 +227,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 
       tc::mbar_wait(&tmem_full[buf], use & 1);
       tc::fence_after_sync();
-      if (!(P.dbg & 2)) {
+      if (!(OF_DBG(P) & 2)) {
         // software pipeline over 16-column chunks: the TMEM load of chunk c+1 and the global loads of
         // its add (and row-wise mask) operands are in flight while chunk c is finished
         uint32_t rr[2][16];
@@ -334,7 +334,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], P.E.mask_act);
             }
             // profiling only (dbg 64): all the epilogue math, no global store
-            if (!(P.dbg & 64) || v[0] + v[7] + v[15] == 1.2345e-30f) store16(P.E, pix, c0, v);
+            if (!(OF_DBG(P) & 64) || v[0] + v[7] + v[15] == 1.2345e-30f) store16(P.E, pix, c0, v);
           } else {
             epilogue_store16(P.E, pix, c0, rr[slot]);    // ragged channel tail / unaligned strides: generic path
           }
@@ -392,7 +392,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   const bool view = c->view_w_stride > 0;
   if (view || c->KH != 3 || c->KW != 3 || c->stride != 1 || (c->stride_w > 1) || (c->stride_h > 1)) return 0;
   if (c->n_mma > 128) return 0;                         // 2 halves x 2 buffers x n_mma TMEM columns <= 512
-  if (getenv("OF_CONV_NO_SLAB")) return 0;
+  if (of_tune_env("OF_CONV_NO_SLAB")) return 0;
   Conv3Params P;
   memset(&P, 0, sizeof(P));
   P.num_src = c->num_src;
@@ -427,11 +427,11 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.coal = c->out_dtype == OF_BF16 && (c->out_stride % 8) == 0 && ((uintptr_t)c->out & 15) == 0 && c->n_valid >= 8 &&
            (c->n_valid % 8) == 0 && mask_coal_ok && add_coal_ok;
   {
-    const char* e = getenv("OF_T3_COAL");                 // 1 = always, 2 = only with a mask operand (dgrad)
+    const char* e = of_tune_env("OF_T3_COAL");                 // 1 = always, 2 = only with a mask operand (dgrad)
     const int mode = e ? atoi(e) : 0;
     P.coal = P.coal && (mode == 1 || (mode == 2 && c->mask != nullptr));
   }
-  if (const char* e = getenv("OF_T3_DBG")) P.dbg = atoi(e);
+  if (const char* e = of_tune_env("OF_T3_DBG")) P.dbg = atoi(e);
   const bool bits = c->sign_out != nullptr || (c->mask != nullptr && c->mask_dtype == OF_MASK_BITS);
   if (bits) {
     OF_REQUIRE((c->n_valid % 16) == 0 && c->n_valid <= 128 && (c->out_stride % 8) == 0 &&
@@ -448,7 +448,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes;
   if (P.nb < 4) { P.na = 2; P.nb = (budget - P.na * P.slab_bytes) / P.btile_bytes; }
   if (P.nb > T3_MAX_B) P.nb = T3_MAX_B;
-  if (const char* e = getenv("OF_T3_RINGS")) {            // tuning hook: "na,nb"
+  if (const char* e = of_tune_env("OF_T3_RINGS")) {            // tuning hook: "na,nb"
     int a_ = 0, b_ = 0;
     if (sscanf(e, "%d,%d", &a_, &b_) == 2 && a_ >= 1 && a_ <= T3_MAX_A && b_ >= 3 && b_ <= T3_MAX_B &&
         a_ * P.slab_bytes + b_ * P.btile_bytes <= budget) { P.na = a_; P.nb = b_; }
@@ -460,7 +460,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     const int kch = kb / 64;
     int b_ = (100 * 1024 - stg_bytes - 2 * P.slab_bytes) / P.btile_bytes;
     if (b_ > T3_MAX_B) b_ = T3_MAX_B;
-    const char* e = getenv("OF_T3_2CTA");                  // 0 = never, 1 = every layer with n_mma <= 64
+    const char* e = of_tune_env("OF_T3_2CTA");                  // 0 = never, 1 = every layer with n_mma <= 64
     const bool want = e ? (atoi(e) > 0 && c->n_mma <= 64) : (c->n_mma <= 32 || (c->n_mma <= 64 && kch >= 2));
     if (want && !P.coal && b_ >= 3 && P.m_tiles > OF_NUM_SMS) { two = 1; P.na = 2; P.nb = b_; }
   }

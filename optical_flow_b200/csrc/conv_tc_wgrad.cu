@@ -375,20 +375,20 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int x_chunks = 0;
   for (int s_ = 0; s_ < c->num_src; ++s_) x_chunks += (c->x_valid[s_] + 63) / 64;
   P.slab = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view && x_chunks >= 2 &&
-            (512 - (c->db ? P.n_mma : 0)) / P.n_mma >= 3 && P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_SLAB"))
+            (512 - (c->db ? P.n_mma : 0)) / P.n_mma >= 3 && P.TW >= 8 && P.TW <= 32 && !of_tune_env("OF_WG_NO_SLAB"))
                ? 1 : 0;
   P.slab_bytes = (P.TH + 2) * P.TW * 128;
   if (P.slab) { tpp = 3; passes = 3; }
-  P.slab2 = (x_chunks == 1 && !getenv("OF_WG_NO_PACK2") && c->KH == 3 && c->KW == 3 && P.stride_w == 1 &&
+  P.slab2 = (x_chunks == 1 && !of_tune_env("OF_WG_NO_PACK2") && c->KH == 3 && c->KW == 3 && P.stride_w == 1 &&
              P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && (5 + (c->db ? 1 : 0)) * P.n_mma <= 512 &&
-             !getenv("OF_WG_NO_SLAB2"))
+             !of_tune_env("OF_WG_NO_SLAB2"))
                 ? 1 : 0;
   P.nstack = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view &&
-              (P.n_chunks == 1 || (P.n_chunks == 2 && x_chunks >= 2 && !getenv("OF_WG_NO_NSTACK2"))) &&
-              P.TW >= 8 && P.TW <= 32 && !getenv("OF_WG_NO_NSTACK"))
+              (P.n_chunks == 1 || (P.n_chunks == 2 && x_chunks >= 2 && !of_tune_env("OF_WG_NO_NSTACK2"))) &&
+              P.TW >= 8 && P.TW <= 32 && !of_tune_env("OF_WG_NO_NSTACK"))
                  ? 1 : 0;
   P.nstack_one = (P.nstack && x_chunks == 1) ? 1 : 0;
-  P.one_split = (P.nstack_one && P.n_chunks == 1 && !getenv("OF_WG_NO_ONE_SPLIT")) ? 1 : 0;
+  P.one_split = (P.nstack_one && P.n_chunks == 1 && !of_tune_env("OF_WG_NO_ONE_SPLIT")) ? 1 : 0;
   if (P.nstack) { P.slab = 0; P.slab2 = 0; }
   CUtensorMap tmX[2], tmDY;
   memset(tmX, 0, sizeof(tmX));
@@ -423,7 +423,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
     attr_set = true;
   }
   P.taps = taps;
-  P.pack2 = (nch == 1 && taps > 1 && !P.nstack && !getenv("OF_WG_NO_PACK2")) ? 1 : 0;
+  P.pack2 = (nch == 1 && taps > 1 && !P.nstack && !of_tune_env("OF_WG_NO_PACK2")) ? 1 : 0;
   const int units = P.pack2 ? (taps + 1) / 2 : taps;       // accumulators needed per M tile
   if (P.pack2) {
     tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
@@ -461,9 +461,9 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   // (also the stem's strided-view wgrad: its overlapping-window boxes fill shared memory at ~20 B/clk per CTA)
   const int acc_cols = P.nstack ? tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0) : (tpp + (c->db ? 1 : 0)) * P.n_mma;
   const bool two_per_sm = ((P.nstack && (!P.nstack_one || P.one_split) && P.n_chunks == 1) || (view && acc_cols <= 256)) &&
-                          !getenv("OF_WG_NO_2CTA");
+                          !of_tune_env("OF_WG_NO_2CTA");
   if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
-  if (const char* e = getenv("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
+  if (const char* e = of_tune_env("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
   if (splits > P.ktiles) splits = P.ktiles;
   if (splits < 1) splits = 1;
   P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
@@ -474,7 +474,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.stages = (200 * 1024) / P.stage_bytes;
   if (P.stages > 8) P.stages = 8;
   if (two_per_sm) { int cap = (100 * 1024) / P.stage_bytes; if (cap < 2) cap = 2; if (P.stages > cap) P.stages = cap; }
-  if (const char* e = getenv("OF_WG_STAGES")) { int v = atoi(e); if (v >= 1 && v < P.stages) P.stages = v; }
+  if (const char* e = of_tune_env("OF_WG_STAGES")) { int v = atoi(e); if (v >= 1 && v < P.stages) P.stages = v; }
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
   if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);

@@ -449,7 +449,7 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
 #define CT_SMEM_BUDGET (220 * 1024)
 
 static bool cvtc_applicable(const void* a, const void* b, const void* c, int C, int cv_stride) {
-  if (getenv("OF_CV_NO_TC")) return false;
+  if (of_tune_env("OF_CV_NO_TC")) return false;
   if (C % 64 != 0 || C > 256 || cv_stride != 64) return false;
   return (((uintptr_t)a | (uintptr_t)b | (uintptr_t)c) & 15) == 0;
 }

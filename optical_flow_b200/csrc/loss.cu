@@ -303,7 +303,7 @@ int of_loss_l1_pyramid_fwdbwd(const float* imgs, const float* const* flows, floa
                               void* workspace, void* stream) {
   OF_REQUIRE(mode == OF_WARP_REF_IJ || mode == OF_WARP_XY, OF_ERR_ARG, "bad warp mode %d", mode);
   OF_REQUIRE(imgs && flows && hs && ws && loss && workspace, OF_ERR_ARG, "null pointer argument");
-  if (of_lf_supported(B, H, W, num_scales, hs, ws) && !getenv("OF_LOSS_GENERIC")) {
+  if (of_lf_supported(B, H, W, num_scales, hs, ws) && !of_tune_env("OF_LOSS_GENERIC")) {
     for (int s = 0; s < num_scales; ++s) OF_REQUIRE(flows[s] != nullptr, OF_ERR_ARG, "flow %d is null", s);
     return of_lf_run(imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
   }

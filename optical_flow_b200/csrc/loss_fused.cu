@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
         const float* T = reinterpret_cast<const float*>(Tb);
         // items enumerated on the full 32 x 32 patch grid (shifts, no divisions); rows / columns beyond
         // the image (last band / chunk) are skipped.  scale s: (32 >> (s+1))^2 resized pixels.
-        int t = (P.dbg & 1) ? 1 << 20 : tid;
+        int t = (OF_DBG(P) & 1) ? 1 << 20 : tid;
 #pragma unroll
         for (int s = 0; s < LF_MAX_SCALES; ++s) {
           const int lc = 4 - s;                         // log2(columns at scale s)
@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
         if (lane == 0) { tc::mbar_arrive(&pub_bar[stage]); tc::mbar_arrive(&empty_bar[stage]); }
       } else {
         // ---- gather unit: 32 x 32 output pixels of one scale, 4 per thread (2 in flight) ----
-        if (b > confirmed && !(P.dbg & 4)) {           // first gather unit of image b in this CTA: wait for its pyramid
+        if (b > confirmed && !(OF_DBG(P) & 4)) {           // first gather unit of image b in this CTA: wait for its pyramid
           if (lane == 0)
           {
             while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(200);
@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_CTAS_PER_SM) loss_fused_kernel(
         if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);   // one poller per warp
         __syncwarp();
 #pragma unroll 1
-        for (int q = (P.dbg & 2) ? 2 : 0; q < 2; ++q) {
+        for (int q = (OF_DBG(P) & 2) ? 2 : 0; q < 2; ++q) {
           const int lj = dj + 16 * q, j = tj * LF_GT_J + lj;
           int ii[2]; bool ok[2]; float2 fl[2];
 #pragma unroll
@@ -517,7 +517,7 @@ int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flow
   P.imgs = imgs; P.loss = loss;
   P.B = B; P.H = H; P.W = W; P.mode = mode;
   P.prows = LF_ROWS; P.pcols = LF_COLS;
-  if (const char* e = getenv("OF_LF_SHAPE")) {            // streaming experiment (use with OF_LF_DBG=7)
+  if (const char* e = of_tune_env("OF_LF_SHAPE")) {            // streaming experiment (use with OF_LF_DBG=7)
     int r_ = 0, c_ = 0;
     if (sscanf(e, "%d,%d", &r_, &c_) == 2 && r_ > 0 && c_ > 0 && c_ % 16 == 0 && r_ * c_ * 24 <= LF_STAGE_BYTES) {
       P.prows = r_; P.pcols = c_;
@@ -528,8 +528,8 @@ int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flow
   P.nb = P.bands * P.chunks;
   P.ng = ng;
   P.lead = B < 4 ? B : 4;   // measured on B200 at C2: lead 1 / 2 / 3 / 4 -> 84 / 64 / 55 / 53 us
-  if (const char* e = getenv("OF_LF_DBG")) P.dbg = atoi(e);
-  if (const char* e = getenv("OF_LF_LEAD")) { int v = atoi(e); if (v >= 1 && v <= B) P.lead = v; }
+  if (const char* e = of_tune_env("OF_LF_DBG")) P.dbg = atoi(e);
+  if (const char* e = of_tune_env("OF_LF_LEAD")) { int v = atoi(e); if (v >= 1 && v <= B) P.lead = v; }
   long long total = (long long)B * (P.nb + P.ng);
   OF_REQUIRE(total < (1ll << 30), OF_ERR_SHAPE, "too many loss work units");
   P.total_units = (int)total;
@@ -569,7 +569,7 @@ int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flow
     if (max_ctas > LF_MAX_GRID) max_ctas = LF_MAX_GRID;
   }
   int grid = P.total_units < max_ctas ? P.total_units : max_ctas;
-  if (const char* e = getenv("OF_LF_GRID")) { int v = atoi(e); if (v >= 1 && v < grid) grid = v; }
+  if (const char* e = of_tune_env("OF_LF_GRID")) { int v = atoi(e); if (v >= 1 && v < grid) grid = v; }
   // co-residency is required (gather units wait on build units of other CTAs): cooperative launch
   // makes the runtime enforce it
   void* args[2] = {(void*)&P, (void*)&M};

@@ -359,7 +359,7 @@ static int launch_fwd(const void* in, const float* coords, void* out, int32_t* i
                       int C, cudaStream_t st) {
   long long ntiles = (long long)B * ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
   int grid = grid_for(ntiles);
-  if (sizeof(T) == 2 && C % 8 == 0 && (((uintptr_t)in | (uintptr_t)out) & 15) == 0 && !getenv("OF_WARP_NO_VEC8"))
+  if (sizeof(T) == 2 && C % 8 == 0 && (((uintptr_t)in | (uintptr_t)out) & 15) == 0 && !of_tune_env("OF_WARP_NO_VEC8"))
     sample_fwd_kernel<T, 8, SRC><<<grid, 256, 0, st>>>((const T*)in, coords, (T*)out, idx, B, H, W, C);
   else if (C % 4 == 0)
     sample_fwd_kernel<T, 4, SRC><<<grid, 256, 0, st>>>((const T*)in, coords, (T*)out, idx, B, H, W, C);
@@ -383,9 +383,9 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
 #define LRUN(TPP)                                                                                    \
   sample_bwd_kernel<T, 4, TPP, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
                                                                    d_coords, B, H, W, C)
-  const bool run = SRC == SRC_REF_IJ && d_in != nullptr && !getenv("OF_WARP_NO_RUN");
+  const bool run = SRC == SRC_REF_IJ && d_in != nullptr && !of_tune_env("OF_WARP_NO_RUN");
   // bf16 features + bf16 gradient, C = 64 / 128: 16-byte accesses, 8 / 16 threads per pixel
-  if (sizeof(T) == 2 && sizeof(G) == 2 && run && (C == 64 || C == 128) && !getenv("OF_WARP_NO_VEC8") &&
+  if (sizeof(T) == 2 && sizeof(G) == 2 && run && (C == 64 || C == 128) && !of_tune_env("OF_WARP_NO_VEC8") &&
       ((((uintptr_t)in | (uintptr_t)d_out) & 15) == 0)) {
     if (C == 64)
       sample_bwd_kernel<T, 8, 8, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);

@@ -9,7 +9,7 @@ BatchNorm runs in inference mode: no cross-replica statistics.
 Two transports, same semantics:
   * ``CAbiComm``  - the library's own NCCL communicator (of_comm_*), used on GPUs;
   * ``TorchDistComm`` - torch.distributed (any backend); with ``gloo`` it lets the host logic be
-    tested on CPU at world_size 2 (tests/test_dp_gloo.py).
+    tested on CPU at world_size 2 (tests/test_c1_dp_gloo.py).
 """
 from __future__ import annotations
 

@@ -22,7 +22,9 @@ class BatchNormalizationTraining:
         self.moving_variance = torch.ones(channels, device=dev)
         self.d_gamma = torch.zeros(channels, device=dev)
         self.d_beta = torch.zeros(channels, device=dev)
-        self._stats = torch.zeros((2, channels), device=dev)      # sum, sum of squares
+        self._stats = torch.zeros((2, channels), device=dev)      # sum, sum of squares (about _shift)
+        self._shift = torch.zeros(channels, device=dev)           # snapshot of the moving mean taken by __call__
+        self._ws = torch.empty(L.load().of_bn_train_workspace_bytes(int(channels)), dtype=torch.uint8, device=dev)
         self._saved = None
 
     def _count(self, npix):
@@ -33,13 +35,16 @@ class BatchNormalizationTraining:
         assert x.shape[-1] == self.C and x.is_contiguous()
         npix = x.numel() // self.C
         lib = L.load()
-        L.check(lib.of_bn_train_stats(L.ptr(x), L.ptr(self._stats[0]), L.ptr(self._stats[1]), npix, self.C, L.dtype_code(x),
-                                      L.stream_ptr()), "of_bn_train_stats")
+        # sums are taken about the moving mean (identical on every replica -> the buffers stay all-reducible);
+        # a snapshot, because apply updates the moving mean and backward needs the value the sums were taken about
+        self._shift.copy_(self.moving_mean)
+        L.check(lib.of_bn_train_stats(L.ptr(x), L.ptr(self._shift), L.ptr(self._stats[0]), L.ptr(self._stats[1]), npix, self.C,
+                                      L.dtype_code(x), L.ptr(self._ws), L.stream_ptr()), "of_bn_train_stats")
         if self.comm is not None:
             self.comm.allreduce_sum_(self._stats)
         count = self._count(npix)
         y = torch.empty_like(x)
-        L.check(lib.of_bn_train_apply(L.ptr(x), L.ptr(self._stats[0]), L.ptr(self._stats[1]), count, L.ptr(self.gamma),
+        L.check(lib.of_bn_train_apply(L.ptr(x), L.ptr(self._stats[0]), L.ptr(self._stats[1]), L.ptr(self._shift), count, L.ptr(self.gamma),
                                       L.ptr(self.beta), self.epsilon, self.act, L.ptr(y),
                                       L.ptr(self.moving_mean) if update_moving else None,
                                       L.ptr(self.moving_variance) if update_moving else None, self.momentum, npix, self.C,
@@ -53,14 +58,15 @@ class BatchNormalizationTraining:
         assert dy.shape == x.shape and dy.dtype == x.dtype and dy.is_contiguous()
         npix = x.numel() // self.C
         lib = L.load()
-        L.check(lib.of_bn_train_bwd_reduce(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]), count,
-                                           self.epsilon, self.act, L.ptr(self.d_beta), L.ptr(self.d_gamma), npix, self.C,
-                                           L.dtype_code(x), L.stream_ptr()), "of_bn_train_bwd_reduce")
+        L.check(lib.of_bn_train_bwd_reduce(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]),
+                                           L.ptr(self._shift), count, self.epsilon, self.act, L.ptr(self.d_beta),
+                                           L.ptr(self.d_gamma), npix, self.C, L.dtype_code(x), L.ptr(self._ws),
+                                           L.stream_ptr()), "of_bn_train_bwd_reduce")
         if self.comm is not None:
             self.comm.allreduce_sum_(self.d_beta)
             self.comm.allreduce_sum_(self.d_gamma)
         dx = torch.empty_like(x)
-        L.check(lib.of_bn_train_bwd_apply(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]), count,
-                                          L.ptr(self.gamma), self.epsilon, self.act, L.ptr(self.d_beta), L.ptr(self.d_gamma),
+        L.check(lib.of_bn_train_bwd_apply(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]),
+                                          L.ptr(self._shift), count, L.ptr(self.gamma), self.epsilon, self.act, L.ptr(self.d_beta), L.ptr(self.d_gamma),
                                           L.ptr(dx), npix, self.C, L.dtype_code(x), L.stream_ptr()), "of_bn_train_bwd_apply")
         return dx

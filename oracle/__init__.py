@@ -12,8 +12,8 @@ section 8c).  What pins the oracle is tests/golden/: the reference's unmodified 
 transformations.py, resnet/models.py, old/image_warp.py and old/loss.py executed over a torch-backed stand-in for
 the ~40 TensorFlow calls they make (tests/golden/tf_shim, written from TF's documented op semantics and the
 defaults listed in SURVEY.md F4-F7), with the generating scripts committed (make_golden.py, make_golden_geom.py;
-make_golden_data.py uses the real cv2).  tests/test_golden.py, tests/test_geometry.py and
-tests/test_data_path.py hold every oracle function to those vectors.  Besides that the oracle is two
+make_golden_data.py uses the real cv2).  tests/test_a2_golden.py, tests/test_d2_geometry.py and
+tests/test_d1_data_path.py hold every oracle function to those vectors.  Besides that the oracle is two
 independent implementations (``ref_np*``: literal NumPy forward + hand-derived backward; ``ref_torch``:
-torch-CPU autograd) that must agree, plus the authored known-answer tests of ``tests/test_oracle.py``.
+torch-CPU autograd) that must agree, plus the authored known-answer tests of ``tests/test_a0_oracle.py``.
 """

@@ -28,3 +28,20 @@ def cuda():
     from optical_flow_b200 import build
     build.build_library()
     return torch.device("cuda:0")
+
+
+@pytest.fixture
+def variant():
+    """``variant(name, value)`` selects a kernel variant through of_set_option (the library reads no environment
+    variables); everything set during the test is unset afterwards."""
+    from optical_flow_b200 import _lib
+    lib = _lib.load()
+    used = []
+
+    def set_(name, value="1"):
+        used.append(name)
+        _lib.check(lib.of_set_option(name.encode(), None if value is None else str(value).encode()), "of_set_option")
+
+    yield set_
+    for name in used:
+        lib.of_set_option(name.encode(), None)

@@ -9,7 +9,7 @@ Run in the build container only (/root/reference does not exist on the GPU box):
 
 Outputs (committed): ops.npz (op-level inputs/outputs/gradients at small shapes) and
 net_c1.npz (whole train-step graph at BASELINE configs[0]: batch 1, 128x416 - loss, the four
-flows, and a digest of every weight gradient).  tests/test_golden.py checks the oracle
+flows, and a digest of every weight gradient).  tests/test_a2_golden.py checks the oracle
 (oracle/ref_np*.py, oracle/ref_torch.py) against them on CPU and the CUDA path on GPU.
 """
 import os

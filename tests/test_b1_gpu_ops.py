@@ -232,12 +232,12 @@ def test_cost_volume_fwd_bwd(cuda, shape):
 
 @pytest.mark.parametrize("tc", [True, False])
 @pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128), (1, 6, 200, 64), (3, 5, 300, 128)])
-def test_cost_volume_fwd_bf16(cuda, shape, tc, monkeypatch):
+def test_cost_volume_fwd_bf16(cuda, shape, tc, variant):
     """bf16 cost volume written into the 64-channel decoder input buffer: the tcgen05 banded-GEMM kernel
-    (costvol_tc.cu) and the SIMT kernel (costvol7.cu, OF_CV_NO_TC=1) against the oracle on bf16-rounded inputs."""
+    (costvol_tc.cu) and the SIMT kernel (costvol7.cu, option OF_CV_NO_TC) against the oracle on bf16-rounded inputs."""
     from optical_flow_b200 import _lib as L
     if not tc:
-        monkeypatch.setenv("OF_CV_NO_TC", "1")
+        variant("OF_CV_NO_TC", "1")
     B, H, W, C = shape
     r = rng(14)
     bf = lambda a: torch.tensor(a).bfloat16()
@@ -255,12 +255,12 @@ def test_cost_volume_fwd_bf16(cuda, shape, tc, monkeypatch):
 
 @pytest.mark.parametrize("tc", [True, False])
 @pytest.mark.parametrize("shape", [(2, 24, 80, 64), (1, 8, 26, 256), (2, 33, 17, 128), (1, 6, 200, 64), (3, 5, 300, 128)])
-def test_cost_volume_bwd_bf16_fused(cuda, shape, tc, monkeypatch):
+def test_cost_volume_bwd_bf16_fused(cuda, shape, tc, variant):
     """of_cost_volume_bwd_bf16 (bf16 tensors, d_f1 += the conv-path gradient) vs the oracle on the same
     bf16-rounded inputs; the only extra error is the final bf16 rounding (2^-8 relative to the value)."""
     from optical_flow_b200 import _lib as L
     if not tc:
-        monkeypatch.setenv("OF_CV_NO_TC", "1")
+        variant("OF_CV_NO_TC", "1")
     B, H, W, C = shape
     r = rng(12)
     bf = lambda a: torch.tensor(a).bfloat16()
@@ -366,7 +366,7 @@ def test_loss_layer_fused(cuda, B, H, W):
 
 @pytest.mark.parametrize("mode", ["ref_ij", "xy"])
 @pytest.mark.parametrize("B,H,W", [(1, 16, 16), (3, 48, 80), (2, 64, 208), (8, 384, 1280)])
-def test_loss_fast_path_equals_generic(cuda, monkeypatch, B, H, W, mode):
+def test_loss_fast_path_equals_generic(cuda, variant, B, H, W, mode):
     """The L2-pyramid fast path (loss_fused.cu; H, W multiples of 16) against the direct-gather
     kernel (loss.cu) on the same inputs, up to BASELINE's full 8 x 384 x 1280, twice in a row
     (the kernel re-arms its own counters)."""
@@ -374,9 +374,9 @@ def test_loss_fast_path_equals_generic(cuda, monkeypatch, B, H, W, mode):
     g = torch.Generator(device="cpu").manual_seed(B * 1000 + H)
     imgs = (torch.rand((B, H, W, 6), generator=g) - 0.5).to(cuda)
     flows = [(torch.randn((B, H >> (s + 1), W >> (s + 1), 2), generator=g) * (4.0 / 2 ** s)).to(cuda) for s in range(4)]
-    monkeypatch.setenv("OF_LOSS_GENERIC", "1")
+    variant("OF_LOSS_GENERIC", "1")
     l_ref, d_ref = F.loss_l1_pyramid(imgs, flows, mode=mode)
-    monkeypatch.delenv("OF_LOSS_GENERIC")
+    variant("OF_LOSS_GENERIC", None)
     for _ in range(2):
         l_fast, d_fast = F.loss_l1_pyramid(imgs, flows, mode=mode)
         assert abs(l_fast.item() - l_ref.item()) <= 1e-6 * abs(l_ref.item())

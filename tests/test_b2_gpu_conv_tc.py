@@ -134,9 +134,9 @@ TWO_CTA_CASES = [
 
 
 @pytest.mark.parametrize("cfg", TWO_CTA_CASES)
-def test_tc_two_ctas_per_sm(cuda, cfg, monkeypatch):
+def test_tc_two_ctas_per_sm(cuda, cfg, variant):
     """fprop, dgrad (+ mask epilogue) and sign-bit masks on grids large enough for the two-CTA variants; the
-    one-CTA launch of the same layer (OF_T3_2CTA=0 / OF_TC_CTAS=1) must give the same bits."""
+    one-CTA launch of the same layer (options OF_T3_2CTA=0 / OF_TC_CTAS=1) must give the same bits."""
     from optical_flow_b200 import conv_tc, _lib as L
     test_tc_fprop(cuda, cfg)
     test_tc_dgrad(cuda, cfg)
@@ -144,19 +144,19 @@ def test_tc_two_ctas_per_sm(cuda, cfg, monkeypatch):
     x, w, b = make(cfg, 11)
     xd, wd, bd = torch.tensor(x, device=cuda).bfloat16(), torch.tensor(w, device=cuda), torch.tensor(b, device=cuda)
     two = conv_tc.conv2d_fprop_tc(xd, wd, bd, stride=s, act=L.OF_ACT_LEAKY)
-    monkeypatch.setenv("OF_T3_2CTA", "0")
-    monkeypatch.setenv("OF_TC_CTAS", "1")
+    variant("OF_T3_2CTA", "0")
+    variant("OF_TC_CTAS", "1")
     one = conv_tc.conv2d_fprop_tc(xd, wd, bd, stride=s, act=L.OF_ACT_LEAKY)
     assert torch.equal(one, two)
     if s == 1:
-        monkeypatch.delenv("OF_T3_2CTA")
+        variant("OF_T3_2CTA", None)
         test_tc3_sign_bit_mask(cuda, cfg)
 
 
 @pytest.mark.parametrize("cfg", [(2, 24, 32, 64, 3, 64, 1), (1, 16, 48, 128, 3, 96, 1), (1, 9, 13, 64, 3, 32, 1)])
-def test_tc3_staged_epilogue_variant(cuda, cfg, monkeypatch):
-    """conv_tc3.cu's optional staged (coalesced) epilogue, OF_T3_COAL=1: same results as the default."""
-    monkeypatch.setenv("OF_T3_COAL", "1")
+def test_tc3_staged_epilogue_variant(cuda, cfg, variant):
+    """conv_tc3.cu's optional staged (coalesced) epilogue, option OF_T3_COAL=1: same results as the default."""
+    variant("OF_T3_COAL", "1")
     test_tc_fprop(cuda, cfg)
     test_tc_dgrad(cuda, cfg)
 
@@ -311,7 +311,7 @@ def test_bf16_train_step_vs_oracle(cuda):
     rounding through ~20 stacked convs; the L1 loss gradient is sign(err) and a warp index flips
     where a bf16-noisy flow crosses an integer, which moves that pixel's whole gradient - visible
     on the 8x26 coarsest level, whose decoder measured 0.90-0.95 on B200; every other tensor
-    > 0.95).  The exact-arithmetic check of the same graph is test_gpu_net (fp32 mode, 1e-4)."""
+    > 0.95).  The exact-arithmetic check of the same graph is test_b3_gpu_net (fp32 mode, 1e-4)."""
     from optical_flow_b200.loss import LossLayer
     from optical_flow_b200.model import build_flow_net
     B, H, W = 1, 128, 416

@@ -3,7 +3,7 @@ Adam) against the torch-CPU oracle, through the reference-named Python surface.
 
 conv_mode='fp32' (SIMT convs): flows, loss and all 4 937 608 gradient entries within
 1e-4 of max-abs per tensor (fp32 accumulation-order noise through ~40 layers; the
-per-op 1e-5 bars are in test_gpu_ops.py).
+per-op 1e-5 bars are in test_b1_gpu_ops.py).
 """
 import numpy as np
 import pytest
