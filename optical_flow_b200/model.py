@@ -275,7 +275,11 @@ class FlowModule:
             assert previous_flow.shape[2] * 2 == features1.shape[2]
             assert previous_flow.shape[3] == 2
             self.flow_up = F.upscale_flow_fwd(previous_flow)
-            self.f2w = F.warp_features_fwd(self.flow_up, features2, mode=net.warp_mode)
+            # sampling coordinates: this level's own up-scaled flow, unless the caller pinned them
+            # (net.frozen_warp_flows: parity tests that separate conv rounding from warp-index flips)
+            frozen = net.frozen_warp_flows
+            self.warp_flow = frozen[self.level] if frozen is not None else self.flow_up
+            self.f2w = F.warp_features_fwd(self.warp_flow, features2, mode=net.warp_mode)
         else:
             self.flow_up, self.f2w = None, features2
         x = net.backend_concat_fwd(self, features1, self.f2w, self.flow_up)
@@ -293,7 +297,7 @@ class FlowModule:
             d = conv.backward(d)
         d_f1, d_f2w, d_flow_up = net.backend_concat_bwd(self, d, out_f1, out_f2)
         if self.has_prev:
-            d_f2, d_flow_up_b = F.warp_features_bwd(self.flow_up, self.f2, d_f2w, mode=net.warp_mode)
+            d_f2, d_flow_up_b = F.warp_features_bwd(self.warp_flow, self.f2, d_f2w, mode=net.warp_mode)
             _accumulate(d_flow_up, d_flow_up_b)
             d_prev = F.upscale_flow_bwd(d_flow_up)
         else:
@@ -318,6 +322,7 @@ class FlowNet:
         self.store = ParamStore(self.device, max_disp)
         self.store.init_glorot(seed)
         self._bufs = {}
+        self.frozen_warp_flows = None      # {level: (B,h,w,2) f32} overrides the warp coordinates (tests only)
         self.conv_mode = conv_mode
         if conv_mode == "fp32":
             self.backend = Fp32Backend(self)

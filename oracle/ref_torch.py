@@ -120,6 +120,30 @@ def create_cost_volume(f1, f2, max_disp):
     return torch.stack(corr, dim=-1)
 
 
+def create_cost_volume_fwd_bwd(f1, f2, max_disp, d_cv):
+    """model.py:29-42 forward and its hand-derived gradient in one multi-threaded torch loop that keeps no
+    autograd tape (49 saved products of the full feature map are 12 GB at 8 x 192 x 640 x 64): the large-shape
+    oracle of tests/test_b4_bench_shapes.py.  Agrees with create_cost_volume + autograd and with
+    ref_np_ops.create_cost_volume_bwd (tests/test_a0_oracle.py)."""
+    B, H, W, C = f1.shape
+    m = max_disp
+    f2p = F.pad(f2, (0, 0, m, m, m, m))
+    cv = torch.empty((B, H, W, (2 * m + 1) ** 2), dtype=f1.dtype)
+    d_f1 = torch.zeros_like(f1)
+    d_f2p = torch.zeros_like(f2p)
+    k = 0
+    with torch.no_grad():
+        for i in range(2 * m + 1):
+            for j in range(2 * m + 1):
+                win = f2p[:, i:i + H, j:j + W, :]
+                cv[..., k] = (f1 * win).sum(dim=-1)
+                gk = d_cv[..., k:k + 1]
+                d_f1.addcmul_(gk, win)
+                d_f2p[:, i:i + H, j:j + W, :].addcmul_(gk, f1)
+                k += 1
+    return cv, d_f1, d_f2p[:, m:m + H, m:m + W, :].contiguous()
+
+
 # ----------------------------------------------------------------- losses --
 
 def loss_layer(batch_imgs, flows):

@@ -188,6 +188,11 @@ def test_two_impl_cost_volume_bwd():
     d1, d2 = O.create_cost_volume_bwd(f1, f2, 3, g)
     np.testing.assert_allclose(d1, a.grad.numpy(), atol=1e-5)
     np.testing.assert_allclose(d2, b.grad.numpy(), atol=1e-5)
+    # the tape-free large-shape form used by tests/test_b4_bench_shapes.py
+    cv3, e1, e2 = T.create_cost_volume_fwd_bwd(torch.tensor(f1), torch.tensor(f2), 3, torch.tensor(g))
+    np.testing.assert_allclose(cv3.numpy(), cv.detach().numpy(), atol=1e-6)
+    np.testing.assert_allclose(e1.numpy(), a.grad.numpy(), atol=1e-5)
+    np.testing.assert_allclose(e2.numpy(), b.grad.numpy(), atol=1e-5)
 
 
 def test_two_impl_loss_layer():
