@@ -152,37 +152,60 @@ def cpu_loss_baseline(B, budget_s=15.0):
             "sample": "oracle/ref_torch.loss_layer fwd+bwd, batch 1 at %dx%d, %d passes" % (H_FULL, W_FULL, n)}
 
 
-def cpu_train_baseline(budget_s=25.0, height=H_FULL, width=W_FULL, max_steps=20, warmup=1):
-    """Oracle port (torch-CPU fp32 autograd, all host threads) of the full train step
-    (forward + loss + backward; Adam excluded: 5 M parameters, negligible) on a bounded sample of the
-    SAME workload: batch 1 at the bench's resolution, as many steps as fit the time budget."""
+def cpu_train_baseline(budget_s=25.0, height=H_FULL, width=W_FULL, max_steps=20, warmup=1, sample_batch=1):
+    """Oracle port (torch-CPU fp32 autograd, all host threads) of the full train step - forward, loss, backward AND the
+    Adam update of all 4.9 M parameters (train.py:47-56) - on a bounded sample of the SAME workload: ``sample_batch``
+    pairs per step at the bench's resolution (a batch-8 tape at 384x1280 needs tens of GB of host memory), as many
+    steps as fit the time budget.  value = pairs per second."""
     import torch
     from oracle import ref_torch as T
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     params, stats = T.init_params(seed=42)
     net = T.FlowNetRef(params, stats)
-    imgs = torch.tensor(T.synthetic_pairs(1, height, width, seed=1))
+    imgs = torch.tensor(T.synthetic_pairs(sample_batch, height, width, seed=1))
+    m = {k: torch.zeros_like(v) for k, v in net.p.items()}
+    v = {k: torch.zeros_like(p) for k, p in net.p.items()}
+    state = {"step": 0}
+
+    def one():
+        _, _, grads = net.loss_and_grads(imgs)
+        state["step"] += 1
+        with torch.no_grad():
+            for k, p in net.p.items():
+                pn, m[k], v[k] = T.adam_step(p.detach(), grads[k], m[k], v[k], state["step"])
+                p.copy_(pn)
+
     for _ in range(max(warmup, 1)):
-        net.loss_and_grads(imgs)
+        one()
     t0, n = time.time(), 0
     while True:
-        net.loss_and_grads(imgs)
+        one()
         n += 1
         if time.time() - t0 > budget_s or n >= max_steps:
             break
     dt = (time.time() - t0) / n
-    return {"value": 1.0 / dt, "unit": "image-pairs/s", "cores": cores, "kind": "port",
-            "sample": "oracle/ref_torch.FlowNetRef fwd+loss+bwd (torch-CPU fp32), batch 1 at %dx%d, %d steps of %.2f s"
-                      % (height, width, n, dt)}
+    return {"value": sample_batch / dt, "unit": "image-pairs/s", "cores": cores, "kind": "port",
+            "sample": "oracle/ref_torch.FlowNetRef fwd+loss+bwd+Adam (torch-CPU fp32, %d threads), %d pair(s) per step at "
+                      "%dx%d, %d steps of %.2f s" % (cores, sample_batch, height, width, n, dt)}
 
 
 def train_metric(H, W):
     return "image-pairs/s per train step at %dx%d" % (H, W)
 
 
-def train_config(B, H, W, world, conv_mode):
-    return {"workload": "full train step fwd+bwd+Adam, ResNet encoder + cost-volume decoder, batch %d/GPU at %dx%d (configs[2])" % (B, H, W),
+def per_gpu_batch(args, world):
+    """weak scaling: --batch pairs per GPU; strong scaling (BASELINE configs[3] read literally): --global-batch
+    pairs over all GPUs (64 -> 32 / 16 / 8 per GPU at 2 / 4 / 8)."""
+    if args.scaling == "strong":
+        assert args.global_batch % world == 0, "global batch must divide by the number of GPUs"
+        return args.global_batch // world
+    return args.batch
+
+
+def train_config(B, H, W, world, conv_mode, scaling="weak"):
+    tag = "configs[2]" if scaling == "weak" else "configs[3], fixed global batch"
+    return {"workload": "full train step fwd+bwd+Adam, ResNet encoder + cost-volume decoder, batch %d/GPU at %dx%d (%s)" % (B, H, W, tag),
             "global_batch": B * world, "parallelism": "dp%d" % world, "conv_mode": conv_mode,
             "l2": "activations per step (GBs) far exceed the 126 MB L2; 2 rotating input batches"}
 
@@ -190,26 +213,27 @@ def train_config(B, H, W, world, conv_mode):
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path.  TensorFlow is not
     installable here (no wheel, no network), so this is the oracle port (torch-CPU fp32, all host
-    threads) on the same metric / config; a step = one batch-1 pass of the same graph at the same
-    resolution (bounded sample), rank 0 only."""
+    threads) on the same metric / config keys; a step = a bounded sample of that workload (2 pairs of the
+    batch at the same resolution, Adam included), value normalised to pairs per second; rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     steps = max(args.steps, 1)
     world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    B = per_gpu_batch(args, world)
     if args.workload == "loss":
-        base = cpu_loss_baseline(B_PER_GPU, budget_s=min(60.0, 4.0 * steps))
+        base = cpu_loss_baseline(B, budget_s=min(60.0, 4.0 * steps))
         metric = "image-pairs/s through the fused warp+loss (fwd+bwd) at %dx%d" % (H_FULL, W_FULL)
-        cfg = {"workload": "fused warp+L1 pyramid loss fwd+bwd, 384x1280 (configs[1])"}
+        cfg = {"workload": "fused warp + L1 pyramid loss fwd+bwd, batch %d/GPU at %dx%d (configs[1])" % (B, args.height, args.width)}
     else:
-        base = cpu_train_baseline(budget_s=120.0, height=args.height, width=args.width, max_steps=steps,
-                                  warmup=min(args.warmup, 2))
+        base = cpu_train_baseline(budget_s=150.0, height=args.height, width=args.width, max_steps=steps,
+                                  warmup=min(args.warmup, 2), sample_batch=min(B, 2))
         metric = train_metric(args.height, args.width)
-        cfg = train_config(args.batch, args.height, args.width, world, "fp32 (CPU)")
-    cfg["cpu_sample"] = base["sample"]
+        cfg = train_config(B, args.height, args.width, world, "bf16", args.scaling)
     line = {"impl": "reference", "metric": metric, "value": base["value"], "unit": "image-pairs/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / base["value"],
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1000.0 * B / base["value"],       # normalised to the config's batch (the sample is smaller)
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": cfg, "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "image-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -228,7 +252,12 @@ def main():
     ap.add_argument("--batch", type=int, default=B_PER_GPU)
     ap.add_argument("--height", type=int, default=H_FULL)
     ap.add_argument("--width", type=int, default=W_FULL)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --batch pairs per GPU (default); strong: --global-batch pairs over all GPUs (configs[3])")
+    ap.add_argument("--global-batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="train workload: skip the distribution / timeline / loss-kernel legs (scaling sweeps)")
     ap.add_argument("--flows", default="smooth", choices=["smooth", "iid"],
                     help="loss workload: flow field statistics (SURVEY 8d: realistic smooth / worst-case i.i.d.)")
     ap.add_argument("--no-graph", action="store_true", help="time direct launches instead of CUDA graph replay")
@@ -256,7 +285,9 @@ def main():
         line = bench_train(args, dev, world, rank)
     if rank == 0:
         if not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_loss_baseline(args.batch) if args.workload == "loss" else cpu_train_baseline(budget_s=20.0, height=args.height, width=args.width, max_steps=12)
+            line["cpu_baseline"] = (cpu_loss_baseline(args.batch) if args.workload == "loss" else
+                                    cpu_train_baseline(budget_s=20.0, height=args.height, width=args.width, max_steps=12,
+                                                       sample_batch=min(per_gpu_batch(args, world), 2)))
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -280,15 +311,9 @@ def _timed(torch, dist, world, fn_steps, steps):
     return ms
 
 
-def bench_loss(args, dev, world, rank):
-    import numpy as np
-    import torch
-    import torch.distributed as dist
-    from optical_flow_b200 import functional as F
+def make_loss_sets(torch, dev, B, H, W, flows_kind, rank, nsets=4):
+    """nsets x (images, 4 flows, 4 d_flows, loss): 4 x 115 MB of inputs / outputs rotate through the 126 MB L2."""
     from optical_flow_b200.train import synthetic_batch
-    B, H, W = args.batch, args.height, args.width
-    peaks = measured_peaks()
-    nsets = 4   # 4 x 115 MB of inputs/outputs rotate through the 126 MB L2
     sets = []
     for k in range(nsets):
         imgs = synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev)
@@ -296,7 +321,7 @@ def bench_loss(args, dev, world, rank):
         flows = []
         for s in range(4):
             h, w = H >> (s + 1), W >> (s + 1)
-            if args.flows == "iid":
+            if flows_kind == "iid":
                 # SURVEY 8d worst case: i.i.d. N(0, (4/2^s)^2) px per pixel (every tap a different line)
                 f = torch.randn((B, h, w, 2), generator=g) * (4.0 / 2 ** s)
             else:
@@ -308,17 +333,23 @@ def bench_loss(args, dev, world, rank):
             flows.append(f.to(dev))
         d_flows = [torch.empty_like(f) for f in flows]
         sets.append((imgs, flows, d_flows, torch.empty(1, device=dev)))
+    return sets
+
+
+def loss_runner(torch, sets, use_graph=True):
+    """Returns (run(n), launch mode): the kernel (~25-50 us) is shorter than a Python + ctypes launch, so the
+    len(sets) launches are replayed from a CUDA graph - the device, not the host, is what is timed."""
+    from optical_flow_b200 import functional as F
+    nsets = len(sets)
 
     def run(n):
         for i in range(n):
             imgs, flows, d_flows, lo = sets[i % nsets]
             F.loss_l1_pyramid(imgs, flows, need_grads=True, loss_out=lo, d_flows=d_flows)
 
-    run(max(args.warmup, 3))
-    # the kernel (~25 us) is shorter than a Python + ctypes launch: replay the nsets launches from a
-    # CUDA graph so the device, not the host, is what is timed
+    run(max(3, nsets))
     graph = None
-    if not args.no_graph:
+    if use_graph:
         try:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
@@ -332,13 +363,52 @@ def bench_loss(args, dev, world, rank):
         except Exception as e:          # noqa: BLE001 - fall back to direct launches, say so
             graph = None
             sys.stderr.write("CUDA graph capture failed (%s); timing direct launches\n" % e)
+    if graph is None:
+        return run, "direct"
 
-    def run_timed(n):
-        if graph is None:
-            return run(n)
-        for _ in range(n // nsets):
+    def run_graph(n):
+        for _ in range(max(n // nsets, 1)):
             graph.replay()
 
+    return run_graph, "cuda graph replay"
+
+
+def loss_kernel_leg(torch, dev, B, H, W, rank, peaks, iters=200):
+    """configs[1] inside the default line: the fused warp+loss kernel alone, both flow statistics, CUDA events around
+    `iters` graph-replayed launches over 4 rotating input sets (> L2)."""
+    out = {}
+    alg = loss_algorithmic_bytes(B, H, W)
+    for kind in ("smooth", "iid"):
+        sets = make_loss_sets(torch, dev, B, H, W, kind, rank)
+        run, mode = loss_runner(torch, sets)
+        n = max(iters // len(sets), 1) * len(sets)
+        run(len(sets) * 3)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        run(n)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / n * 1e3
+        ach = alg / (us * 1e-6) / 1e9
+        out[kind] = {"us": us, "achieved": ach, "frac": ach / peaks["hbm"], "launches": n, "launch": mode}
+        del sets
+    return {"bound": "hbm", "unit": "GB/s", "peak": peaks["hbm"], "peak_source": peaks["src"],
+            "algorithmic_bytes": alg, "kernel": "loss_fused_kernel (warp + L1 pyramid loss fwd + d_flow, one launch)",
+            "workload": "batch %d at %dx%d (configs[1]), 4 rotating input sets (> 126 MB L2)" % (B, H, W),
+            "flows": out, "achieved": out["smooth"]["achieved"], "frac": out["smooth"]["frac"],
+            "note": "headline = low-pass (decoder-like) flows; iid = SURVEY 8d worst-case scatter"}
+
+
+def bench_loss(args, dev, world, rank):
+    import torch
+    import torch.distributed as dist
+    from optical_flow_b200 import functional as F
+    B, H, W = args.batch, args.height, args.width
+    peaks = measured_peaks()
+    sets = make_loss_sets(torch, dev, B, H, W, args.flows, rank)
+    nsets = len(sets)
+    run_timed, mode = loss_runner(torch, sets, use_graph=not args.no_graph)
     steps = max(args.steps // nsets, 1) * nsets
     clocks = ClockSampler(dev.index or 0)
     clocks.start()
@@ -380,7 +450,7 @@ def bench_loss(args, dev, world, rank):
             "data": "synthetic",
             "config": {"workload": "fused warp + L1 pyramid loss fwd+bwd, batch %d/GPU at %dx%d (configs[1])" % (B, H, W),
                        "l2": "4 rotating input/output sets (4 x %.0f MB > 126 MB L2)" % (alg / 1e6),
-                       "launch": "cuda graph replay" if graph is not None else "direct",
+                       "launch": mode,
                        "flows": args.flows + (" (low-pass N(0,(4/2^s)^2) px)" if args.flows == "smooth" else " (i.i.d. N(0,(4/2^s)^2) px, worst-case scatter)")},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s",
                          "frac": ach / peaks["hbm"], "traffic": None, "kernel": "loss_fused_kernel",
@@ -417,12 +487,34 @@ def time_dominant_conv(torch, dev, N, H, W, Cin, Cout, iters=20):
     return {"us": us, "flops": fl, "tflops": fl / us / 1e6, "iters": iters}
 
 
+TC_CONV_KERNELS = ("conv_tc3_kernel", "conv_tc_kernel", "conv_tc_wgrad_kernel")
+
+
+def step_timeline(tr, batches, nsteps=3):
+    """Per-kernel device time of one train step, measured LIVE with one CUDA event after every launch of the library
+    (of_prof_enable / of_prof_collect) over `nsteps` steps: {kernel: (us per step, launches per step)}."""
+    from optical_flow_b200 import _lib as L
+
+    def run():
+        for i in range(nsteps):
+            tr.train_step(batches[i % len(batches)], i)
+
+    recs = L.timeline(run)
+    agg = {}
+    for name, ms, work in recs:
+        a = agg.setdefault(name, [0.0, 0, 0.0])
+        a[0] += ms * 1e3 / nsteps
+        a[1] += 1
+        a[2] += work / nsteps
+    return {k: {"us": v[0], "launches": v[1] / nsteps, "flops": v[2]} for k, v in agg.items()}, recs
+
+
 def bench_train(args, dev, world, rank):
     import torch
     import torch.distributed as dist
     from optical_flow_b200 import _lib as L
-    from optical_flow_b200.train import Trainer, synthetic_batch
-    B, H, W = args.batch, args.height, args.width
+    from optical_flow_b200.train import Trainer, synthetic_batch, HostFramePrefetcher
+    B, H, W = per_gpu_batch(args, world), args.height, args.width
     peaks = measured_peaks()
     comm = None
     if world > 1:
@@ -431,7 +523,6 @@ def bench_train(args, dev, world, rank):
     tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm)
     nsets = 2
     batches = [synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev) for k in range(nsets)]
-    loss_acc = torch.zeros(1, device=dev)
 
     def run(n):
         for i in range(n):
@@ -446,16 +537,35 @@ def bench_train(args, dev, world, rank):
     launches = L.load().of_launch_count() - launches_before
     per = ms / args.steps
     value = world * B / (per * 1e-3)
-    # end to end through the public API with HOST batches: pinned host -> device copy of the
-    # step's images and a device -> host read of the loss, every step
-    h_batches = [b.cpu().pin_memory() for b in batches]
+
+    # distribution over >= 100 individually timed steps (SURVEY 8d protocol): median, p10, p90
+    dist_stats = None
+    if not args.no_extras:
+        n_d = int(max(20, min(100, 4000.0 / max(per, 1e-3))))
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_d + 1)]
+        torch.cuda.synchronize()
+        evs[0].record()
+        for i in range(n_d):
+            tr.train_step(batches[i % nsets], i)
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        t = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(n_d))
+        dist_stats = {"steps": n_d, "median_ms": t[n_d // 2], "p10_ms": t[n_d // 10], "p90_ms": t[(n_d * 9) // 10],
+                      "min_ms": t[0], "max_ms": t[-1]}
+
+    # end to end through the public API from HOST frames (data_reader.py:35-64 -> train.py:47-61): pinned uint8 pairs
+    # -> one H2D copy per batch (copy stream, under the previous step) -> of_preprocess_batch -> train_step, and a
+    # device -> host read of the loss, every step
+    means = torch.tensor([123.0, 117.0, 104.0] * 2, device=dev) / 255.0
+    h_frames = []
+    for b in batches:
+        u8 = ((b + means) * 255.0).round().clamp(0, 255).to(torch.uint8)                   # (B,H,W,6)
+        fr = u8.view(B, H, W, 2, 3).permute(0, 3, 1, 2, 4).contiguous()                    # (B,2,H,W,3)
+        h_frames.append(fr.cpu().pin_memory())
     h_loss = torch.empty(1).pin_memory()
-    from optical_flow_b200.train import HostBatchPrefetcher
 
     def run_e2e(n):
-        # the user-facing loop: host batches through the prefetcher (copy of batch i+1 under the compute of
-        # batch i), train_step, and a device -> host read of the loss every step
-        feed = HostBatchPrefetcher((h_batches[i % nsets] for i in range(n)), dev)
+        feed = HostFramePrefetcher((h_frames[i % nsets] for i in range(n)), dev, H, W)
         for i, (d_in, release) in enumerate(feed):
             loss, _ = tr.train_step(d_in, i)
             release()
@@ -465,39 +575,68 @@ def bench_train(args, dev, world, rank):
     run_e2e(2)
     ms_e = _timed(torch, dist, world, run_e2e, args.steps)
     ck = clocks.stop()
-    d_in = batches[0]
     e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
-           "h2d_bytes_per_step": d_in.numel() * 4, "d2h_bytes_per_step": 4}
+           "h2d_bytes_per_step": h_frames[0].numel(), "d2h_bytes_per_step": 4,
+           "input": "pinned uint8 frame pairs (B,2,H,W,3) -> of_preprocess_batch -> train_step"}
     flops = conv_flops(B, H, W)
     tc_flops = conv_flops(B, H, W, tc_only=True)
     step_tf = (tc_flops if args.conv_mode == "bf16" else flops) / (per * 1e-3) / 1e12
+    line_extra = {}
     if args.conv_mode == "bf16":
-        # dominant kernel = conv_tc3_kernel on the decoder's finest level (model.py:104-114; 55 % of the
-        # step's FLOPs are level-3 3x3 convs): its 128->128 layer timed live, alone, with CUDA events
-        dom = time_dominant_conv(torch, dev, B, H // 2, W // 2, 128, 128, iters=max(args.steps, 10))
-        traffic = None                                   # DRAM bytes per launch of that kernel, from the committed ncu capture
-        tpath = os.path.join(ROOT, "profiles", "r01_roofline_traffic.json")
-        if (B, H, W) == (8, 384, 1280) and os.path.exists(tpath):
-            traffic = json.load(open(tpath))["conv_tc3_fprop_N8_192x640_128_128"]["traffic_bytes"]
-        roof = {"bound": "tensor", "achieved": dom["tflops"], "peak": peaks["tf_burst"], "unit": "TFLOP/s",
-                "frac": dom["tflops"] / peaks["tf_burst"], "traffic": traffic,
-                "kernel": "conv_tc3_kernel (tcgen05 implicit GEMM), decoder level-3 conv 128->128 3x3 fprop: "
-                          "M=%d K=1152 N=128, %.1f us/launch over %d launches" % (B * (H // 2) * (W // 2), dom["us"], dom["iters"]),
-                "algorithmic_flops": dom["flops"], "peak_source": peaks["src"] + " (burst bf16: kernel timed alone)",
+        roof = {"bound": "tensor", "unit": "TFLOP/s", "peak": peaks["tf_sust"],
+                "peak_source": peaks["src"] + " (sustained bf16: kernels timed inside a long step)",
+                "algorithmic_flops": tc_flops,
                 "step": {"tensor_path_flops": tc_flops, "achieved": step_tf, "peak": peaks["tf_sust"],
                          "frac": step_tf / peaks["tf_sust"],
                          "note": "all tensor-core conv FLOPs of one step / whole step time (includes every non-conv kernel)"}}
+        if not args.no_extras:
+            # FLOP-weighted in-step figure: all tensor-core conv launches of the step, timed live by the library's
+            # per-launch CUDA-event timeline over 3 steps
+            agg, _ = step_timeline(tr, batches)
+            tc_us = sum(v["us"] for k, v in agg.items() if k in TC_CONV_KERNELS)
+            tot_us = sum(v["us"] for v in agg.values())
+            ach = tc_flops / (tc_us * 1e-6) / 1e12
+            roof.update({"achieved": ach, "frac": ach / peaks["tf_sust"],
+                         "kernel": "conv_tc3_kernel + conv_tc_kernel + conv_tc_wgrad_kernel (tcgen05 implicit GEMM): all %d "
+                                   "tensor-core conv launches of one step, FLOP-weighted; %.0f us of a %.0f us step "
+                                   "(CUDA events after every launch, 3 steps)"
+                                   % (round(sum(v["launches"] for k, v in agg.items() if k in TC_CONV_KERNELS)), tc_us, tot_us),
+                         "conv_share_of_step": tc_us / tot_us})
+            top = sorted(agg.items(), key=lambda kv: -kv[1]["us"])[:12]
+            line_extra["kernels"] = {k: {"us": round(v["us"], 1), "launches": round(v["launches"], 1),
+                                         "share": round(v["us"] / tot_us, 4)} for k, v in top}
+            # best single layer, timed alone (burst peak): decoder level-3 128 -> 128
+            dom = time_dominant_conv(torch, dev, B, H // 2, W // 2, 128, 128, iters=max(args.steps, 10))
+            traffic = None                               # DRAM bytes per launch of that kernel, from the committed ncu capture
+            tpath = os.path.join(ROOT, "profiles", "r01_roofline_traffic.json")
+            if (B, H, W) == (8, 384, 1280) and os.path.exists(tpath):
+                traffic = json.load(open(tpath))["conv_tc3_fprop_N8_192x640_128_128"]["traffic_bytes"]
+            roof["traffic"] = traffic
+            roof["best_layer"] = {"kernel": "conv_tc3_kernel, decoder level-3 conv 128->128 3x3 fprop: M=%d K=1152 N=128, timed alone"
+                                            % (B * (H // 2) * (W // 2)),
+                                  "us": dom["us"], "achieved": dom["tflops"], "peak": peaks["tf_burst"],
+                                  "frac": dom["tflops"] / peaks["tf_burst"], "traffic": traffic,
+                                  "peak_source": peaks["src"] + " (burst bf16: kernel timed alone)"}
+            # BASELINE metric part 2 ("warp+loss HBM GB/s", configs[1]) in the same run
+            roof["loss_fused"] = loss_kernel_leg(torch, dev, B, H, W, rank, peaks)
+        else:
+            roof.update({"achieved": step_tf, "frac": step_tf / peaks["tf_sust"], "traffic": None,
+                         "kernel": "whole step (--no-extras: no per-kernel timeline)"})
     else:
         roof = {"bound": "tensor", "achieved": step_tf, "peak": peaks["tf_sust"], "unit": "TFLOP/s",
                 "frac": step_tf / peaks["tf_sust"], "traffic": None,
                 "kernel": "gemm_simt_kernel (fp32 SIMT parity mode, whole step)", "algorithmic_flops": flops,
                 "peak_source": peaks["src"]}
-    return {"metric": train_metric(H, W), "value": value, "unit": "image-pairs/s",
+    line = {"metric": train_metric(H, W), "value": value, "unit": "image-pairs/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": per,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "bf16" if args.conv_mode == "bf16" else "f32", "data": "synthetic",
-            "config": train_config(B, H, W, world, args.conv_mode),
+            "config": train_config(B, H, W, world, args.conv_mode, args.scaling),
             "roofline": roof, "e2e": e2e, "gpu_launches": launches if launches else None, "clocks": ck}
+    if dist_stats is not None:
+        line["distribution"] = dist_stats
+    line.update(line_extra)
+    return line
 
 
 if __name__ == "__main__":

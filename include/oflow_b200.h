@@ -48,6 +48,14 @@ unsigned long long of_launch_count(void);
  * "OF_LOSS_GENERIC": direct-gather loss kernel).  value NULL unsets.  Process-wide, not thread-safe against
  * concurrent launches; meant for tests and tuning scripts.  The shipped library reads NO environment variables. */
 int of_set_option(const char* name, const char* value);
+/* Per-launch timeline, for bench.py's in-step kernel shares (no ncu needed): after of_prof_enable(1, stream) every
+ * launch this library makes records a CUDA event on `stream` (all launches must go to that one stream; not during
+ * graph capture); of_prof_collect synchronises and returns up to max_recs records (launch order): kernel name, the
+ * device time since the previous launch's end, and the work (FLOPs) the host code noted for it (0 = not noted).
+ * of_prof_enable(0, NULL) switches it off. */
+typedef struct { char name[40]; double work; float ms; } of_prof_rec;
+int of_prof_enable(int on, void* stream);
+int of_prof_collect(of_prof_rec* out, int max_recs);
 
 /* ---- sampler ------------------------------------------------------------
  * transformations.py:85-129 bilinear_interpolation (+ :70-81 gather).
@@ -299,6 +307,10 @@ int of_bn_fold_bwd_batch(const of_bn_job* jobs_device, int njobs, int total_bloc
  * (the np.random.rand() < 0.5 branch of :46-51 is drawn by the caller). */
 int of_preprocess_pair(const uint8_t* img1, const uint8_t* img2, int src_h, int src_w, float* out,
                        int H, int W, int flip, void* stream);
+/* The whole batch in one launch: frames = (B, 2, src_h, src_w, 3) uint8 in device memory (one H2D copy of the
+ * decoded pairs), out = (B, H, W, 6) f32; flips = B HOST bytes (nullable = no swaps). */
+int of_preprocess_batch(const uint8_t* frames, int B, int src_h, int src_w, float* out, int H, int W,
+                        const uint8_t* flips, void* stream);
 
 /* ---- depth / pose re-projection ---------------------------
  * transformations.py:12-67,133-191.  points are (B,H,W,4) f32 homogeneous, depth (B,H,W,1) f32, pixel

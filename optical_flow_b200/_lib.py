@@ -72,6 +72,11 @@ class BnJob(C.Structure):
                [("K", C.c_int), ("Cout", C.c_int), ("fwd_block_begin", C.c_int), ("bwd_block_begin", C.c_int)]
 
 
+class ProfRec(C.Structure):
+    """of_prof_rec (include/oflow_b200.h)."""
+    _fields_ = [("name", C.c_char * 40), ("work", C.c_double), ("ms", C.c_float)]
+
+
 OF_BN_FWD_BLOCK = 2048
 
 # name -> (restype, argtypes); must list every symbol include/oflow_b200.h declares
@@ -94,6 +99,8 @@ PROTOTYPES = {
     "of_last_error": (C.c_char_p, []),
     "of_launch_count": (C.c_ulonglong, []),
     "of_set_option": (C.c_int, [C.c_char_p, C.c_char_p]),
+    "of_prof_enable": (C.c_int, [C.c_int, C.c_void_p]),
+    "of_prof_collect": (C.c_int, [C.POINTER(ProfRec), C.c_int]),
     "of_bilinear_sample_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_bilinear_sample_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_warp_features_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
@@ -107,6 +114,7 @@ PROTOTYPES = {
     "of_cost_volume_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_cost_volume_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_preprocess_pair": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _i, _vp]),
+    "of_preprocess_batch": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "of_flow_head_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_cost_volume_bwd_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "of_loss_workspace_bytes": (_sz, [_i, _i, _i, _i]),
@@ -186,6 +194,19 @@ class option:
     def __exit__(self, *exc):
         load().of_set_option(self.name, None)
         return False
+
+
+def timeline(fn, max_recs=8192):
+    """Run ``fn()`` with the per-launch timeline on (current stream); returns [(kernel name, ms, work), ...]."""
+    lib = load()
+    check(lib.of_prof_enable(1, stream_ptr()), "of_prof_enable")
+    try:
+        fn()
+    finally:
+        recs = (ProfRec * max_recs)()
+        n = lib.of_prof_collect(recs, max_recs)
+        lib.of_prof_enable(0, None)
+    return [(recs[i].name.decode(), float(recs[i].ms), float(recs[i].work)) for i in range(n)]
 
 
 def check(rc: int, what: str = ""):

@@ -75,8 +75,12 @@ static inline cudaError_t of_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim
 }
 #endif
 
+void of_prof_mark(const char* what);   // util.cu: event after this launch when the timeline is enabled
+void of_prof_note(double work);        // util.cu: FLOPs (or bytes) of the NEXT launch, for the timeline
+
 static inline int of_launch_check(const char* what) {
   of_count_launch();
+  of_prof_mark(what);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     of_set_error("launch of %s failed: %s", what, cudaGetErrorString(e));

@@ -386,6 +386,8 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   OF_REQUIRE(c->n_rows >= c->n_valid && c->k_pad % 64 == 0 && of_valid_dtype(c->out_dtype), OF_ERR_SHAPE,
              "bad packed weight dims / out dtype");
   for (int s = 0; s < c->num_src; ++s) OF_REQUIRE(c->src[s] && c->src_c[s] > 0, OF_ERR_ARG, "bad source %d", s);
+  of_prof_note(2.0 * c->N * c->Ho * c->Wo * (double)(c->src_c[0] + (c->num_src == 2 ? c->src_c[1] : 0)) * c->n_valid *
+               c->KH * c->KW);
   if (int r = of_conv_tc3_try(c, stream)) return r < 0 || r > 1 ? r : 0;    // 3x3 / stride-1 fast path
   OF_REQUIRE(c->out2 == nullptr, OF_ERR_UNSUPPORTED, "split outputs are a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
   OF_REQUIRE(c->sign_out == nullptr && !(c->mask != nullptr && c->mask_dtype == 2), OF_ERR_UNSUPPORTED,

@@ -333,6 +333,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");
   OF_REQUIRE(c->stride == 1 || c->stride == 2, OF_ERR_UNSUPPORTED, "stride %d unsupported", c->stride);
   OF_REQUIRE(c->Cout >= 1 && c->Cout <= 256 && c->dy_c >= c->Cout, OF_ERR_SHAPE, "Cout %d unsupported", c->Cout);
+  of_prof_note(2.0 * c->N * c->Ho * c->Wo * (double)c->Cin * c->Cout * c->KH * c->KW);
   cudaStream_t st = (cudaStream_t)stream;
   const int taps = c->KH * c->KW;
   OF_CUDA(cudaMemsetAsync(c->dw, 0, (size_t)taps * c->Cin * c->Cout * sizeof(float), st));

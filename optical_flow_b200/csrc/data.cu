@@ -32,11 +32,21 @@ __device__ __forceinline__ AxisTap axis_tap(int d, double scale, int src, bool v
   return t;
 }
 
+// blockIdx.y = item of the batch: frames (items, 2, sh, sw, 3) uint8, out (items, H, W, 6); bit i of flip_mask swaps
+// pair i.  With item_stride == 0 (single-item entry point) img1 / img2 are the two frames themselves.
 __global__ void __launch_bounds__(256)
-preprocess_pair_kernel(const uint8_t* __restrict__ img1, const uint8_t* __restrict__ img2, int sh, int sw,
-                       float* __restrict__ out, int H, int W, double scale_y, double scale_x, double m0, double m1,
-                       double m2) {
+preprocess_pair_kernel(const uint8_t* __restrict__ img1, const uint8_t* __restrict__ img2, size_t item_stride,
+                       unsigned long long flip_mask, int sh, int sw, float* __restrict__ out, int H, int W,
+                       double scale_y, double scale_x, double m0, double m1, double m2) {
   const size_t total = (size_t)H * W * 2;
+  if (item_stride != 0) {
+    const uint8_t* a = img1 + (size_t)blockIdx.y * item_stride;
+    const uint8_t* b = a + (size_t)sh * sw * 3;
+    const bool flip = (flip_mask >> blockIdx.y) & 1ull;
+    img1 = flip ? b : a;
+    img2 = flip ? a : b;
+    out += (size_t)blockIdx.y * H * W * 6;
+  }
   const bool same = sh == H && sw == W;                              // cv2.resize returns a copy
   for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
     const int which = (int)(e & 1);
@@ -80,10 +90,33 @@ int of_preprocess_pair(const uint8_t* img1, const uint8_t* img2, int src_h, int 
   size_t total = (size_t)H * W * 2;
   size_t blocks = (total + 255) / 256;
   if (blocks > (size_t)OF_NUM_SMS * 8) blocks = (size_t)OF_NUM_SMS * 8;
-  preprocess_pair_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(flip ? img2 : img1, flip ? img1 : img2, src_h,
-                                                                        src_w, out, H, W, scale_y, scale_x,
+  preprocess_pair_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(flip ? img2 : img1, flip ? img1 : img2, 0, 0ull,
+                                                                        src_h, src_w, out, H, W, scale_y, scale_x,
                                                                         123.0 / 255.0, 117.0 / 255.0, 104.0 / 255.0);
   return of_launch_check("preprocess_pair_kernel");
+}
+
+int of_preprocess_batch(const uint8_t* frames, int B, int src_h, int src_w, float* out, int H, int W,
+                        const uint8_t* flips, void* stream) {
+  OF_REQUIRE(frames && out, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(B > 0 && src_h > 0 && src_w > 0 && H > 0 && W > 0, OF_ERR_SHAPE, "bad batch dims");
+  const double scale_x = 1.0 / ((double)W / (double)src_w), scale_y = 1.0 / ((double)H / (double)src_h);
+  const size_t item = (size_t)2 * src_h * src_w * 3;
+  size_t total = (size_t)H * W * 2;
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = ((size_t)OF_NUM_SMS * 16 + B - 1) / B;           // ~16 CTAs per SM over the whole batch
+  if (blocks > cap) blocks = cap;
+  for (int b0 = 0; b0 < B; b0 += 64) {                                // 64 flip bits per launch
+    const int nb = B - b0 < 64 ? B - b0 : 64;
+    unsigned long long mask = 0ull;
+    if (flips)
+      for (int i = 0; i < nb; ++i) mask |= (unsigned long long)(flips[b0 + i] != 0) << i;
+    preprocess_pair_kernel<<<dim3((unsigned)blocks, (unsigned)nb), 256, 0, (cudaStream_t)stream>>>(
+        frames + (size_t)b0 * item, nullptr, item, mask, src_h, src_w, out + (size_t)b0 * H * W * 6, H, W, scale_y, scale_x,
+        123.0 / 255.0, 117.0 / 255.0, 104.0 / 255.0);
+    if (int r = of_launch_check("preprocess_pair_kernel")) return r;
+  }
+  return 0;
 }
 
 }  // extern "C"

@@ -1,5 +1,6 @@
 // Error string + version of liboflow_b200.
 #include "common.cuh"
+#include <string.h>
 
 static thread_local char g_err[512] = "";
 
@@ -12,6 +13,66 @@ void of_set_error(const char* fmt, ...) {
 
 static unsigned long long g_launches = 0;
 void of_count_launch(void) { __atomic_fetch_add(&g_launches, 1ull, __ATOMIC_RELAXED); }
+
+// ---- per-launch timeline (of_prof_*): one CUDA event after every launch of this library on the profiled stream;
+// the duration of launch k is event[k] - event[k-1] (one stream, in order), so bench.py can report the live,
+// in-step time of each kernel class without ncu.  Off by default: of_prof_mark() is one predictable branch.
+#define OF_PROF_MAX 8192
+static bool g_prof_on = false;
+static cudaStream_t g_prof_stream = nullptr;
+static cudaEvent_t g_prof_ev[OF_PROF_MAX + 1];
+static int g_prof_nev_created = 0;
+static int g_prof_n = 0;
+static struct { char name[40]; double work; } g_prof_rec[OF_PROF_MAX];
+static double g_prof_pending_work = 0.0;
+
+void of_prof_note(double work) { if (g_prof_on) g_prof_pending_work = work; }
+
+void of_prof_mark(const char* what) {
+  if (!g_prof_on || g_prof_n >= OF_PROF_MAX) return;
+  const int k = g_prof_n + 1;
+  if (k >= g_prof_nev_created) {
+    if (cudaEventCreate(&g_prof_ev[k]) != cudaSuccess) { g_prof_on = false; return; }
+    g_prof_nev_created = k + 1;
+  }
+  if (cudaEventRecord(g_prof_ev[k], g_prof_stream) != cudaSuccess) { cudaGetLastError(); return; }   // e.g. capturing
+  strncpy(g_prof_rec[g_prof_n].name, what, sizeof(g_prof_rec[0].name) - 1);
+  g_prof_rec[g_prof_n].name[sizeof(g_prof_rec[0].name) - 1] = 0;
+  g_prof_rec[g_prof_n].work = g_prof_pending_work;
+  g_prof_pending_work = 0.0;
+  ++g_prof_n;
+}
+
+extern "C" int of_prof_enable(int on, void* stream) {
+  g_prof_on = false;
+  g_prof_n = 0;
+  g_prof_pending_work = 0.0;
+  if (!on) return 0;
+  g_prof_stream = (cudaStream_t)stream;
+  if (g_prof_nev_created == 0) {
+    OF_CUDA(cudaEventCreate(&g_prof_ev[0]));
+    g_prof_nev_created = 1;
+  }
+  OF_CUDA(cudaEventRecord(g_prof_ev[0], g_prof_stream));
+  g_prof_on = true;
+  return 0;
+}
+
+extern "C" int of_prof_collect(of_prof_rec* out, int max_recs) {
+  const bool was_on = g_prof_on;
+  g_prof_on = false;
+  if (g_prof_n > 0) OF_CUDA(cudaEventSynchronize(g_prof_ev[g_prof_n]));
+  int n = g_prof_n < max_recs ? g_prof_n : max_recs;
+  for (int i = 0; i < n; ++i) {
+    float ms = 0.f;
+    OF_CUDA(cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[i + 1]));
+    memcpy(out[i].name, g_prof_rec[i].name, sizeof(out[i].name));
+    out[i].work = g_prof_rec[i].work;
+    out[i].ms = ms;
+  }
+  g_prof_on = was_on;
+  return n;
+}
 
 // ---- kernel-variant options (of_set_option): a tiny process-wide table, empty by default --------------------
 #include <string.h>

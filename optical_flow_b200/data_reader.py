@@ -59,3 +59,22 @@ def read_batch(frame_pairs, opts, flips=None, device=None):
         keep.append(item._keepalive)
     batch._keepalive = keep
     return batch
+
+
+def read_batch_frames(frames, opts, flips=None, out=None):
+    """The same batch assembly from ONE device tensor of decoded pairs, frames = (B, 2, h, w, 3) uint8 (a single
+    pinned host -> device copy of 6 bytes per pixel pair instead of 24 bytes of float32), one launch for the whole
+    batch (of_preprocess_batch).  ``flips``: None = no swaps, else B booleans (data_reader.py:46-51 drawn by the caller)."""
+    assert frames.dtype == torch.uint8 and frames.dim() == 5 and frames.shape[1] == 2 and frames.shape[4] == 3
+    assert frames.is_cuda and frames.is_contiguous()
+    B, _, h, w, _ = frames.shape
+    if out is None:
+        out = torch.empty((B, opts.img_height, opts.img_width, 6), dtype=torch.float32, device=frames.device)
+    assert out.is_contiguous() and tuple(out.shape) == (B, opts.img_height, opts.img_width, 6)
+    fl = None
+    if flips is not None:
+        import ctypes
+        fl = (ctypes.c_uint8 * B)(*[1 if f else 0 for f in flips])
+    L.check(L.load().of_preprocess_batch(L.ptr(frames), B, h, w, L.ptr(out), opts.img_height, opts.img_width, fl,
+                                         L.stream_ptr()), "of_preprocess_batch")
+    return out

@@ -127,6 +127,31 @@ class HostBatchPrefetcher:
         return self.bufs[slot], (lambda: self.free[slot].record(cur))
 
 
+class HostFramePrefetcher(HostBatchPrefetcher):
+    """The data path of data_reader.py:35-64 feeding ``Trainer.train_step``: ``batches`` yields pinned uint8 CPU
+    tensors (B, 2, h, w, 3) of decoded frame pairs (6 bytes per pixel pair over PCIe instead of 24 bytes of float32);
+    the copy of batch i+1 runs on a copy stream under the compute of batch i, and one of_preprocess_batch launch on
+    the compute stream turns the frames into the (B, H, W, 6) float32 network input (resize, / 255, BGR means)."""
+
+    def __init__(self, batches, device, height, width):
+        from .data_reader import ReaderOpts
+        self.opts = ReaderOpts(img_height=height, img_width=width)
+        self.net_in = [None, None]
+        super().__init__(batches, device)
+
+    def __next__(self):
+        from .data_reader import read_batch_frames
+        slot = self.pending                                   # the buffer pair this batch uses (None -> StopIteration)
+        frames, release = super().__next__()
+        B = frames.shape[0]
+        if self.net_in[slot] is None or self.net_in[slot].shape[0] != B:
+            self.net_in[slot] = torch.empty((B, self.opts.img_height, self.opts.img_width, 6), dtype=torch.float32,
+                                            device=self.device)
+        x = read_batch_frames(frames, self.opts, out=self.net_in[slot])
+        release()                                             # the uint8 buffer is free once the kernel is queued
+        return x, (lambda: None)
+
+
 _default_trainer = None
 
 

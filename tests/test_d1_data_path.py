@@ -65,3 +65,18 @@ def test_cuda_read_batch_full_size(cuda):
     batch = R.read_batch(pairs, opts, flips=[False, True], device=cuda).cpu().numpy()
     for i, (f1, f2) in enumerate(pairs):
         assert np.array_equal(batch[i], D.read_item(f1, f2, 384, 1280, flip=bool(i)))
+
+
+@pytest.mark.gpu
+def test_cuda_read_batch_frames_one_launch(cuda):
+    """of_preprocess_batch (one H2D copy of the uint8 pairs + one launch) == the per-item path, with and without resize."""
+    import torch
+    from optical_flow_b200 import data_reader as R
+    r = np.random.default_rng(6)
+    for (sh, sw, oh, ow) in ((375, 1242, 384, 1280), (48, 64, 48, 64)):
+        frames = r.integers(0, 256, (3, 2, sh, sw, 3), dtype=np.uint8)
+        flips = [False, True, False]
+        opts = R.ReaderOpts(batch_size=3, img_height=oh, img_width=ow)
+        got = R.read_batch_frames(torch.from_numpy(frames).to(cuda), opts, flips=flips).cpu().numpy()
+        for i in range(3):
+            assert np.array_equal(got[i], D.read_item(frames[i, 0], frames[i, 1], oh, ow, flip=flips[i]))
