@@ -261,6 +261,8 @@ def main():
     ap.add_argument("--flows", default="smooth", choices=["smooth", "iid"],
                     help="loss workload: flow field statistics (SURVEY 8d: realistic smooth / worst-case i.i.d.)")
     ap.add_argument("--no-graph", action="store_true", help="time direct launches instead of CUDA graph replay")
+    ap.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
+                    help="kernel-variant option passed to of_set_option (A/B runs; recorded in config.options)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -279,10 +281,17 @@ def main():
         build.build_library()
     if world > 1:
         dist.barrier()
+    if args.option:
+        from optical_flow_b200 import _lib as L
+        for kv in args.option:
+            name, _, val = kv.partition("=")
+            L.check(L.load().of_set_option(name.encode(), (val or "1").encode()), "of_set_option")
     if args.workload == "loss":
         line = bench_loss(args, dev, world, rank)
     else:
         line = bench_train(args, dev, world, rank)
+    if args.option:
+        line["config"]["options"] = list(args.option)
     if rank == 0:
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = (cpu_loss_baseline(args.batch) if args.workload == "loss" else

@@ -232,6 +232,8 @@ __global__ void __launch_bounds__(256) fused_loss_kernel(const __grid_constant__
 // fast path (loss_fused.cu): H, W multiples of 16, power-of-two pyramid
 size_t of_lf_workspace_bytes(int B, int H, int W, int num_scales);
 bool of_lf_supported(int B, int H, int W, int num_scales, const int* hs, const int* ws);
+int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flows, const int* hs, const int* ws,
+               int num_scales, float* loss, int B, int H, int W, int mode, void* workspace, void* stream);
 int of_lf_run(const float* imgs, const float* const* flows, float* const* d_flows, const int* hs, const int* ws,
               int num_scales, float* loss, int B, int H, int W, int mode, void* workspace, void* stream);
 
@@ -305,7 +307,10 @@ int of_loss_l1_pyramid_fwdbwd(const float* imgs, const float* const* flows, floa
   OF_REQUIRE(imgs && flows && hs && ws && loss && workspace, OF_ERR_ARG, "null pointer argument");
   if (of_lf_supported(B, H, W, num_scales, hs, ws) && !of_tune_env("OF_LOSS_GENERIC")) {
     for (int s = 0; s < num_scales; ++s) OF_REQUIRE(flows[s] != nullptr, OF_ERR_ARG, "flow %d is null", s);
-    return of_lf_run(imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
+    // warp-specialised kernel (loss_fused2.cu) by default; option OF_LF_V1 selects the first-generation kernel
+    if (of_tune_env("OF_LF_V1"))
+      return of_lf_run(imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
+    return of_lf2_run(imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
   }
   return run_loss(0, imgs, flows, d_flows, hs, ws, num_scales, loss, B, H, W, mode, workspace, stream);
 }

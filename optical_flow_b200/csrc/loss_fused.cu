@@ -20,6 +20,7 @@
 #include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "loss_fused_common.cuh"
 
 #define LF_MAX_SCALES 4
 #define LF_ROWS 32           // full-resolution rows per build unit
@@ -69,70 +70,6 @@ struct LfParams {
   int total_units;
 };
 
-__device__ __forceinline__ uint64_t policy_evict_first() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint64_t policy_evict_last() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar,
-                                          uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-      ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_3d_hint(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                                 int c2, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
-      ::"r"(tc::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1),
-      "r"(c2), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_4d_hint(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                                 int c2, int c3, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
-      ::"r"(tc::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1),
-      "r"(c2), "r"(c3), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ void st_f4_policy(float4* p, float4 v, uint64_t policy) {
-  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
-               "f"(v.w), "l"(policy)
-               : "memory");
-}
-__device__ __forceinline__ float4 ld_f4_policy(const float4* p, uint64_t policy) {
-  float4 v;
-  asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "l"(p), "l"(policy)
-               : "memory");
-  return v;
-}
-// poll with relaxed loads (an acquire load invalidates the SM's L1 on every iteration); the caller
-// issues ONE acquire fence after the value has been seen
-__device__ __forceinline__ unsigned ld_relaxed(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(tc::smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(LF_CONSUMERS) : "memory"); }
 
 // unit index -> (is_build, image, local index).  Order: build(0..L-1), then pairs
@@ -152,15 +89,6 @@ __device__ __forceinline__ void decode_unit(const LfParams& P, int u, bool* buil
   v -= pairs * per;
   int k = v / P.ng;
   *build = false; *b = pairs + k; *local = v - k * P.ng;
-}
-
-__device__ __forceinline__ int lf_clamp(int v, int lo, int hi) { return min(max(v, lo), hi); }
-__device__ __forceinline__ float lf_sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
-
-// tf.image.resize at an integer factor 2^k: t = 0.5 on both axes (same op order as loss.cu fetch_resized)
-__device__ __forceinline__ float lf_mean4(float a, float b, float c, float d) {
-  float top = a + (b - a) * 0.5f, bot = c + (d - c) * 0.5f;
-  return top + (bot - top) * 0.5f;
 }
 
 // one resized pixel of BOTH frames from the staged patch: the central 2x2 block starting at

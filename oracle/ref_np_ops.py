@@ -117,8 +117,10 @@ def create_cost_volume_bwd(features1, features2, max_disp, d_cv):
 # loss.py:5-32 LossLayer
 # ---------------------------------------------------------------------------
 
-def loss_layer(batch_imgs, flows, return_grads=False):
-    """loss.py:5-32.  Returns loss (float32 scalar) and optionally d_flows.
+def loss_layer(batch_imgs, flows, return_grads=False, return_diffs=False):
+    """loss.py:5-32.  Returns loss (float32 scalar) and optionally d_flows (and, with return_diffs, the per-scale
+    photometric differences im1 - warped: |diff| ~ 1 ulp marks the pixels whose sign(diff) - hence whose whole
+    d_flow - is an fp32 tie-break, which large-shape tests exclude from max-abs bounds).
 
     Forward in fp32 like the reference; the mean/sum and the backward are
     accumulated in float64 (the "exact" value the CUDA reduction is held to)."""
@@ -126,6 +128,7 @@ def loss_layer(batch_imgs, flows, return_grads=False):
     num_scales = len(flows)
     loss = 0.0
     d_flows = []
+    diffs = []
     for s in range(num_scales):
         sh = int(imgs.shape[1] / (2.0 ** (s + 1)))   # :11
         sw = int(imgs.shape[2] / (2.0 ** (s + 1)))   # :12
@@ -137,6 +140,7 @@ def loss_layer(batch_imgs, flows, return_grads=False):
         warped = R.warp_features(flow, im2)          # :26
         diff = (im1 - warped).astype(F32)
         n = diff.size
+        diffs.append(diff)
         loss += float(np.sum(np.abs(diff), dtype=np.float64)) / n   # :28 reduce_mean
         if return_grads:
             # d|d|/dwarped = -sign(diff) (tf.abs grad = sign, sign(0)=0); /n mean; /num_scales (:30)
@@ -144,6 +148,8 @@ def loss_layer(batch_imgs, flows, return_grads=False):
             _, d_flow = R.warp_features_bwd(flow, im2, d_warped)
             d_flows.append(d_flow)
     loss = F32(loss / float(num_scales))             # :30
+    if return_grads and return_diffs:
+        return loss, d_flows, diffs
     if return_grads:
         return loss, d_flows
     return loss

@@ -4,7 +4,8 @@ Everything else in tests/ runs at shapes the oracle finishes instantly; this fil
 tile / TMA-box / grid arithmetic is also right where bench.py measures:
 
   (i)   LossLayer fast path (loss_fused.cu) vs oracle.ref_np_ops.loss_layer at 8 x 384 x 1280 and 1 x 1024 x 2048
-        (loss.py:5-32): loss 1e-5 relative, every d_flow 1e-5 of max-abs.
+        (loss.py:5-32): loss 1e-5 relative, every d_flow within 1e-5 of max-abs plus the cancellation-aware term of
+        dflow_bound() (clipped taps carry weights of magnitude w - h in the reference's transposed sampling).
   (ii)  a whole fp32-mode step (forward, loss, all gradients) vs oracle.ref_torch.FlowNetRef at 1 x 384 x 1280.
   (iii) bf16 tensor-core mode vs the repo's own fp32 mode at 2 x 384 x 1280 with the warp coordinates pinned to the
         fp32 run's and the SAME d_flows fed to both backward passes: per-tensor relative L2 of every weight gradient
@@ -21,6 +22,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import ref_np as R
 from oracle import ref_np_ops as O
 from oracle import ref_torch as T
 
@@ -55,6 +57,24 @@ def rel_l2(got, exp):
     return float(np.linalg.norm(got - exp) / max(np.linalg.norm(exp), 1e-30))
 
 
+def dflow_bound(flow, e_d, num_scales=4):
+    """Cancellation-aware fp32 bound for d loss / d flow of LossLayer: 1e-5 of max|ref| plus the rounding of the two
+    products that cancel when a tap pair is clipped.  The reference forms its weights from the CLIPPED x1 / y1
+    (transformations.py:98-112), and its transposed sampling (model.py:65-71: y = column + flow, clipped to h - 1)
+    puts every column j >= h out of range, so |weight| reaches w - h (hundreds): d = a (v10 - v00) + (1 - a)(v11 - v01)
+    with v10 - v00 == v11 - v01 is the difference of two products ~|a| times larger than the result, and an fp32
+    kernel legitimately carries |a| ulps there (the float64 oracle does not)."""
+    B, h, w, _ = flow.shape
+    pts = (R.warp_grid(h, w) + flow).astype(np.float32)
+    x0, x1, y0, y1 = R.sample_indices(pts, h, w)
+    ax = np.abs(x1.astype(np.float32) - pts[..., 0])
+    ay = np.abs(y1.astype(np.float32) - pts[..., 1])
+    wmag = np.stack([ay + np.abs(1 - ay), ax + np.abs(1 - ax)], axis=-1)      # d0 uses (ay, by); d1 uses (ax, bx)
+    inv_n = 1.0 / (B * h * w * 3.0 * num_scales)
+    eps = 2.0 ** -24
+    return 1e-5 * np.abs(e_d).max() + 4 * eps * wmag * (3 * 1.2) * inv_n      # 3 channels, |pixel difference| <= 1.2
+
+
 # ------------------------------------------------------------------ (i) fused loss vs the oracle --
 @pytest.mark.parametrize("B,H,W", [(8, 384, 1280), (1, 1024, 2048), (4, 1024, 2048)])
 @pytest.mark.parametrize("flows_kind", ["iid", "smooth"])
@@ -74,7 +94,13 @@ def test_loss_layer_oracle_at_bench_shape(cuda, B, H, W, flows_kind):
             f = torch.nn.functional.interpolate(c, size=(h, w), mode="bilinear", align_corners=False)
             f = (f * (4.0 / 2 ** s) / f.std()).permute(0, 2, 3, 1).contiguous()
         flows.append(f.numpy().astype(np.float32))
-    e_loss, e_d = O.loss_layer(imgs, flows, return_grads=True)
+    e_loss, e_d, e_diff = O.loss_layer(imgs, flows, return_grads=True, return_diffs=True)
+    # d loss / d flow carries sign(im1 - warped) (loss.py:28): where a channel's |diff| is within a few fp32 ulps of 0
+    # the sign is a rounding tie-break and that pixel's whole gradient may legitimately flip; with millions of pixels
+    # such ties exist (measured 2-6e-5 of the pixels), so they are excluded from the max-abs bound - and counted
+    firm = [np.abs(d).min(axis=-1) >= 2e-6 for d in e_diff]
+    for s in range(4):
+        assert firm[s].mean() > 0.999, (s, firm[s].mean())
     layer = LossLayer()
     x = torch.tensor(imgs, device=cuda)
     fd = [torch.tensor(f, device=cuda) for f in flows]
@@ -82,7 +108,9 @@ def test_loss_layer_oracle_at_bench_shape(cuda, B, H, W, flows_kind):
         loss = layer(x, fd)
         assert abs(loss.item() - float(e_loss)) <= 1e-5 * abs(float(e_loss)), (loss.item(), float(e_loss))
         for s in range(4):
-            assert rel_err(layer.d_flows[s], e_d[s]) <= 1e-5, (s, rel_err(layer.d_flows[s], e_d[s]))
+            got = layer.d_flows[s].cpu().numpy()
+            excess = (np.abs(got - e_d[s]) - dflow_bound(flows[s], e_d[s])).max(axis=-1)
+            assert excess[firm[s]].max() <= 0, (s, excess[firm[s]].max() / np.abs(e_d[s]).max())
 
 
 # ------------------------------------------------------------------ (ii) fp32 step vs the oracle --
@@ -112,12 +140,12 @@ def test_fp32_step_oracle_at_384x1280(cuda):
     record("fp32_step_384x1280", {"loss": loss.item(), "ref_loss": r_loss.item(), "rel_l2": rows})
     # a warp index flips where an fp32-noisy flow crosses an integer (isolated pixels); relative L2 per tensor
     worst = max(rows.items(), key=lambda kv: kv[1])
-    assert worst[1] < 5e-3, worst
+    assert worst[1] < 1e-3, worst          # measured on B200: worst 1.1e-4 (flow1_conv3/kernel)
 
 
 # ------------------------------------------------------------------ (iii) bf16 vs fp32 mode --
-BF16_GRAD_REL_L2 = 0.12          # stated bf16 tolerance per weight tensor with pinned warp coordinates (measured: see
-BF16_GRAD_REL_L2_MEDIAN = 0.04   # profiles/r02_parity_summary.md); bf16 operand rounding through ~20 stacked convs
+BF16_GRAD_REL_L2 = 0.05          # stated bf16 tolerance per weight tensor with pinned warp coordinates (measured on
+BF16_GRAD_REL_L2_MEDIAN = 0.02   # B200: worst 0.0205 conv1/kernel, median 0.0108; profiles/r02_parity_summary.md)
 
 
 def test_bf16_vs_fp32_mode_frozen_warp_384x1280(cuda):
