@@ -261,6 +261,10 @@ def main():
     ap.add_argument("--flows", default="smooth", choices=["smooth", "iid"],
                     help="loss workload: flow field statistics (SURVEY 8d: realistic smooth / worst-case i.i.d.)")
     ap.add_argument("--no-graph", action="store_true", help="time direct launches instead of CUDA graph replay")
+    ap.add_argument("--graph", default="on", choices=["on", "off"],
+                    help="train workload: replay the whole step from one CUDA graph (Trainer.enable_graph) or launch eagerly")
+    ap.add_argument("--dump-timeline", default=None, metavar="PATH",
+                    help="train workload: write the per-launch records (kernel, us, FLOPs) of the timeline pass as JSON")
     ap.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
                     help="kernel-variant option passed to of_set_option (A/B runs; recorded in config.options)")
     args = ap.parse_args()
@@ -532,6 +536,14 @@ def bench_train(args, dev, world, rank):
     tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm)
     nsets = 2
     batches = [synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev) for k in range(nsets)]
+    launch_mode = "eager (one ctypes call per kernel)"
+    if args.graph == "on":
+        try:
+            tr.enable_graph(batches[0])
+            launch_mode = "one CUDA graph launch per step (+ a device-to-device copy of the batch into the graph's input)"
+        except Exception as e:          # noqa: BLE001 - say so and time the eager path
+            tr._graph = None
+            sys.stderr.write("CUDA graph capture of the train step failed (%s); eager launches\n" % e)
 
     def run(n):
         for i in range(n):
@@ -544,6 +556,8 @@ def bench_train(args, dev, world, rank):
     clocks.mark()
     ms = _timed(torch, dist, world, run, args.steps)
     launches = L.load().of_launch_count() - launches_before
+    if tr._graph is not None:           # replayed launches are not counted by the library: kernels per captured step
+        launches = args.steps * getattr(tr, "graph_kernels", 0)
     per = ms / args.steps
     value = world * B / (per * 1e-3)
 
@@ -601,7 +615,12 @@ def bench_train(args, dev, world, rank):
         if not args.no_extras:
             # FLOP-weighted in-step figure: all tensor-core conv launches of the step, timed live by the library's
             # per-launch CUDA-event timeline over 3 steps
-            agg, _ = step_timeline(tr, batches)
+            graph_saved, tr._graph = tr._graph, None     # the per-launch events need eager launches
+            agg, recs = step_timeline(tr, batches)
+            tr._graph = graph_saved
+            if args.dump_timeline and rank == 0:
+                with open(args.dump_timeline, "w") as f:
+                    json.dump([{"kernel": n, "us": ms * 1e3, "flops": w} for n, ms, w in recs], f)
             tc_us = sum(v["us"] for k, v in agg.items() if k in TC_CONV_KERNELS)
             tot_us = sum(v["us"] for v in agg.values())
             ach = tc_flops / (tc_us * 1e-6) / 1e12
@@ -640,7 +659,7 @@ def bench_train(args, dev, world, rank):
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": per,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "bf16" if args.conv_mode == "bf16" else "f32", "data": "synthetic",
-            "config": train_config(B, H, W, world, args.conv_mode, args.scaling),
+            "config": dict(train_config(B, H, W, world, args.conv_mode, args.scaling), launch=launch_mode),
             "roofline": roof, "e2e": e2e, "gpu_launches": launches if launches else None, "clocks": ck}
     if dist_stats is not None:
         line["distribution"] = dist_stats

@@ -349,6 +349,13 @@ int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n,
                  int step, float lr, float beta1, float beta2, float eps,
                  float grad_scale, void* stream);
 
+/* The same update with the optimiser state in device memory: *state holds the number of COMPLETED steps and the
+ * learning rate; the call applies step (state->step + 1) and then increments state->step on the stream.  No host
+ * scalar that changes from step to step is a kernel argument, so a captured CUDA graph of the train step replays. */
+typedef struct { int step; float lr; } of_adam_state;
+int of_adam_step_dev(float* param, const float* grad, float* m, float* v, size_t n, of_adam_state* state,
+                     float beta1, float beta2, float eps, float grad_scale, void* stream);
+
 /* ---- training-mode BatchNormalization (OPT-IN) --------------
  * The reference's step runs layers.BatchNormalization (model.py:14; resnet/models.py:19,24) in inference mode
  * (SURVEY F5), which is what of_bn_fold_* implement; these four passes are the batch-statistics variant.

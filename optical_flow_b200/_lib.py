@@ -146,6 +146,7 @@ PROTOTYPES = {
     "of_bn_fold_fwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_bn_fold_bwd_batch": (_i, [_vp, _i, _i, _f, _vp]),
     "of_adam_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
+    "of_adam_step_dev": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _f, _f, _f, _f, _vp]),
     "of_bn_train_workspace_bytes": (_sz, [_i]),
     "of_bn_train_stats": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _i, _vp, _vp]),
     "of_bn_train_apply": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _f, _i, _vp, _vp, _vp, _f, _sz, _i, _i, _vp]),

@@ -62,6 +62,8 @@ struct L2fParams {
   int ngu;               // gather tiles per image
   int tile_i, tile_j;    // gather tile shape (REF_IJ 8 x 16, XY 4 x 32)
   int total_build, total_gather;
+  int dbg;               // -DOF_PROFILE_HOOKS only: 1 no build math / stores, 2 no gather, 4 gather does not wait for
+                         // the builds, 8 no release fence + counter, 16 no image stream at all (with 4: gather only)
 };
 
 __device__ __forceinline__ void st_release_cta_shared(unsigned* p, unsigned v) {
@@ -162,7 +164,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
   float acc = 0.f;
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (lane == 0 && !(OF_DBG(P) & 16)) {
       tc::prefetch_tmap(&img_map);
       const uint64_t pol = policy_evict_first();
       int k = 0;
@@ -179,7 +181,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     }
   } else if (warp == 1) {
     // ===================== watcher =====================
-    if (lane == 0) {
+    if (lane == 0 && !(OF_DBG(P) & (4 | 8 | 16))) {
       for (int b = 0; b < P.B; ++b) {
         while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(128);
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
@@ -191,7 +193,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     const int bw = warp - L2F_FIRST_BUILD;
     const uint64_t keep = policy_evict_last();
     int k = 0;
-    for (int p = blockIdx.x; p < P.total_build; p += gridDim.x, ++k) {
+    for (int p = blockIdx.x; p < ((OF_DBG(P) & 16) ? 0 : P.total_build); p += gridDim.x, ++k) {
       if (k % L2F_BUILD_WARPS != bw) continue;
       const int stage = k % L2F_STAGES;
       const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
@@ -203,7 +205,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       const float* T = reinterpret_cast<const float*>(tiles + (size_t)stage * L2F_STAGE_BYTES);
 #pragma unroll
       for (int s = 0; s < L2F_MAX_SCALES; ++s) {
-        if (s < P.ns) {
+        if (s < P.ns && !(OF_DBG(P) & 1)) {
           const L2fScale& S = P.sc[s];
           const int lc = 4 - s, bs = 2 << s;                 // log2(columns at scale s), block size
           const int n_s = (L2F_ROWS >> (s + 1)) << lc;
@@ -222,9 +224,11 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       }
       __syncwarp();                       // every lane's shared-memory reads and pyramid stores are issued
       if (lane == 0) {
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");          // the warp's stores, cumulatively, before the count
-        asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(P.done + b) : "memory");
-        tc::mbar_arrive(&empty_bar[stage]);
+        tc::mbar_arrive(&empty_bar[stage]);                       // the ring slot refills while the release drains
+        if (!(OF_DBG(P) & 8)) {
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");        // the warp's stores, cumulatively, before the count
+          asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(P.done + b) : "memory");
+        }
       }
     }
   } else {
@@ -235,14 +239,15 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     int confirmed = 0;                  // images known complete
     float2 nfl[4];
     L2fTile nt;
-    if (gw < P.total_gather) { nt = l2f_decode(P, gw); l2f_load_flows(P, nt, lane, nfl); }
-    for (int u = gw; u < P.total_gather; u += tgw) {
+    const int total_gather = (OF_DBG(P) & 2) ? 0 : P.total_gather;
+    if (gw < total_gather) { nt = l2f_decode(P, gw); l2f_load_flows(P, nt, lane, nfl); }
+    for (int u = gw; u < total_gather; u += tgw) {
       const L2fTile t = nt;
       float2 fl[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) fl[q] = nfl[q];
-      if (u + tgw < P.total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows(P, nt, lane, nfl); }   // in flight
-      if (t.b >= confirmed) {
+      if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows(P, nt, lane, nfl); }   // in flight
+      if (t.b >= confirmed && !(OF_DBG(P) & 4)) {
         unsigned v;
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
         confirmed = (int)v;
@@ -387,6 +392,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
   OF_REQUIRE(tb < (1ll << 30) && tg < (1ll << 30), OF_ERR_SHAPE, "too many loss work units");
   P.total_build = (int)tb;
   P.total_gather = (int)tg;
+  if (const char* e = of_tune_env("OF_LF2_DBG")) P.dbg = atoi(e);
 
   CUtensorMap img_map;
   memset(&img_map, 0, sizeof(img_map));

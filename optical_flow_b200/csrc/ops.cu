@@ -249,6 +249,28 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// Adam with the step count and learning rate in DEVICE memory (of_adam_state), so a CUDA graph of the whole train
+// step can be replayed: nothing about the optimiser is baked into the captured kernel arguments.
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ m, float* __restrict__ v, size_t n,
+                                                       const of_adam_state* __restrict__ st, float beta1, float beta2,
+                                                       float eps, float gscale) {
+  const int step = st->step + 1;                                   // 1-based count of THIS update
+  const float lr_t = (float)((double)st->lr * sqrt(1.0 - pow((double)beta2, (double)step)) /
+                             (1.0 - pow((double)beta1, (double)step)));
+  const float omb1 = 1.0f - beta1, omb2 = 1.0f - beta2;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    float gr = g[e] * gscale;
+    float mm = m[e], vv = v[e];
+    mm = mm + (gr - mm) * omb1;
+    vv = vv + (gr * gr - vv) * omb2;
+    m[e] = mm;
+    v[e] = vv;
+    p[e] = p[e] - lr_t * mm / (sqrtf(vv) + eps);
+  }
+}
+__global__ void adam_advance_kernel(of_adam_state* st) { st->step += 1; }
+
 // ---- opt-in L2 regulariser (model.py:7,13 / resnet/models.py:5,18,23: declared with l2(1e-4) on the encoder convs'
 // kernels and biases, but train.py never adds model.losses - SURVEY F6; off by default) ----------------------------
 // Keras l2(l): penalty = l * sum(w^2)  ->  grad += 2 l w, loss += l * sum(w^2)
@@ -391,6 +413,15 @@ int of_adam_step(float* param, const float* grad, float* m, float* v, size_t n, 
   adam_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, m, v, n, (float)lr_t, 1.0f - beta1,
                                                             1.0f - beta2, eps, grad_scale);
   return of_launch_check("adam_kernel");
+}
+
+int of_adam_step_dev(float* param, const float* grad, float* m, float* v, size_t n, of_adam_state* state, float beta1,
+                     float beta2, float eps, float grad_scale, void* stream) {
+  OF_REQUIRE(param && grad && m && v && state, OF_ERR_ARG, "null pointer argument");
+  adam_dev_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, m, v, n, state, beta1, beta2, eps, grad_scale);
+  if (int r = of_launch_check("adam_kernel")) return r;
+  adam_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);          // after every block has read the old count
+  return of_launch_check("adam_advance_kernel");
 }
 
 }  // extern "C"

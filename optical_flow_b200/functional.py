@@ -307,6 +307,16 @@ def adam_step(param, grad, m, v, step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-7
                                   L.stream_ptr()), "of_adam_step")
 
 
+def adam_step_dev(param, grad, m, v, state, beta1=0.9, beta2=0.999, eps=1e-7, grad_scale=1.0):
+    """The same update with (step, lr) read from the 8-byte device ``state`` (of_adam_state) and the step count
+    advanced on the stream: graph-capturable."""
+    assert param.dtype == grad.dtype == m.dtype == v.dtype == torch.float32
+    assert param.numel() == grad.numel() == m.numel() == v.numel() and state.numel() * state.element_size() == 8
+    L.check(L.load().of_adam_step_dev(L.ptr(param), L.ptr(grad), L.ptr(m), L.ptr(v), param.numel(), L.ptr(state),
+                                      float(beta1), float(beta2), float(eps), float(grad_scale), L.stream_ptr()),
+            "of_adam_step_dev")
+
+
 def l2_regularizer(param, grad, l2, loss=None):
     """Keras ``l2(l)`` on one tensor (opt-in): grad += 2 l w; loss (0-d / 1-element f32 tensor) += l sum(w^2)."""
     assert param.dtype == grad.dtype == torch.float32 and param.numel() == grad.numel()

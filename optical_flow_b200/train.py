@@ -45,8 +45,10 @@ class Trainer:
         self.flow_net = build_flow_net(height, width, pretrained_weights_path, conv_mode=conv_mode,
                                        warp_mode=warp_mode, seed=seed)
         self.loss_layer = LossLayer(warp_mode=warp_mode)
-        self.lr = lr
+        self._lr = float(lr)
         self.step = 0
+        self._graph = None              # (input shape, static input, CUDAGraph, loss, flows) once enable_graph() ran
+        self._opt_state = None          # device of_adam_state {int step; float lr} (graph mode)
         self.comm = comm
         self.world_size = comm.world_size if comm is not None else 1
         self.apply_l2, self.l2_reg = bool(apply_l2), float(l2_reg)
@@ -54,6 +56,22 @@ class Trainer:
     @property
     def trainable_weights(self):
         return self.flow_net.trainable_weights
+
+    @property
+    def lr(self):
+        return self._lr
+
+    @lr.setter
+    def lr(self, value):
+        """train.py:69-71 changes the learning rate mid-run; in graph mode it lives in device memory."""
+        self._lr = float(value)
+        if self._opt_state is not None:
+            self._write_opt_state()
+
+    def _write_opt_state(self):
+        import struct
+        raw = torch.frombuffer(bytearray(struct.pack("<if", int(self.step), self._lr)), dtype=torch.uint8)
+        self._opt_state.copy_(raw.to(self._opt_state.device))
 
     def forward_backward(self, batch_imgs):
         """tape.gradient(loss, trainable_weights) of train.py:50-55: loss + flat gradient."""
@@ -71,13 +89,63 @@ class Trainer:
         st = self.flow_net.store
         scale = parallel.exchange_gradients(st.grad, self.comm)    # sum over replicas; 1/N goes into Adam
         self.step += 1
-        F.adam_step(st.flat, st.grad, st.adam_m, st.adam_v, self.step, lr=self.lr, grad_scale=scale)
+        if self._opt_state is not None:                            # graph mode: the device holds (step, lr)
+            F.adam_step_dev(st.flat, st.grad, st.adam_m, st.adam_v, self._opt_state, grad_scale=scale)
+        else:
+            F.adam_step(st.flat, st.grad, st.adam_m, st.adam_v, self.step, lr=self.lr, grad_scale=scale)
 
     def train_step(self, batch_imgs, step_count=None):
-        """train.py:47-61.  Returns (loss_value [0-d device tensor], flows)."""
+        """train.py:47-61.  Returns (loss_value [0-d device tensor], flows).  After ``enable_graph`` a batch of the
+        captured shape is ONE graph launch (train.py:47's @tf.function): forward, loss, backward, gradient exchange
+        and Adam; the returned tensors are the graph's static outputs (overwritten by the next step)."""
+        g = self._graph
+        if g is not None and tuple(batch_imgs.shape) == g[0]:
+            if batch_imgs.data_ptr() != g[1].data_ptr():
+                g[1].copy_(batch_imgs, non_blocking=True)
+            g[2].replay()
+            self.step += 1
+            return g[3], g[4]
         loss_value, flows = self.forward_backward(batch_imgs)
         self.apply_gradients()
         return loss_value, flows
+
+    def enable_graph(self, sample_batch, warmup=2):
+        """Capture the whole step for batches shaped like ``sample_batch`` (B, H, W, 6) into a CUDA graph.  Everything
+        that changes from step to step is device state: the input buffer, the weights / Adam moments, and the
+        optimiser's (step, lr) pair (of_adam_step_dev), so replaying the graph IS the next step.  ``warmup`` eager
+        forward + backward passes over the sample run first on a side stream (lazy allocations, tensor-map encodes,
+        function attributes); they compute gradients but apply nothing."""
+        dev = self.flow_net.device
+        st = self.flow_net.store
+        self._opt_state = torch.zeros(8, dtype=torch.uint8, device=dev)
+        static_in = sample_batch.detach().clone().contiguous()
+
+        def step_dev():
+            loss_value, flows = self.forward_backward(static_in)
+            scale = parallel.exchange_gradients(st.grad, self.comm)
+            F.adam_step_dev(st.flat, st.grad, st.adam_m, st.adam_v, self._opt_state, grad_scale=scale)
+            return loss_value, flows
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            self._write_opt_state()
+            for _ in range(max(warmup, 1)):
+                self.forward_backward(static_in)
+                parallel.exchange_gradients(st.grad, self.comm)
+            graph = torch.cuda.CUDAGraph()
+            n0 = L.load().of_launch_count()
+            with torch.cuda.graph(graph, stream=side):
+                loss_value, flows = step_dev()
+            self.graph_kernels = int(L.load().of_launch_count() - n0)      # this library's kernels in one replay
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._graph = (tuple(static_in.shape), static_in, graph, loss_value, flows)
+        return static_in
+
+    def graph_input(self):
+        """The captured step's static input buffer (fill it in place to skip the device-to-device copy)."""
+        return self._graph[1] if self._graph is not None else None
 
 
 class HostBatchPrefetcher:

@@ -94,6 +94,38 @@ def test_train_step_adam_parity(cuda, small_case):
         np.testing.assert_allclose(upd_got[big], upd_ref[big], rtol=2e-2, atol=1e-7)
 
 
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_graph_step_equals_eager_step(cuda, small_case, mode):
+    """Trainer.enable_graph: the captured step (forward, loss, backward, Adam with device-side step count / learning
+    rate) replayed 4 times == 4 eager steps, including a learning-rate change between steps (train.py:69-71)."""
+    from optical_flow_b200.train import Trainer
+    imgs = [torch.tensor(T.synthetic_pairs(small_case["B"], small_case["H"], small_case["W"], seed=50 + k), device=cuda)
+            for k in range(2)]
+    out = {}
+    for use_graph in (False, True):
+        tr = Trainer(small_case["H"], small_case["W"], None, conv_mode=mode)
+        tr.flow_net.store.load_numpy(small_case["params"], small_case["stats"])
+        if use_graph:
+            tr.enable_graph(imgs[0])
+        losses = []
+        for i in range(4):
+            if i == 2:
+                tr.lr = 3e-5
+            lv, flows = tr.train_step(imgs[i % 2], i)
+            losses.append(lv.item())
+        assert tr.step == 4
+        out[use_graph] = (losses, tr.flow_net.store.flat.detach().clone())
+    p0 = torch.cat([torch.tensor(small_case["params"][n]).reshape(-1) for n in tr.flow_net.store.specs]).to(cuda)
+    upd_e, upd_g = out[False][1] - p0, out[True][1] - p0
+    if mode == "fp32":        # atomics-free path: same arithmetic, only lr_t is formed on the device instead of the host
+        assert np.allclose(out[True][0], out[False][0], rtol=1e-6)
+        assert float((upd_e - upd_g).abs().max()) <= 1e-4 * float(upd_e.abs().max())
+    else:                     # split-K wgrad atomics reorder fp32 sums run to run
+        assert np.allclose(out[True][0], out[False][0], rtol=2e-3)
+        cos = float((upd_e * upd_g).sum() / (upd_e.norm() * upd_g.norm()))
+        assert cos > 0.98, cos
+
+
 def test_dp_average_equals_concatenated_batch(cuda, small_case):
     """the average of replica gradients over batch shards equals the
     single-replica gradient on the concatenated batch (loss is a batch mean, BN is

@@ -69,10 +69,14 @@ def dflow_bound(flow, e_d, num_scales=4):
     x0, x1, y0, y1 = R.sample_indices(pts, h, w)
     ax = np.abs(x1.astype(np.float32) - pts[..., 0])
     ay = np.abs(y1.astype(np.float32) - pts[..., 1])
-    wmag = np.stack([ay + np.abs(1 - ay), ax + np.abs(1 - ax)], axis=-1)      # d0 uses (ay, by); d1 uses (ax, bx)
+    wx, wy = ax + np.abs(1 - ax), ay + np.abs(1 - ay)
+    wmag = np.stack([wy, wx], axis=-1)                                        # d0 uses (ay, by); d1 uses (ax, bx)
     inv_n = 1.0 / (B * h * w * 3.0 * num_scales)
     eps = 2.0 ** -24
-    return 1e-5 * np.abs(e_d).max() + 4 * eps * wmag * (3 * 1.2) * inv_n      # 3 channels, |pixel difference| <= 1.2
+    bound = 1e-5 * np.abs(e_d).max() + 4 * eps * wmag * (3 * 1.2) * inv_n     # 3 channels, |pixel difference| <= 1.2
+    # the forward value sum_k w_k v_k rounds against sum |w_k| |v_k| <= wx wy max|v|: below that, sign(diff) is a tie
+    tie = 2e-6 + 8 * eps * wx * wy * 0.6
+    return bound, tie
 
 
 # ------------------------------------------------------------------ (i) fused loss vs the oracle --
@@ -97,10 +101,12 @@ def test_loss_layer_oracle_at_bench_shape(cuda, B, H, W, flows_kind):
     e_loss, e_d, e_diff = O.loss_layer(imgs, flows, return_grads=True, return_diffs=True)
     # d loss / d flow carries sign(im1 - warped) (loss.py:28): where a channel's |diff| is within a few fp32 ulps of 0
     # the sign is a rounding tie-break and that pixel's whole gradient may legitimately flip; with millions of pixels
-    # such ties exist (measured 2-6e-5 of the pixels), so they are excluded from the max-abs bound - and counted
-    firm = [np.abs(d).min(axis=-1) >= 2e-6 for d in e_diff]
+    # such ties exist (a few 1e-5 of the in-range pixels; more where clipped taps carry weights in the hundreds and the
+    # forward value itself only holds ~1e-4), so they are excluded from the max-abs bound - and counted
+    bounds = [dflow_bound(flows[s], e_d[s]) for s in range(4)]
+    firm = [np.abs(e_diff[s]).min(axis=-1) >= bounds[s][1] for s in range(4)]
     for s in range(4):
-        assert firm[s].mean() > 0.999, (s, firm[s].mean())
+        assert firm[s].mean() > 0.99, (s, firm[s].mean())
     layer = LossLayer()
     x = torch.tensor(imgs, device=cuda)
     fd = [torch.tensor(f, device=cuda) for f in flows]
@@ -109,7 +115,7 @@ def test_loss_layer_oracle_at_bench_shape(cuda, B, H, W, flows_kind):
         assert abs(loss.item() - float(e_loss)) <= 1e-5 * abs(float(e_loss)), (loss.item(), float(e_loss))
         for s in range(4):
             got = layer.d_flows[s].cpu().numpy()
-            excess = (np.abs(got - e_d[s]) - dflow_bound(flows[s], e_d[s])).max(axis=-1)
+            excess = (np.abs(got - e_d[s]) - bounds[s][0]).max(axis=-1)
             assert excess[firm[s]].max() <= 0, (s, excess[firm[s]].max() / np.abs(e_d[s]).max())
 
 
