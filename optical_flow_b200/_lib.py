@@ -13,7 +13,10 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # OF_PROFILE_LIB=1 selects the -DOF_PROFILE_HOOKS build (scripts/ only; tests, smoke and bench use the shipped library)
-LIB_PATH = os.path.join(_HERE, "liboflow_b200_prof.so" if os.environ.get("OF_PROFILE_LIB") == "1" else "liboflow_b200.so")
+# (OF_PROFILE_LIB=<tag> selects an A/B variant liboflow_b200_<tag>.so built by `build.py --tag=<tag> -D...`)
+_variant = os.environ.get("OF_PROFILE_LIB", "")
+LIB_PATH = os.path.join(_HERE, "liboflow_b200.so" if not _variant else
+                        ("liboflow_b200_prof.so" if _variant == "1" else "liboflow_b200_%s.so" % _variant))
 
 OF_F32, OF_BF16 = 0, 1
 OF_MASK_BITS = 2      # of_tc_conv.mask_dtype: sign-bit mask written by a conv_tc3 fprop (sign_out)

@@ -47,12 +47,17 @@ def _deps_mtime():
     return m
 
 
-def build_library(force: bool = False, verbose: bool = False, profile_hooks: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, profile_hooks: bool = False, tag: str = "",
+                  defines=()) -> str:
     """profile_hooks: build liboflow_b200_prof.so with -DOF_PROFILE_HOOKS (environment-variable tuning knobs and the
-    "skip part of the kernel" debug paths; see csrc/common.cuh).  The shipped library has none of them."""
-    build_dir = BUILD + ("_prof" if profile_hooks else "")
+    "skip part of the kernel" debug paths; see csrc/common.cuh).  The shipped library has none of them.
+    tag / defines: an A/B variant liboflow_b200_<tag>.so compiled with extra -D macros (tuning scripts only; selected
+    at run time with OF_PROFILE_LIB=<tag>)."""
+    build_dir = BUILD + ("_prof" if profile_hooks else "") + ("_" + tag if tag else "")
     lib_path = LIB_PROF if profile_hooks else LIB
-    extra = ["-DOF_PROFILE_HOOKS"] if profile_hooks else []
+    if tag:
+        lib_path = os.path.join(HERE, "liboflow_b200_%s.so" % tag)
+    extra = (["-DOF_PROFILE_HOOKS"] if profile_hooks else []) + ["-D" + d for d in defines]
     os.makedirs(build_dir, exist_ok=True)
     nvcc = _nvcc()
     hdr_m = _deps_mtime()
@@ -90,4 +95,7 @@ def build_library(force: bool = False, verbose: bool = False, profile_hooks: boo
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose=True, profile_hooks="--profile-hooks" in sys.argv))
+    _tag = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--tag=")), "")
+    _defs = [a[2:] for a in sys.argv if a.startswith("-D")]
+    print(build_library(force="--force" in sys.argv, verbose=True, profile_hooks="--profile-hooks" in sys.argv,
+                        tag=_tag, defines=_defs))

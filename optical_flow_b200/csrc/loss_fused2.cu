@@ -4,39 +4,44 @@
 // Same dataflow through L2 as loss_fused.cu (the image pair is streamed from HBM exactly once, the float4 pyramid of
 // both frames lives in the 126 MB L2 between its producer and its consumers), but the two halves of the work no
 // longer take turns inside a CTA.  One persistent CTA per SM runs, side by side,
-//   warp 0          TMA producer: 32 x 32 pixel patches of the 6-channel pair into an 8-stage shared-memory ring
-//                   (24 KB per stage, mbarrier full / empty per stage, evict_first);
+//   warp 0          TMA producer: 16 x 32 pixel patches of the 6-channel pair into a 16-stage shared-memory ring
+//                   (12 KB per stage, mbarrier full / built / empty per stage, evict_first);
 //   warp 1          watcher: the only poller of the global per-image "pyramid complete" counters; it republishes
 //                   them to a shared-memory word the gather warps spin on (no L2 hot spot);
-//   warps 2..5      BUILD: each warp owns every fourth patch of its CTA: all four pyramid levels of both frames
+//   warp 2          publisher: follows the patches of its CTA in order (built barriers), hands ring slots back to the
+//                   producer, and at every image boundary issues ONE gpu-scope release fence + counter add for all the
+//                   patches of that image this CTA built - the ~1-2 us fence stalls nobody who computes;
+//   warps 3..10     BUILD: each warp owns every eighth patch of its CTA: all four pyramid levels of both frames
 //                   (tf.image.resize at 2^k = the central 2x2 mean) from shared memory -> float4 texels, evict_last;
-//                   then ONE gpu-scope release + counter increment per patch;
-//   warps 6..       GATHER: each warp owns its own 128-pixel output tiles (static round-robin over the whole grid, so
+//   warps 11..      GATHER: each warp owns its own 128-pixel output tiles (static round-robin over the whole grid, so
 //                   the loss sum stays deterministic): flow prefetched one tile ahead, 4 bilinear taps of frame 2
 //                   and the frame-1 texel as LDG.128 from the L2-resident pyramid, |diff| -> loss partial, sign ->
 //                   d_flow.  A gather tile of image b only waits until all patches of image b are built.
 // So the HBM stream (BUILD) and the L2-latency-bound taps (GATHER) overlap on every SM for the whole kernel; only the
 // first image's build and the last image's gather are exposed.  No CTA-wide barrier after start-up.
+// Measured dissection on B200 at C2 (profile-hooks build, OF_LF2_DBG): launch + final reduction 4.1 us, the TMA stream
+// alone 14.6 us more (6.5 TB/s); everything else has to hide under that stream.
 // HBM traffic = image pair once + flows + d_flows (the algorithmic bytes of SURVEY 8d).
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "loss_fused_common.cuh"
 
 #define L2F_MAX_SCALES 4
-#define L2F_ROWS 32
+#define L2F_ROWS 16
 #define L2F_COLS 32
 #define L2F_ROW_FLOATS (L2F_COLS * 6)
-#define L2F_STAGE_BYTES (L2F_ROWS * L2F_COLS * 24)      // 24576: one TMA box {96 floats, 2 segments, 32 rows}
-#define L2F_STAGES 8
-#define L2F_BUILD_WARPS 4
+#define L2F_STAGE_BYTES (L2F_ROWS * L2F_COLS * 24)      // 12288: one TMA box {96 floats, 2 segments, 16 rows}
+#define L2F_STAGES 16
+#define L2F_BUILD_WARPS 8
 #ifndef L2F_GATHER_WARPS
-#define L2F_GATHER_WARPS 18
+#define L2F_GATHER_WARPS 17
 #endif
-#define L2F_FIRST_BUILD 2
+#define L2F_FIRST_BUILD 3
 #define L2F_FIRST_GATHER (L2F_FIRST_BUILD + L2F_BUILD_WARPS)
 #define L2F_WARPS (L2F_FIRST_GATHER + L2F_GATHER_WARPS)
 #define L2F_THREADS (L2F_WARPS * 32)
 #define L2F_HDR_BYTES 32768      // same header layout as loss_fused.cu: ticket, per-image counters, per-CTA partials
+#define L2F_PUB_BATCH 8          // images one publisher fence can cover
 
 struct L2fScale {
   const float* flow;
@@ -56,11 +61,10 @@ struct L2fParams {
   unsigned* ticket;      // [0]
   unsigned* done;        // [B] patches built per image
   double* partials;      // [grid]
-  int B, H, W, mode;
+  int B, H, W;
   int chunks;            // patches per row of patches
   int nb;                // patches per image
   int ngu;               // gather tiles per image
-  int tile_i, tile_j;    // gather tile shape (REF_IJ 8 x 16, XY 4 x 32)
   int total_build, total_gather;
   int dbg;               // -DOF_PROFILE_HOOKS only: 1 no build math / stores, 2 no gather, 4 gather does not wait for
                          // the builds, 8 no release fence + counter, 16 no image stream at all (with 4: gather only)
@@ -118,34 +122,127 @@ __device__ __forceinline__ L2fTile l2f_decode(const L2fParams& P, int u) {
   return t;
 }
 
-// pixel q (0..3) of this lane within a tile
-__device__ __forceinline__ void l2f_pixel(const L2fParams& P, const L2fTile& t, int lane, int q, int* i, int* j) {
-  if (P.mode == OF_WARP_REF_IJ) {       // 8 x 16 tile; an instruction covers 8 rows x 4 columns: the transposed gather
-    *i = t.ti * 8 + (lane & 7);         // (source column = i) then reads 8 consecutive texels of 4 source rows
-    *j = t.tj * 16 + (lane >> 3) + 4 * q;
-  } else {                              // 4 x 32 tile, one output row per instruction
-    *i = t.ti * 4 + q;
+// Gather tile geometry.  REF_IJ: 8 x 16 pixels, an instruction covers 8 rows x 4 columns - the transposed gather
+// (source column = i) then reads 8 consecutive texels of 4 source rows.  XY: 4 x 32, one output row per instruction.
+// Pixel q of a lane sits at a constant offset (di(q), dj(q)) from the lane's first pixel.
+template <int MODE> struct L2fGeom;
+template <> struct L2fGeom<OF_WARP_REF_IJ> {
+  static constexpr int TI = 8, TJ = 16;
+  __device__ static __forceinline__ void first(const L2fTile& t, int lane, int* i, int* j) {
+    *i = t.ti * 8 + (lane & 7);
+    *j = t.tj * 16 + (lane >> 3);
+  }
+  __device__ static __forceinline__ int di(int) { return 0; }
+  __device__ static __forceinline__ int dj(int q) { return 4 * q; }
+};
+template <> struct L2fGeom<OF_WARP_XY> {
+  static constexpr int TI = 4, TJ = 32;
+  __device__ static __forceinline__ void first(const L2fTile& t, int lane, int* i, int* j) {
+    *i = t.ti * 4;
     *j = t.tj * 32 + lane;
   }
+  __device__ static __forceinline__ int di(int q) { return q; }
+  __device__ static __forceinline__ int dj(int) { return 0; }
+};
+
+// Ragged tiles (h or w not a multiple of the tile) are handled without a second code path: a pixel outside the image
+// is CLAMPED onto the last row / column (all of its loads are then valid) and its contribution is masked at the end.
+template <int MODE>
+__device__ __forceinline__ void l2f_load_flows(const L2fParams& P, const L2fTile& t, int lane, float2& fl0, float2& fl1,
+                                               float2& fl2, float2& fl3) {
+  using G = L2fGeom<MODE>;
+  const L2fScale& S = P.sc[t.s];
+  int i0, j0;
+  G::first(t, lane, &i0, &j0);
+  const float2* g = reinterpret_cast<const float2*>(S.flow) + (size_t)t.b * S.h * S.w;
+  const int hm = S.h - 1, wm = S.w - 1;
+  fl0 = __ldg(g + min(i0 + G::di(0), hm) * S.w + min(j0 + G::dj(0), wm));
+  fl1 = __ldg(g + min(i0 + G::di(1), hm) * S.w + min(j0 + G::dj(1), wm));
+  fl2 = __ldg(g + min(i0 + G::di(2), hm) * S.w + min(j0 + G::dj(2), wm));
+  fl3 = __ldg(g + min(i0 + G::di(3), hm) * S.w + min(j0 + G::dj(3), wm));
 }
 
-__device__ __forceinline__ void l2f_load_flows(const L2fParams& P, const L2fTile& t, int lane, float2 (&fl)[4]) {
-  const L2fScale& S = P.sc[t.s];
-  const float2* gflow = reinterpret_cast<const float2*>(S.flow) + (size_t)t.b * S.h * S.w;
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    int i, j;
-    l2f_pixel(P, t, lane, q, &i, &j);
-    fl[q] = (i < S.h && j < S.w) ? __ldg(gflow + i * S.w + j) : make_float2(0.f, 0.f);
+// one pixel of a gather tile in two steps, so a thread keeps the taps of two pixels in flight: l2f_issue computes the
+// sampling position and sends out the 5 loads, l2f_finish does the arithmetic.
+struct L2fPix {
+  float ax, ay, bx, by;
+  float4 v00, v01, v10, v11, ref;
+  int off;            // pixel offset within the image; bit 31 set = outside the image (masked)
+};
+
+template <int MODE>
+__device__ __forceinline__ void l2f_issue(L2fPix& r, const float4* __restrict__ q1, const float4* __restrict__ q2,
+                                          int h, int w, uint64_t keep, int i_raw, int j_raw, float2 f) {
+  const int i = min(i_raw, h - 1), j = min(j_raw, w - 1);
+  r.off = (i * w + j) | ((i_raw < h && j_raw < w) ? 0 : (int)0x80000000);
+  // model.py:65-71 + transformations.py:93-125 (same op order as loss.cu / warp.cu)
+  float x, y;
+  if (MODE == OF_WARP_REF_IJ) { x = __fadd_rn((float)i, f.x); y = __fadd_rn((float)j, f.y); }
+  else { x = __fadd_rn((float)j, f.x); y = __fadd_rn((float)i, f.y); }
+  const int xf = __float2int_rd(x), yf = __float2int_rd(y);
+  // clip(floor + 1) with the +1 saturating (floor may be INT_MAX for a saturated cast)
+  const int x0 = lf_clamp(xf, 0, w - 1), x1 = lf_clamp(min(xf, 0x7ffffffe) + 1, 0, w - 1);
+  const int y0 = lf_clamp(yf, 0, h - 1), y1 = lf_clamp(min(yf, 0x7ffffffe) + 1, 0, h - 1);
+  r.ax = __fsub_rn((float)x1, x);
+  r.ay = __fsub_rn((float)y1, y);
+  r.bx = __fsub_rn(1.f, r.ax);
+  r.by = __fsub_rn(1.f, r.ay);
+  const float4* r0 = q2 + y0 * w;
+  const float4* r1 = q2 + y1 * w;
+  r.v00 = ld_f4_policy(r0 + x0, keep);
+  r.v01 = ld_f4_policy(r1 + x0, keep);
+  r.v10 = ld_f4_policy(r0 + x1, keep);
+  r.v11 = ld_f4_policy(r1 + x1, keep);
+  r.ref = ld_f4_policy(q1 + (r.off & 0x7fffffff), keep);
+}
+
+__device__ __forceinline__ void l2f_finish(const L2fPix& r, float2* __restrict__ gdflow, float inv_n, float& acc) {
+  const bool inside = r.off >= 0;
+  const float w00 = r.ax * r.ay, w01 = r.ax * r.by, w10 = r.bx * r.ay, w11 = r.bx * r.by;
+  const float wx = w00 * r.v00.x + w01 * r.v01.x + w10 * r.v10.x + w11 * r.v11.x;
+  const float wy = w00 * r.v00.y + w01 * r.v01.y + w10 * r.v10.y + w11 * r.v11.y;
+  const float wz = w00 * r.v00.z + w01 * r.v01.z + w10 * r.v10.z + w11 * r.v11.z;
+  const float ex = r.ref.x - wx, ey = r.ref.y - wy, ez = r.ref.z - wz;               // loss.py:28
+  const float term = (fabsf(ex) + fabsf(ey) + fabsf(ez)) * inv_n;
+  acc += inside ? term : 0.f;
+  if (gdflow != nullptr && inside) {
+    const float gxx = r.ay * (r.v10.x - r.v00.x) + r.by * (r.v11.x - r.v01.x);
+    const float gxy = r.ay * (r.v10.y - r.v00.y) + r.by * (r.v11.y - r.v01.y);
+    const float gxz = r.ay * (r.v10.z - r.v00.z) + r.by * (r.v11.z - r.v01.z);
+    const float gyx = r.ax * (r.v01.x - r.v00.x) + r.bx * (r.v11.x - r.v10.x);
+    const float gyy = r.ax * (r.v01.y - r.v00.y) + r.bx * (r.v11.y - r.v10.y);
+    const float gyz = r.ax * (r.v01.z - r.v00.z) + r.bx * (r.v11.z - r.v10.z);
+    const float sx_ = -lf_sgn(ex) * inv_n, sy_ = -lf_sgn(ey) * inv_n, sz_ = -lf_sgn(ez) * inv_n;
+    const float d0 = sx_ * gxx + sy_ * gxy + sz_ * gxz;
+    const float d1 = sx_ * gyx + sy_ * gyy + sz_ * gyz;
+    gdflow[r.off] = make_float2(d0, d1);
   }
 }
 
+template <int MODE>
+__device__ __forceinline__ void l2f_gather_tile(const float4* __restrict__ q1, const float4* __restrict__ q2,
+                                                float2* __restrict__ gdflow, int h, int w, float inv_n, uint64_t keep,
+                                                int i0, int j0, float2 f0, float2 f1, float2 f2, float2 f3, float& acc) {
+  using G = L2fGeom<MODE>;
+  L2fPix a, b;
+  l2f_issue<MODE>(a, q1, q2, h, w, keep, i0 + G::di(0), j0 + G::dj(0), f0);
+  l2f_issue<MODE>(b, q1, q2, h, w, keep, i0 + G::di(1), j0 + G::dj(1), f1);
+  l2f_finish(a, gdflow, inv_n, acc);
+  l2f_finish(b, gdflow, inv_n, acc);
+  l2f_issue<MODE>(a, q1, q2, h, w, keep, i0 + G::di(2), j0 + G::dj(2), f2);
+  l2f_issue<MODE>(b, q1, q2, h, w, keep, i0 + G::di(3), j0 + G::dj(3), f3);
+  l2f_finish(a, gdflow, inv_n, acc);
+  l2f_finish(b, gdflow, inv_n, acc);
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(L2F_THREADS, 1)
 loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUtensorMap img_map) {
   extern __shared__ __align__(128) uint8_t l2f_smem[];
   uint8_t* tiles = l2f_smem;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(l2f_smem + L2F_STAGES * L2F_STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + L2F_STAGES;
+  uint64_t* empty_bar = full_bar + L2F_STAGES;      // publisher -> producer
+  uint64_t* built_bar = empty_bar + L2F_STAGES;     // builder warp -> publisher
   __shared__ double s_part[L2F_GATHER_WARPS];
   __shared__ unsigned s_built;          // images whose pyramid is complete and visible (watcher -> gather warps)
   __shared__ bool s_last;
@@ -155,20 +252,23 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     for (int s = 0; s < L2F_STAGES; ++s) {
       tc::mbar_init(&full_bar[s], 1);
       tc::mbar_init(&empty_bar[s], 1);
+      tc::mbar_init(&built_bar[s], 1);
     }
     s_built = 0u;
     tc::fence_barrier_init();
   }
   __syncthreads();
+  const bool stream_on = !(OF_DBG(P) & 16);
+  const int n_build = stream_on ? P.total_build : 0;
 
   float acc = 0.f;
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0 && !(OF_DBG(P) & 16)) {
+    if (lane == 0) {
       tc::prefetch_tmap(&img_map);
       const uint64_t pol = policy_evict_first();
       int k = 0;
-      for (int p = blockIdx.x; p < P.total_build; p += gridDim.x, ++k) {
+      for (int p = blockIdx.x; p < n_build; p += gridDim.x, ++k) {
         const int stage = k % L2F_STAGES;
         const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
         tc::mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -183,18 +283,50 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     // ===================== watcher =====================
     if (lane == 0 && !(OF_DBG(P) & (4 | 8 | 16))) {
       for (int b = 0; b < P.B; ++b) {
-        while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(128);
+        while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(100);
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
         st_release_cta_shared(&s_built, (unsigned)(b + 1));
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== publisher =====================
+    if (lane == 0) {
+      int k = 0;
+      int p = blockIdx.x;
+      int cur_cnt = 0;                             // patches of the current image counted so far
+      int pub_img[L2F_PUB_BATCH], pub_cnt[L2F_PUB_BATCH];
+      while (p < n_build) {
+        int npub = 0;
+        bool first = true;
+        // take every patch that is already built (blocking only for the first), in order
+        while (p < n_build && npub < L2F_PUB_BATCH) {
+          const int stage = k % L2F_STAGES;
+          const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
+          if (first) tc::mbar_wait(&built_bar[stage], phase);
+          else if (!mbar_test(&built_bar[stage], phase)) break;
+          first = false;
+          tc::mbar_arrive(&empty_bar[stage]);                      // the slot refills while the release drains
+          const int b = p / P.nb;
+          ++cur_cnt;
+          p += gridDim.x; ++k;
+          if (p >= n_build || p / P.nb != b) {                     // that was this CTA's last patch of image b
+            pub_img[npub] = b; pub_cnt[npub] = cur_cnt; ++npub; cur_cnt = 0;
+          }
+        }
+        if (npub > 0 && !(OF_DBG(P) & 8)) {
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");         // the builders' stores (observed through the built
+          for (int i = 0; i < npub; ++i)                           // barriers), cumulatively, before the counts
+            asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(P.done + pub_img[i]), "r"((unsigned)pub_cnt[i])
+                         : "memory");
+        }
       }
     }
   } else if (warp < L2F_FIRST_GATHER) {
     // ===================== BUILD =====================
     const int bw = warp - L2F_FIRST_BUILD;
     const uint64_t keep = policy_evict_last();
-    int k = 0;
-    for (int p = blockIdx.x; p < ((OF_DBG(P) & 16) ? 0 : P.total_build); p += gridDim.x, ++k) {
-      if (k % L2F_BUILD_WARPS != bw) continue;
+    int k = bw;
+    for (int p = blockIdx.x + bw * gridDim.x; p < n_build; p += L2F_BUILD_WARPS * gridDim.x, k += L2F_BUILD_WARPS) {
       const int stage = k % L2F_STAGES;
       const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
       const int b = p / P.nb, local = p - b * P.nb;
@@ -203,19 +335,49 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);
       __syncwarp();
       const float* T = reinterpret_cast<const float*>(tiles + (size_t)stage * L2F_STAGE_BYTES);
-#pragma unroll
-      for (int s = 0; s < L2F_MAX_SCALES; ++s) {
-        if (s < P.ns && !(OF_DBG(P) & 1)) {
-          const L2fScale& S = P.sc[s];
-          const int lc = 4 - s, bs = 2 << s;                 // log2(columns at scale s), block size
-          const int n_s = (L2F_ROWS >> (s + 1)) << lc;
-          const unsigned base = ((unsigned)b * S.h + band * (L2F_ROWS / bs)) * S.w + cx * (L2F_COLS / bs);
-          for (int t = lane; t < n_s; t += 32) {
+      if (!(OF_DBG(P) & 1)) {
+        // scale 0: 8 x 16 resized pixels, 4 per lane, two at a time (independent chains)
+        if (P.ns > 0) {
+          const L2fScale& S = P.sc[0];
+          const unsigned base = ((unsigned)b * S.h + band * (L2F_ROWS / 2)) * S.w + cx * (L2F_COLS / 2);
+          const int ocol = lane & 15, or0 = lane >> 4;
+#pragma unroll 2
+          for (int it = 0; it < 4; ++it) {
+            const int orow = or0 + 2 * it;
+            if (ocol * 2 < wc && orow * 2 < hr) {
+              float4 o1, o2;
+              l2f_build_pixel(true, T, 2 * orow, 2 * ocol, &o1, &o2);
+              const unsigned pix = base + orow * S.w + ocol;
+              st_f4_policy(S.p1 + pix, o1, keep);
+              st_f4_policy(S.p2 + pix, o2, keep);
+            }
+          }
+        }
+        // scale 1: 4 x 8 pixels, one per lane
+        if (P.ns > 1) {
+          const L2fScale& S = P.sc[1];
+          const int orow = lane >> 3, ocol = lane & 7;
+          if (ocol * 4 < wc && orow * 4 < hr) {
+            float4 o1, o2;
+            l2f_build_pixel(false, T, 4 * orow + 1, 4 * ocol + 1, &o1, &o2);
+            const unsigned pix = ((unsigned)b * S.h + band * (L2F_ROWS / 4) + orow) * S.w + cx * (L2F_COLS / 4) + ocol;
+            st_f4_policy(S.p1 + pix, o1, keep);
+            st_f4_policy(S.p2 + pix, o2, keep);
+          }
+        }
+        // scales 2 and 3 in one pass: lanes 0-7 -> the 2 x 4 pixels of scale 2, lanes 8-9 -> the 1 x 2 of scale 3
+        if (P.ns > 2 && lane < 10) {
+          const int s = lane < 8 ? 2 : 3;
+          if (s < P.ns) {
+            const L2fScale& S = P.sc[s];
+            const int bs = 2 << s;
+            const int t = lane < 8 ? lane : lane - 8;
+            const int lc = 4 - s;                                    // log2(columns of this scale per patch)
             const int orow = t >> lc, ocol = t & ((1 << lc) - 1);
             if (ocol * bs < wc && orow * bs < hr) {
               float4 o1, o2;
-              l2f_build_pixel(s == 0, T, bs * orow + (bs >> 1) - 1, bs * ocol + (bs >> 1) - 1, &o1, &o2);
-              const unsigned pix = base + orow * S.w + ocol;
+              l2f_build_pixel(false, T, bs * orow + (bs >> 1) - 1, bs * ocol + (bs >> 1) - 1, &o1, &o2);
+              const unsigned pix = ((unsigned)b * S.h + band * (L2F_ROWS / bs) + orow) * S.w + cx * (L2F_COLS / bs) + ocol;
               st_f4_policy(S.p1 + pix, o1, keep);
               st_f4_policy(S.p2 + pix, o2, keep);
             }
@@ -223,30 +385,23 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         }
       }
       __syncwarp();                       // every lane's shared-memory reads and pyramid stores are issued
-      if (lane == 0) {
-        tc::mbar_arrive(&empty_bar[stage]);                       // the ring slot refills while the release drains
-        if (!(OF_DBG(P) & 8)) {
-          asm volatile("fence.acq_rel.gpu;" ::: "memory");        // the warp's stores, cumulatively, before the count
-          asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(P.done + b) : "memory");
-        }
-      }
+      if (lane == 0) tc::mbar_arrive(&built_bar[stage]);
     }
   } else {
     // ===================== GATHER =====================
+    using G = L2fGeom<MODE>;
     const uint64_t keep = policy_evict_last();
     const int gw = (warp - L2F_FIRST_GATHER) * gridDim.x + blockIdx.x;
     const int tgw = L2F_GATHER_WARPS * gridDim.x;
-    int confirmed = 0;                  // images known complete
-    float2 nfl[4];
-    L2fTile nt;
     const int total_gather = (OF_DBG(P) & 2) ? 0 : P.total_gather;
-    if (gw < total_gather) { nt = l2f_decode(P, gw); l2f_load_flows(P, nt, lane, nfl); }
+    int confirmed = 0;                  // images known complete
+    float2 n0 = make_float2(0.f, 0.f), n1 = n0, n2 = n0, n3 = n0;
+    L2fTile nt;
+    if (gw < total_gather) { nt = l2f_decode(P, gw); l2f_load_flows<MODE>(P, nt, lane, n0, n1, n2, n3); }
     for (int u = gw; u < total_gather; u += tgw) {
       const L2fTile t = nt;
-      float2 fl[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) fl[q] = nfl[q];
-      if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows(P, nt, lane, nfl); }   // in flight
+      const float2 f0 = n0, f1 = n1, f2 = n2, f3 = n3;
+      if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows<MODE>(P, nt, lane, n0, n1, n2, n3); }   // in flight
       if (t.b >= confirmed && !(OF_DBG(P) & 4)) {
         unsigned v;
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
@@ -258,58 +413,9 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       const float4* q2 = S.p2 + img_px;
       const float4* q1 = S.p1 + img_px;
       float2* gdflow = S.d_flow ? reinterpret_cast<float2*>(S.d_flow) + img_px : nullptr;
-      const float inv_n = S.inv_n;
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        int ii[2], jj[2]; bool ok[2];
-        float ax[2], ay[2], bx[2], by[2];
-        float4 v00[2], v01[2], v10[2], v11[2], ref[2];
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-          l2f_pixel(P, t, lane, 2 * half + p, &ii[p], &jj[p]);
-          ok[p] = ii[p] < h && jj[p] < w;
-          if (!ok[p]) continue;
-          // model.py:65-71 + transformations.py:93-125 (same op order as loss.cu / warp.cu)
-          const float2 f = fl[2 * half + p];
-          float x, y;
-          if (P.mode == OF_WARP_REF_IJ) { x = __fadd_rn((float)ii[p], f.x); y = __fadd_rn((float)jj[p], f.y); }
-          else { x = __fadd_rn((float)jj[p], f.x); y = __fadd_rn((float)ii[p], f.y); }
-          const int xf = __float2int_rd(x), yf = __float2int_rd(y);
-          const int x0 = lf_clamp(xf, 0, w - 1), x1 = lf_clamp(xf == 0x7fffffff ? xf : xf + 1, 0, w - 1);
-          const int y0 = lf_clamp(yf, 0, h - 1), y1 = lf_clamp(yf == 0x7fffffff ? yf : yf + 1, 0, h - 1);
-          ax[p] = __fsub_rn((float)x1, x);
-          ay[p] = __fsub_rn((float)y1, y);
-          bx[p] = __fsub_rn(1.f, ax[p]);
-          by[p] = __fsub_rn(1.f, ay[p]);
-          v00[p] = ld_f4_policy(q2 + y0 * w + x0, keep);
-          v01[p] = ld_f4_policy(q2 + y1 * w + x0, keep);
-          v10[p] = ld_f4_policy(q2 + y0 * w + x1, keep);
-          v11[p] = ld_f4_policy(q2 + y1 * w + x1, keep);
-          ref[p] = ld_f4_policy(q1 + ii[p] * w + jj[p], keep);
-        }
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-          if (!ok[p]) continue;
-          const float w00 = ax[p] * ay[p], w01 = ax[p] * by[p], w10 = bx[p] * ay[p], w11 = bx[p] * by[p];
-          const float wx = w00 * v00[p].x + w01 * v01[p].x + w10 * v10[p].x + w11 * v11[p].x;
-          const float wy = w00 * v00[p].y + w01 * v01[p].y + w10 * v10[p].y + w11 * v11[p].y;
-          const float wz = w00 * v00[p].z + w01 * v01[p].z + w10 * v10[p].z + w11 * v11[p].z;
-          const float ex = ref[p].x - wx, ey = ref[p].y - wy, ez = ref[p].z - wz;               // loss.py:28
-          acc += (fabsf(ex) + fabsf(ey) + fabsf(ez)) * inv_n;
-          if (gdflow != nullptr) {
-            const float gxx = ay[p] * (v10[p].x - v00[p].x) + by[p] * (v11[p].x - v01[p].x);
-            const float gxy = ay[p] * (v10[p].y - v00[p].y) + by[p] * (v11[p].y - v01[p].y);
-            const float gxz = ay[p] * (v10[p].z - v00[p].z) + by[p] * (v11[p].z - v01[p].z);
-            const float gyx = ax[p] * (v01[p].x - v00[p].x) + bx[p] * (v11[p].x - v10[p].x);
-            const float gyy = ax[p] * (v01[p].y - v00[p].y) + bx[p] * (v11[p].y - v10[p].y);
-            const float gyz = ax[p] * (v01[p].z - v00[p].z) + bx[p] * (v11[p].z - v10[p].z);
-            const float sx_ = -lf_sgn(ex) * inv_n, sy_ = -lf_sgn(ey) * inv_n, sz_ = -lf_sgn(ez) * inv_n;
-            const float d0 = sx_ * gxx + sy_ * gxy + sz_ * gxz;
-            const float d1 = sx_ * gyx + sy_ * gyy + sz_ * gyz;
-            gdflow[ii[p] * w + jj[p]] = make_float2(d0, d1);
-          }
-        }
-      }
+      int i0, j0;
+      G::first(t, lane, &i0, &j0);
+      l2f_gather_tile<MODE>(q1, q2, gdflow, h, w, S.inv_n, keep, i0, j0, f0, f1, f2, f3, acc);
     }
   }
 
@@ -365,8 +471,8 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
   P.done = reinterpret_cast<unsigned*>(wsb + 64);                         // B <= 2048 -> 8 KB
   P.partials = reinterpret_cast<double*>(wsb + 64 + 2048 * 4);
   float4* pyr = reinterpret_cast<float4*>(wsb + L2F_HDR_BYTES);
-  P.tile_i = mode == OF_WARP_REF_IJ ? 8 : 4;
-  P.tile_j = mode == OF_WARP_REF_IJ ? 16 : 32;
+  const int tile_i = mode == OF_WARP_REF_IJ ? L2fGeom<OF_WARP_REF_IJ>::TI : L2fGeom<OF_WARP_XY>::TI;
+  const int tile_j = mode == OF_WARP_REF_IJ ? L2fGeom<OF_WARP_REF_IJ>::TJ : L2fGeom<OF_WARP_XY>::TJ;
   int ngu = 0;
   for (int s = 0; s < num_scales; ++s) {
     L2fScale& S = P.sc[s];
@@ -375,15 +481,15 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
     S.h = hs[s]; S.w = ws[s];
     const size_t px = (size_t)B * S.h * S.w;
     S.p1 = pyr; S.p2 = pyr + px; pyr += 2 * px;
-    S.t_i = (S.h + P.tile_i - 1) / P.tile_i;
-    S.t_j = (S.w + P.tile_j - 1) / P.tile_j;
+    S.t_i = (S.h + tile_i - 1) / tile_i;
+    S.t_j = (S.w + tile_j - 1) / tile_j;
     S.u_begin = ngu;
     ngu += S.t_i * S.t_j;
     S.inv_n = (float)(1.0 / ((double)B * S.h * S.w * 3.0 * num_scales));
   }
   P.ns = num_scales;
   P.loss = loss;
-  P.B = B; P.H = H; P.W = W; P.mode = mode;
+  P.B = B; P.H = H; P.W = W;
   const int bands = (H + L2F_ROWS - 1) / L2F_ROWS;
   P.chunks = (W + L2F_COLS - 1) / L2F_COLS;
   P.nb = bands * P.chunks;
@@ -399,7 +505,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
   {
     void* fn;
     if (int r = of_tc_get_encode(&fn)) return r;
-    // (B, H, W/16, 96 floats): 16-pixel segments of a row; box {96, 2, 32, 1} = a 32 x 32 pixel patch
+    // (B, H, W/16, 96 floats): 16-pixel segments of a row; box {96, 2, 16, 1} = a 16 x 32 pixel patch
     cuuint64_t dims[4] = {96, (cuuint64_t)(W / 16), (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t strides[3] = {384, (cuuint64_t)W * 24, (cuuint64_t)H * W * 24};
     cuuint32_t box[4] = {96, (cuuint32_t)(L2F_COLS / 16), (cuuint32_t)L2F_ROWS, 1};
@@ -410,12 +516,13 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
     OF_REQUIRE(r == CUDA_SUCCESS, OF_ERR_STATE, "cuTensorMapEncodeTiled(images) failed: %d", (int)r);
   }
 
-  const size_t smem = (size_t)L2F_STAGES * L2F_STAGE_BYTES + 2 * L2F_STAGES * sizeof(uint64_t);
+  const size_t smem = (size_t)L2F_STAGES * L2F_STAGE_BYTES + 3 * L2F_STAGES * sizeof(uint64_t);
   static int max_ctas = 0;
   if (max_ctas == 0) {
-    OF_CUDA(cudaFuncSetAttribute(loss_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    OF_CUDA(cudaFuncSetAttribute(loss_ws_kernel<OF_WARP_REF_IJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    OF_CUDA(cudaFuncSetAttribute(loss_ws_kernel<OF_WARP_XY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, dev = 0, sms = 0;
-    OF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_ws_kernel, L2F_THREADS, smem));
+    OF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_ws_kernel<OF_WARP_REF_IJ>, L2F_THREADS, smem));
     OF_CUDA(cudaGetDevice(&dev));
     OF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     OF_REQUIRE(per_sm >= 1, OF_ERR_STATE, "fused loss kernel does not fit on an SM");
@@ -425,7 +532,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
   if (grid > (L2F_HDR_BYTES - 64 - 2048 * 4) / 8) grid = (L2F_HDR_BYTES - 64 - 2048 * 4) / 8;
   // co-residency is required (gather warps wait on patches built by other CTAs): cooperative launch enforces it
   void* args[2] = {(void*)&P, (void*)&img_map};
-  OF_CUDA(cudaLaunchCooperativeKernel((const void*)loss_ws_kernel, dim3(grid), dim3(L2F_THREADS), args, smem,
-                                      (cudaStream_t)stream));
+  const void* fn = mode == OF_WARP_REF_IJ ? (const void*)loss_ws_kernel<OF_WARP_REF_IJ> : (const void*)loss_ws_kernel<OF_WARP_XY>;
+  OF_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(L2F_THREADS), args, smem, (cudaStream_t)stream));
   return of_launch_check("loss_ws_kernel");
 }

@@ -484,8 +484,10 @@ class FlowNet:
                 "of_split_image_pair")
         return out
 
-    def backward(self, d_flows):
-        """d_flows: [d_flow3, d_flow2, d_flow1, d_flow0] (finest first, like the outputs)."""
+    def backward(self, d_flows, after_decoder=None):
+        """d_flows: [d_flow3, d_flow2, d_flow1, d_flow0] (finest first, like the outputs).  ``after_decoder``: called
+        once the four flow modules' gradients are final and before the encoder's backward starts (the data-parallel
+        trainer launches the decoder bucket's all-reduce there, under the encoder backward)."""
         B = self.B
         # with a packed-weight back-end every BN fold is un-folded by ONE launch after the last wgrad
         table = self._bn_job_table() if getattr(self.backend, "pack_cache", None) is not None else None
@@ -506,6 +508,8 @@ class FlowNet:
             if d_f2.data_ptr() != de[B:].data_ptr():
                 _copy_channels(d_f2, 0, de[B:], 0, d_f2.shape[-1])
             d_enc[3 - lvl] = de
+        if after_decoder is not None:
+            after_decoder()
         try:
             self.encoder.backward(d_enc)
         finally:

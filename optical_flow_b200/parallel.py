@@ -109,3 +109,16 @@ def exchange_gradients(flat_grad, comm):
         return 1.0
     comm.allreduce_sum_(flat_grad)
     return 1.0 / comm.world_size
+
+
+def exchange_gradients_in_buckets(flat_grad, comm, boundaries):
+    """The same exchange as ``exchange_gradients`` issued bucket by bucket, LAST bucket first (the order in which the
+    backward pass finishes them: decoder, then encoder - Trainer launches the first of these on a side stream under
+    the encoder backward).  ``boundaries``: increasing element offsets that split the flat gradient."""
+    if comm is None or comm.world_size == 1:
+        return 1.0
+    edges = [0] + [int(b) for b in boundaries] + [flat_grad.numel()]
+    assert all(a < b for a, b in zip(edges, edges[1:])), "bucket boundaries must be strictly increasing and inside"
+    for a, b in reversed(list(zip(edges, edges[1:]))):
+        comm.allreduce_sum_(flat_grad[a:b])
+    return 1.0 / comm.world_size

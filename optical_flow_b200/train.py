@@ -51,6 +51,23 @@ class Trainer:
         self._opt_state = None          # device of_adam_state {int step; float lr} (graph mode)
         self.comm = comm
         self.world_size = comm.world_size if comm is not None else 1
+        # data-parallel gradient exchange in two buckets: the decoder's 2 153 736 gradients are final
+        # before the encoder's backward starts, so their all-reduce runs on a side stream under it; the encoder
+        # bucket follows on the compute stream
+        self._dec_off = None
+        self._comm_stream = None
+        if comm is not None and self.world_size > 1:
+            st = self.flow_net.store
+            first = min((st.g[n].data_ptr() for n in st.specs if n.startswith("flow")))
+            self._dec_off = (first - st.grad.data_ptr()) // 4
+            assert all((st.g[n].data_ptr() - st.grad.data_ptr()) // 4 >= self._dec_off
+                       for n in st.specs if n.startswith("flow"))
+            assert all((st.g[n].data_ptr() - st.grad.data_ptr()) // 4 < self._dec_off
+                       for n in st.specs if not n.startswith("flow"))
+            self._comm_stream = torch.cuda.Stream(device=self.flow_net.device)
+            self._dec_ready = torch.cuda.Event()
+            self._dec_done = torch.cuda.Event()
+        self._dec_in_flight = False
         self.apply_l2, self.l2_reg = bool(apply_l2), float(l2_reg)
 
     @property
@@ -77,17 +94,38 @@ class Trainer:
         """tape.gradient(loss, trainable_weights) of train.py:50-55: loss + flat gradient."""
         flows = self.flow_net(batch_imgs)
         loss_value = self.loss_layer(batch_imgs, flows)            # also yields d loss / d flow_s
-        self.flow_net.backward(self.loss_layer.d_flows)
+        self.flow_net.backward(self.loss_layer.d_flows,
+                               after_decoder=self._exchange_decoder_bucket if self._comm_stream is not None else None)
         if self.apply_l2:
             st = self.flow_net.store
             for name in regularized_parameters(st.specs):
                 F.l2_regularizer(st.p[name], st.g[name], self.l2_reg, loss_value)
         return loss_value, flows
 
+    def _exchange_decoder_bucket(self):
+        cur = torch.cuda.current_stream(self.flow_net.device)
+        self._dec_ready.record(cur)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(self._dec_ready)
+            self.comm.allreduce_sum_(self.flow_net.store.grad[self._dec_off:])
+            self._dec_done.record(self._comm_stream)
+        self._dec_in_flight = True
+
+    def _exchange_gradients(self):
+        """Sum the replicas' gradients; returns the 1/N the optimizer applies.  With the decoder bucket already in
+        flight only the encoder bucket is exchanged here, then the compute stream joins the side stream."""
+        st = self.flow_net.store
+        if self._dec_in_flight:
+            self._dec_in_flight = False
+            self.comm.allreduce_sum_(st.grad[:self._dec_off])
+            torch.cuda.current_stream(self.flow_net.device).wait_event(self._dec_done)
+            return 1.0 / self.world_size
+        return parallel.exchange_gradients(st.grad, self.comm)
+
     def apply_gradients(self):
         """optimizer.apply_gradients (train.py:56): Adam, Keras defaults (eps 1e-7)."""
         st = self.flow_net.store
-        scale = parallel.exchange_gradients(st.grad, self.comm)    # sum over replicas; 1/N goes into Adam
+        scale = self._exchange_gradients()                         # sum over replicas; 1/N goes into Adam
         self.step += 1
         if self._opt_state is not None:                            # graph mode: the device holds (step, lr)
             F.adam_step_dev(st.flat, st.grad, st.adam_m, st.adam_v, self._opt_state, grad_scale=scale)
@@ -122,7 +160,7 @@ class Trainer:
 
         def step_dev():
             loss_value, flows = self.forward_backward(static_in)
-            scale = parallel.exchange_gradients(st.grad, self.comm)
+            scale = self._exchange_gradients()
             F.adam_step_dev(st.flat, st.grad, st.adam_m, st.adam_v, self._opt_state, grad_scale=scale)
             return loss_value, flows
 
@@ -132,7 +170,7 @@ class Trainer:
             self._write_opt_state()
             for _ in range(max(warmup, 1)):
                 self.forward_backward(static_in)
-                parallel.exchange_gradients(st.grad, self.comm)
+                self._exchange_gradients()
             graph = torch.cuda.CUDAGraph()
             n0 = L.load().of_launch_count()
             with torch.cuda.graph(graph, stream=side):

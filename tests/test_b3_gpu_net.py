@@ -114,7 +114,7 @@ def test_graph_step_equals_eager_step(cuda, small_case, mode):
             lv, flows = tr.train_step(imgs[i % 2], i)
             losses.append(lv.item())
         assert tr.step == 4
-        out[use_graph] = (losses, tr.flow_net.store.flat.detach().clone())
+        out[use_graph] = (losses, torch.cat([tr.flow_net.store.p[n].detach().reshape(-1) for n in tr.flow_net.store.specs]))
     p0 = torch.cat([torch.tensor(small_case["params"][n]).reshape(-1) for n in tr.flow_net.store.specs]).to(cuda)
     upd_e, upd_g = out[False][1] - p0, out[True][1] - p0
     if mode == "fp32":        # atomics-free path: same arithmetic, only lr_t is formed on the device instead of the host

@@ -51,8 +51,12 @@ def _worker(rank, world, port, out_dir):
         assert mine.shape[0] == B_GLOBAL // world
         loss, _, grads = net.loss_and_grads(mine)
         flat = _flat(grads)
+        bucketed = flat.clone()
         scale = parallel.exchange_gradients(flat, comm)                  # in-place sum over replicas
         assert scale == 1.0 / world
+        # two buckets (decoder first, like Trainer's overlapped exchange) give the same sums
+        assert parallel.exchange_gradients_in_buckets(bucketed, comm, [flat.numel() * 9 // 16]) == scale
+        assert torch.equal(bucketed, flat)
         loss_sum = loss.clone().reshape(1)
         dist.all_reduce(loss_sum)
         w = _flat(net.p).detach().clone()
