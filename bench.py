@@ -247,7 +247,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="train", choices=["train", "loss"])
+    ap.add_argument("--workload", default="train", choices=["train", "loss", "kernels"])
     ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=B_PER_GPU)
     ap.add_argument("--height", type=int, default=H_FULL)
@@ -292,13 +292,15 @@ def main():
             L.check(L.load().of_set_option(name.encode(), (val or "1").encode()), "of_set_option")
     if args.workload == "loss":
         line = bench_loss(args, dev, world, rank)
+    elif args.workload == "kernels":
+        line = bench_kernels(args, dev, world, rank)
     else:
         line = bench_train(args, dev, world, rank)
     if args.option:
         line["config"]["options"] = list(args.option)
     if rank == 0:
         if not args.no_cpu_baseline:
-            line["cpu_baseline"] = (cpu_loss_baseline(args.batch) if args.workload == "loss" else
+            line["cpu_baseline"] = (cpu_loss_baseline(args.batch) if args.workload in ("loss", "kernels") else
                                     cpu_train_baseline(budget_s=20.0, height=args.height, width=args.width, max_steps=12,
                                                        sample_batch=min(per_gpu_batch(args, world), 2)))
         print(json.dumps(line))
@@ -469,6 +471,100 @@ def bench_loss(args, dev, world, rank):
                          "frac": ach / peaks["hbm"], "traffic": None, "kernel": "loss_fused_kernel",
                          "algorithmic_bytes": alg, "peak_source": peaks["src"]},
             "e2e": e2e, "gpu_launches": steps, "clocks": ck}
+
+
+def _time_us(torch, fn, iters):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3
+
+
+def bench_kernels(args, dev, world, rank):
+    """Stand-alone HBM-bound kernels of SURVEY 8a at their C2 shapes, each against its algorithmic bytes:
+    K2 / K3 feature warp fwd / bwd (model.py:55-73) at the three decoder levels that warp, fp32 and bf16 storage;
+    K1 absolute-coordinate sampler (transformations.py:85-129); K4 UnFlow image warp (old/image_warp.py:7-78);
+    K7 MyLoss photometric + smoothness (old/loss.py:40-105, 5 scales).  Inputs exceed or rotate through L2."""
+    import torch
+    from optical_flow_b200 import functional as F
+    B, H, W = args.batch, args.height, args.width
+    peaks = measured_peaks()
+    iters = max(args.steps, 10)
+    rows = {}
+    g = torch.Generator(device="cpu").manual_seed(5)
+
+    def smooth_flow(h, w, amp):
+        c = torch.randn((B, 2, max(h // 8, 2), max(w // 8, 2)), generator=g)
+        f = torch.nn.functional.interpolate(c, size=(h, w), mode="bilinear", align_corners=False)
+        return (f * amp / f.std()).permute(0, 2, 3, 1).contiguous().to(dev)
+
+    def add(name, us, nbytes):
+        ach = nbytes / (us * 1e-6) / 1e9
+        rows[name] = {"us": round(us, 2), "algorithmic_bytes": int(nbytes), "achieved": round(ach, 1),
+                      "frac": round(ach / peaks["hbm"], 4)}
+
+    for (lvl, h, w, C) in ((3, H // 2, W // 2, 64), (2, H // 4, W // 4, 64), (1, H // 8, W // 8, 128)):
+        flow = smooth_flow(h, w, 4.0 / 2 ** (3 - lvl))
+        for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
+            feats = torch.randn((B, h, w, C), device=dev).to(dt)
+            d_out = torch.randn((B, h, w, C), device=dev).to(dt)
+            tag = "level%d_%dx%dx%d_%s" % (lvl, h, w, C, "f32" if es == 4 else "bf16")
+            us = _time_us(torch, lambda: F.warp_features_fwd(flow, feats), iters)
+            add("K2_warp_features_fwd_" + tag, us, B * h * w * (2 * C * es + 8))
+            us = _time_us(torch, lambda: F.warp_features_bwd(flow, feats, d_out), iters)
+            add("K3_warp_features_bwd_" + tag, us, B * h * w * (2 * C * es + C * 4 + 16))   # d_features is f32
+        del feats, d_out
+    h, w, C = H // 2, W // 2, 64
+    feats = torch.randn((B, h, w, C), device=dev)
+    pts = (smooth_flow(h, w, 4.0) + torch.stack(torch.meshgrid(torch.arange(w), torch.arange(h), indexing="xy"), -1)
+           .to(dev).float())
+    add("K1_bilinear_sample_fwd_%dx%dx%d_f32" % (h, w, C), _time_us(torch, lambda: F.bilinear_sample_fwd(feats, pts), iters),
+        B * h * w * 4 * (2 * C + 2))
+    del feats, pts
+    im = torch.rand((B, H, W, 3), device=dev)
+    fl = smooth_flow(H, W, 8.0)
+    add("K4_image_warp_fwd_%dx%dx3" % (H, W), _time_us(torch, lambda: F.image_warp_fwd(im, fl), iters), B * H * W * 4 * (2 * 3 + 2))
+    d_im = torch.rand((B, H, W, 3), device=dev)
+    add("K4_image_warp_bwd_%dx%dx3" % (H, W), _time_us(torch, lambda: F.image_warp_bwd(im, fl, d_im), iters),
+        B * H * W * 4 * (3 * 3 + 4))
+    del im, fl, d_im
+    # K7: MyLoss, 5 scales coarse to fine (old/loss.py:24-25), 4 rotating input sets
+    from optical_flow_b200.train import synthetic_batch
+    sets = []
+    for k in range(4):
+        imgs = synthetic_batch(B, H, W, 99 + k, dev)
+        flows = [smooth_flow(H // d, W // d, 8.0 / d) for d in (16, 8, 4, 2, 1)]
+        sets.append((imgs, flows, [torch.empty_like(f) for f in flows], torch.empty(1, device=dev)))
+    state = {"i": 0}
+
+    def k7():
+        imgs, flows, d_flows, lo = sets[state["i"] % 4]
+        state["i"] += 1
+        F.loss_charbonnier_smooth(imgs, flows, need_grads=True, loss_out=lo, d_flows=d_flows)
+
+    px = sum(B * (H // d) * (W // d) for d in (16, 8, 4, 2, 1))
+    add("K7_my_loss_fwdbwd_5_scales", _time_us(torch, k7, iters), 4 * (6 * B * H * W + 4 * px))
+    worst = min(rows.values(), key=lambda r: r["frac"])
+    k3 = rows["K3_warp_features_bwd_level3_%dx%dx64_bf16" % (H // 2, W // 2)]
+    return {"metric": "achieved HBM GB/s of the stand-alone warp / loss kernels (K1-K4, K7) at the C2 shapes",
+            "value": k3["achieved"], "unit": "GB/s", "n_gpus": world, "steps": iters, "warmup": 3,
+            "ms_per_step": k3["us"] * 1e-3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "stand-alone kernels K1-K4, K7, batch %d at %dx%d (value = K3 level-3 bf16 backward)" % (B, H, W),
+                       "l2": "each kernel's tensors exceed the 126 MB L2 at level 3; K7 rotates 4 input sets"},
+            "roofline": {"bound": "hbm", "achieved": k3["achieved"], "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": k3["frac"], "traffic": None, "kernel": "sample_bwd_kernel (K3, level 3, bf16)",
+                         "peak_source": peaks["src"], "kernels": rows,
+                         "note": "algorithmic bytes per SURVEY 8d; the scatter's zero-fill and read-modify-write are overhead"},
+            "e2e": {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "note": "kernel-only leg; the end-to-end number is the train workload's"},
+            "gpu_launches": len(rows) * iters, "clocks": None}
 
 
 def time_dominant_conv(torch, dev, N, H, W, Cin, Cout, iters=20):

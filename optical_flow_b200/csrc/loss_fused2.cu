@@ -8,9 +8,9 @@
 //                   (12 KB per stage, mbarrier full / built / empty per stage, evict_first);
 //   warp 1          watcher: the only poller of the global per-image "pyramid complete" counters; it republishes
 //                   them to a shared-memory word the gather warps spin on (no L2 hot spot);
-//   warp 2          publisher: follows the patches of its CTA in order (built barriers), hands ring slots back to the
-//                   producer, and at every image boundary issues ONE gpu-scope release fence + counter add for all the
-//                   patches of that image this CTA built - the ~1-2 us fence stalls nobody who computes;
+//   warp 2          publisher: follows the patches of its CTA in order (per-builder-warp progress words) and at every
+//                   image boundary issues ONE gpu-scope release fence + counter add for all the patches of that image
+//                   this CTA built - the ~1-2 us fence stalls nobody who computes;
 //   warps 3..10     BUILD: each warp owns every eighth patch of its CTA: all four pyramid levels of both frames
 //                   (tf.image.resize at 2^k = the central 2x2 mean) from shared memory -> float4 texels, evict_last;
 //   warps 11..      GATHER: each warp owns its own 128-pixel output tiles (static round-robin over the whole grid, so
@@ -122,23 +122,26 @@ __device__ __forceinline__ L2fTile l2f_decode(const L2fParams& P, int u) {
   return t;
 }
 
-// Gather tile geometry.  REF_IJ: 8 x 16 pixels, an instruction covers 8 rows x 4 columns - the transposed gather
-// (source column = i) then reads 8 consecutive texels of 4 source rows.  XY: 4 x 32, one output row per instruction.
+// Gather tile geometry: 64 pixels per warp tile, two per lane (both in flight together).  REF_IJ: 8 x 8 pixels, an
+// instruction covers 8 rows x 4 columns - the transposed gather (source column = i) then reads 8 consecutive texels
+// of 4 source rows.  XY: 2 x 32, one output row per instruction.  Small tiles on purpose: a gather tile is one L2
+// round trip (half of it to the far die's L2 partition), and an image's tiles can only start once the whole image is
+// built, so the tiles of one image should cover ALL gather warps of the grid (C2: 2 550 tiles vs 2 516 warps).
 // Pixel q of a lane sits at a constant offset (di(q), dj(q)) from the lane's first pixel.
 template <int MODE> struct L2fGeom;
 template <> struct L2fGeom<OF_WARP_REF_IJ> {
-  static constexpr int TI = 8, TJ = 16;
+  static constexpr int TI = 8, TJ = 8;
   __device__ static __forceinline__ void first(const L2fTile& t, int lane, int* i, int* j) {
     *i = t.ti * 8 + (lane & 7);
-    *j = t.tj * 16 + (lane >> 3);
+    *j = t.tj * 8 + (lane >> 3);
   }
   __device__ static __forceinline__ int di(int) { return 0; }
   __device__ static __forceinline__ int dj(int q) { return 4 * q; }
 };
 template <> struct L2fGeom<OF_WARP_XY> {
-  static constexpr int TI = 4, TJ = 32;
+  static constexpr int TI = 2, TJ = 32;
   __device__ static __forceinline__ void first(const L2fTile& t, int lane, int* i, int* j) {
-    *i = t.ti * 4;
+    *i = t.ti * 2;
     *j = t.tj * 32 + lane;
   }
   __device__ static __forceinline__ int di(int q) { return q; }
@@ -148,8 +151,7 @@ template <> struct L2fGeom<OF_WARP_XY> {
 // Ragged tiles (h or w not a multiple of the tile) are handled without a second code path: a pixel outside the image
 // is CLAMPED onto the last row / column (all of its loads are then valid) and its contribution is masked at the end.
 template <int MODE>
-__device__ __forceinline__ void l2f_load_flows(const L2fParams& P, const L2fTile& t, int lane, float2& fl0, float2& fl1,
-                                               float2& fl2, float2& fl3) {
+__device__ __forceinline__ void l2f_load_flows(const L2fParams& P, const L2fTile& t, int lane, float2& fl0, float2& fl1) {
   using G = L2fGeom<MODE>;
   const L2fScale& S = P.sc[t.s];
   int i0, j0;
@@ -158,8 +160,6 @@ __device__ __forceinline__ void l2f_load_flows(const L2fParams& P, const L2fTile
   const int hm = S.h - 1, wm = S.w - 1;
   fl0 = __ldg(g + min(i0 + G::di(0), hm) * S.w + min(j0 + G::dj(0), wm));
   fl1 = __ldg(g + min(i0 + G::di(1), hm) * S.w + min(j0 + G::dj(1), wm));
-  fl2 = __ldg(g + min(i0 + G::di(2), hm) * S.w + min(j0 + G::dj(2), wm));
-  fl3 = __ldg(g + min(i0 + G::di(3), hm) * S.w + min(j0 + G::dj(3), wm));
 }
 
 // one pixel of a gather tile in two steps, so a thread keeps the taps of two pixels in flight: l2f_issue computes the
@@ -222,15 +222,11 @@ __device__ __forceinline__ void l2f_finish(const L2fPix& r, float2* __restrict__
 template <int MODE>
 __device__ __forceinline__ void l2f_gather_tile(const float4* __restrict__ q1, const float4* __restrict__ q2,
                                                 float2* __restrict__ gdflow, int h, int w, float inv_n, uint64_t keep,
-                                                int i0, int j0, float2 f0, float2 f1, float2 f2, float2 f3, float& acc) {
+                                                int i0, int j0, float2 f0, float2 f1, float& acc) {
   using G = L2fGeom<MODE>;
   L2fPix a, b;
   l2f_issue<MODE>(a, q1, q2, h, w, keep, i0 + G::di(0), j0 + G::dj(0), f0);
   l2f_issue<MODE>(b, q1, q2, h, w, keep, i0 + G::di(1), j0 + G::dj(1), f1);
-  l2f_finish(a, gdflow, inv_n, acc);
-  l2f_finish(b, gdflow, inv_n, acc);
-  l2f_issue<MODE>(a, q1, q2, h, w, keep, i0 + G::di(2), j0 + G::dj(2), f2);
-  l2f_issue<MODE>(b, q1, q2, h, w, keep, i0 + G::di(3), j0 + G::dj(3), f3);
   l2f_finish(a, gdflow, inv_n, acc);
   l2f_finish(b, gdflow, inv_n, acc);
 }
@@ -241,9 +237,9 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
   extern __shared__ __align__(128) uint8_t l2f_smem[];
   uint8_t* tiles = l2f_smem;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(l2f_smem + L2F_STAGES * L2F_STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + L2F_STAGES;      // publisher -> producer
-  uint64_t* built_bar = empty_bar + L2F_STAGES;     // builder warp -> publisher
+  uint64_t* empty_bar = full_bar + L2F_STAGES;      // builder warp -> producer
   __shared__ double s_part[L2F_GATHER_WARPS];
+  __shared__ unsigned s_progress[L2F_BUILD_WARPS];   // builder warp w: 1 + index of its latest finished local patch
   __shared__ unsigned s_built;          // images whose pyramid is complete and visible (watcher -> gather warps)
   __shared__ bool s_last;
 
@@ -252,8 +248,8 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     for (int s = 0; s < L2F_STAGES; ++s) {
       tc::mbar_init(&full_bar[s], 1);
       tc::mbar_init(&empty_bar[s], 1);
-      tc::mbar_init(&built_bar[s], 1);
     }
+    for (int w = 0; w < L2F_BUILD_WARPS; ++w) s_progress[w] = 0u;
     s_built = 0u;
     tc::fence_barrier_init();
   }
@@ -283,7 +279,9 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     // ===================== watcher =====================
     if (lane == 0 && !(OF_DBG(P) & (4 | 8 | 16))) {
       for (int b = 0; b < P.B; ++b) {
-        while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(100);
+        // 148 watchers poll ONE L2 line: keep the rate low (a poll every ~0.4 us per SM) or the slice that owns the
+        // line becomes a hot spot for the image stream that shares it
+        while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(400);
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
         st_release_cta_shared(&s_built, (unsigned)(b + 1));
       }
@@ -298,14 +296,13 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       while (p < n_build) {
         int npub = 0;
         bool first = true;
-        // take every patch that is already built (blocking only for the first), in order
+        // take every patch that is already built (blocking only for the first), in order: local patch k belongs to
+        // builder warp k % 8, whose progress word passes k when its stores are issued
         while (p < n_build && npub < L2F_PUB_BATCH) {
-          const int stage = k % L2F_STAGES;
-          const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
-          if (first) tc::mbar_wait(&built_bar[stage], phase);
-          else if (!mbar_test(&built_bar[stage], phase)) break;
+          const unsigned* word = &s_progress[k % L2F_BUILD_WARPS];
+          if (first) { while (ld_acquire_cta_shared(word) <= (unsigned)k) __nanosleep(40); }
+          else if (ld_acquire_cta_shared(word) <= (unsigned)k) break;
           first = false;
-          tc::mbar_arrive(&empty_bar[stage]);                      // the slot refills while the release drains
           const int b = p / P.nb;
           ++cur_cnt;
           p += gridDim.x; ++k;
@@ -385,7 +382,10 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         }
       }
       __syncwarp();                       // every lane's shared-memory reads and pyramid stores are issued
-      if (lane == 0) tc::mbar_arrive(&built_bar[stage]);
+      if (lane == 0) {
+        tc::mbar_arrive(&empty_bar[stage]);                        // the ring slot refills
+        st_release_cta_shared(&s_progress[bw], (unsigned)(k + 1)); // the publisher follows
+      }
     }
   } else {
     // ===================== GATHER =====================
@@ -395,13 +395,13 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     const int tgw = L2F_GATHER_WARPS * gridDim.x;
     const int total_gather = (OF_DBG(P) & 2) ? 0 : P.total_gather;
     int confirmed = 0;                  // images known complete
-    float2 n0 = make_float2(0.f, 0.f), n1 = n0, n2 = n0, n3 = n0;
+    float2 n0 = make_float2(0.f, 0.f), n1 = n0;
     L2fTile nt;
-    if (gw < total_gather) { nt = l2f_decode(P, gw); l2f_load_flows<MODE>(P, nt, lane, n0, n1, n2, n3); }
+    if (gw < total_gather) { nt = l2f_decode(P, gw); l2f_load_flows<MODE>(P, nt, lane, n0, n1); }
     for (int u = gw; u < total_gather; u += tgw) {
       const L2fTile t = nt;
-      const float2 f0 = n0, f1 = n1, f2 = n2, f3 = n3;
-      if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows<MODE>(P, nt, lane, n0, n1, n2, n3); }   // in flight
+      const float2 f0 = n0, f1 = n1;
+      if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows<MODE>(P, nt, lane, n0, n1); }   // in flight
       if (t.b >= confirmed && !(OF_DBG(P) & 4)) {
         unsigned v;
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
@@ -415,7 +415,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       float2* gdflow = S.d_flow ? reinterpret_cast<float2*>(S.d_flow) + img_px : nullptr;
       int i0, j0;
       G::first(t, lane, &i0, &j0);
-      l2f_gather_tile<MODE>(q1, q2, gdflow, h, w, S.inv_n, keep, i0, j0, f0, f1, f2, f3, acc);
+      l2f_gather_tile<MODE>(q1, q2, gdflow, h, w, S.inv_n, keep, i0, j0, f0, f1, acc);
     }
   }
 
@@ -516,7 +516,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
     OF_REQUIRE(r == CUDA_SUCCESS, OF_ERR_STATE, "cuTensorMapEncodeTiled(images) failed: %d", (int)r);
   }
 
-  const size_t smem = (size_t)L2F_STAGES * L2F_STAGE_BYTES + 3 * L2F_STAGES * sizeof(uint64_t);
+  const size_t smem = (size_t)L2F_STAGES * L2F_STAGE_BYTES + 2 * L2F_STAGES * sizeof(uint64_t);
   static int max_ctas = 0;
   if (max_ctas == 0) {
     OF_CUDA(cudaFuncSetAttribute(loss_ws_kernel<OF_WARP_REF_IJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

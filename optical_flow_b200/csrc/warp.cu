@@ -93,6 +93,18 @@ __device__ __forceinline__ bool tile_pixel(long long tile, int p, int H, int W, 
   j = tx * TILE + p % TILE;
   return i < H && j < W;
 }
+// column-major walk of a TILE x TJ tile (RUN kernels): pixel p -> (row p % TILE, column p / TILE)
+template <int TJ>
+__device__ __forceinline__ bool tile_pixel_run(long long tile, int p, int H, int W, int tiles_x, int tiles_y,
+                                               int& b, int& i, int& j) {
+  int tx = (int)(tile % tiles_x);
+  long long r = tile / tiles_x;
+  int ty = (int)(r % tiles_y);
+  b = (int)(r / tiles_y);
+  i = ty * TILE + p % TILE;
+  j = tx * TJ + p / TILE;
+  return i < H && j < W;
+}
 
 // ------------------------------------------------------------------ forward --
 template <typename T, int VEC, int SRC>
@@ -169,6 +181,9 @@ __device__ __forceinline__ float combine_peers(unsigned peers, int rank, int lan
 // flushed (one red.global.add.v4) when the address changes.  Under model.py:65-71's row/column swap every output
 // column j >= H - 1 - flow reads the clamped last row, so ~70 % of a 192 x 640 level's pixels scatter into one row:
 // the run merge turns 4 atomics per pixel there into 4 per 16-pixel run.
+// RUN tiles are TILE rows x RUN_TJ columns: the longer the walk along j, the longer the runs that merge (in the clamped
+// region one flush per tile instead of one per 16 pixels: 4x fewer atomics on the hot row at RUN_TJ = 64)
+#define RUN_TJ 64
 template <typename T, int VEC, int TPP, int SRC, typename G = float, bool RUN = false>
 __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ in,
                                                          const float* __restrict__ coords,
@@ -177,7 +192,8 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
                                                          float* __restrict__ d_coords,
                                                          int B, int H, int W, int C) {
   const int CV = C / VEC;
-  const int tiles_x = (W + TILE - 1) / TILE, tiles_y = (H + TILE - 1) / TILE;
+  constexpr int TJ = RUN ? RUN_TJ : TILE;
+  const int tiles_x = (W + TJ - 1) / TJ, tiles_y = (H + TILE - 1) / TILE;
   const long long ntiles = (long long)B * tiles_x * tiles_y;
   const int lane = threadIdx.x & 31;
   const int sub = threadIdx.x % TPP;       // lane within the pixel's thread group
@@ -187,11 +203,12 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
     float4 racc[4][VEC == 8 ? 2 : 1];                 // RUN: pending contribution per tap slot
     size_t raddr[4];
     bool rvalid[4] = {false, false, false, false};
-    for (int p0 = 0; p0 < TILE * TILE; p0 += PIX_PER_PASS) {
+    for (int p0 = 0; p0 < TILE * TJ; p0 += PIX_PER_PASS) {
       int p = p0 + grp;
       int b, i, j;
       // RUN walks the tile column by column: pixel p -> (row p % TILE, column p / TILE)
-      bool valid = tile_pixel(tile, RUN ? (p % TILE) * TILE + p / TILE : p, H, W, tiles_x, tiles_y, b, i, j);
+      bool valid = RUN ? tile_pixel_run<TJ>(tile, p, H, W, tiles_x, tiles_y, b, i, j)
+                       : tile_pixel(tile, p, H, W, tiles_x, tiles_y, b, i, j);
       size_t pix = valid ? ((size_t)b * H + i) * W + j : 0;
       float2 c = valid ? __ldg(reinterpret_cast<const float2*>(coords) + pix) : make_float2(0.f, 0.f);
       Taps t = make_taps<SRC>(c.x, c.y, valid ? i : 0, valid ? j : 0, H, W);
@@ -373,6 +390,7 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
                       int B, int H, int W, int C, cudaStream_t st) {
   long long ntiles = (long long)B * ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
   int grid = grid_for(ntiles);
+  const int grid_run = grid_for((long long)B * ((W + RUN_TJ - 1) / RUN_TJ) * ((H + TILE - 1) / TILE));
   if (d_in != nullptr) {
     cudaError_t e = cudaMemsetAsync(d_in, 0, (size_t)B * H * W * C * sizeof(float), st);
     if (e != cudaSuccess) { of_set_error("memset d_in: %s", cudaGetErrorString(e)); return (int)e; }
@@ -381,16 +399,16 @@ static int launch_bwd(const void* in, const float* coords, const void* d_out, fl
   sample_bwd_kernel<T, VEC, TPP, SRC, G><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
                                                                d_coords, B, H, W, C)
 #define LRUN(TPP)                                                                                    \
-  sample_bwd_kernel<T, 4, TPP, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
-                                                                   d_coords, B, H, W, C)
+  sample_bwd_kernel<T, 4, TPP, SRC, G, true><<<grid_run, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, \
+                                                                       d_coords, B, H, W, C)
   const bool run = SRC == SRC_REF_IJ && d_in != nullptr && !of_tune_env("OF_WARP_NO_RUN");
   // bf16 features + bf16 gradient, C = 64 / 128: 16-byte accesses, 8 / 16 threads per pixel
   if (sizeof(T) == 2 && sizeof(G) == 2 && run && (C == 64 || C == 128) && !of_tune_env("OF_WARP_NO_VEC8") &&
       ((((uintptr_t)in | (uintptr_t)d_out) & 15) == 0)) {
     if (C == 64)
-      sample_bwd_kernel<T, 8, 8, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
+      sample_bwd_kernel<T, 8, 8, SRC, G, true><<<grid_run, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
     else
-      sample_bwd_kernel<T, 8, 16, SRC, G, true><<<grid, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
+      sample_bwd_kernel<T, 8, 16, SRC, G, true><<<grid_run, 256, 0, st>>>((const T*)in, coords, (const G*)d_out, d_in, d_coords, B, H, W, C);
   } else
   if (C % 4 == 0) {
     int cv = C / 4;

@@ -93,7 +93,7 @@ class ConvLayer:
         net = self.net
         w = self._p("/kernel")
         b = self._p("/bias") if self.use_bias else None
-        if self.bn is None:
+        if self.bn is None or net.bn_mode == "train":     # batch-statistics BN is a layer of its own, nothing to fold
             return w, b
         K = self.k * self.k * self.cin
         wf = net.buf(self.name + ":wf", w.shape, torch.float32)
@@ -110,8 +110,56 @@ class ConvLayer:
         if not self.weights_ready:
             self.w_eff, self.b_eff = self.effective_weights()
         self.weights_ready = False
+        if self.bn is not None and self.net.bn_mode == "train":
+            # conv (no activation) -> BatchNormalization(training=True) + activation (resnet/batchnorm.py)
+            lin = self._linear_view()
+            lin.x = x
+            z = self.net.backend.fprop(lin, x, self.w_eff, self.b_eff)
+            self.y = self._bn_layer()(z)
+            return self.y
         self.y = self.net.backend.fprop(self, x, self.w_eff, self.b_eff)
         return self.y
+
+    # -- opt-in training-mode BatchNormalization (FlowNet(bn_mode="train")) --------------
+    def _linear_view(self):
+        """This layer as the back-end sees it in bn_mode='train': the bare convolution (no folded BN, no fused
+        activation, no chained epilogues), same weights and gradient buffers."""
+        if getattr(self, "_lin", None) is None:
+            lin = ConvLayer.__new__(ConvLayer)
+            lin.__dict__.update(self.__dict__)
+            lin.act, lin.bn, lin.prev_chain, lin.incoming_is_dz = L.OF_ACT_NONE, None, None, False
+            self._lin = lin
+        return self._lin
+
+    def _bn_layer(self):
+        if getattr(self, "_bn_obj", None) is None:
+            from .resnet.batchnorm import BatchNormalizationTraining
+            st = self.net.store
+            tensors = dict(gamma=st.p[self.bn + "/gamma"], beta=st.p[self.bn + "/beta"],
+                           moving_mean=st.stats[self.bn + "/moving_mean"],
+                           moving_variance=st.stats[self.bn + "/moving_variance"],
+                           d_gamma=st.g[self.bn + "/gamma"], d_beta=st.g[self.bn + "/beta"])
+            self._bn_obj = BatchNormalizationTraining(self.cout, epsilon=BN_EPS, act=self.act, device=self.net.device,
+                                                      comm=self.net.bn_comm, tensors=tensors)
+        return self._bn_obj
+
+    def _backward_bn_train(self, dy, need_dx, add):
+        net = self.net
+        bn = self._bn_layer()
+        dz = bn.backward(dy, act_applied=self.incoming_is_dz)     # d loss / d conv output; fills d_gamma, d_beta
+        self.incoming_is_dz = False
+        if net.bn_comm is not None and net.bn_comm.world_size > 1:
+            # the layer all-reduced its gradient sums; the trainer's exchange will sum the N identical copies again
+            bn.d_gamma.mul_(1.0 / net.bn_comm.world_size)
+            bn.d_beta.mul_(1.0 / net.bn_comm.world_size)
+        lin = self._linear_view()
+        net.backend.wgrad(lin, lin.x, dz, self._g("/kernel"), self._g("/bias") if self.use_bias else None)
+        if not need_dx:
+            return None
+        in_hw = (lin.x.shape[1], lin.x.shape[2])
+        if add is not None:
+            return net.backend.dgrad(lin, dz, self.w_eff, in_hw, chain=None, add=add)
+        return net.backend.dgrad(lin, dz, self.w_eff, in_hw, chain=None)
 
     def backward(self, dy, need_dx=True, add=None):
         """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None.
@@ -120,6 +168,8 @@ class ConvLayer:
         if (need_dx and self.bn is None and self.act == L.OF_ACT_NONE and self.k == 3 and self.stride == 1
                 and self.cout == 2 and self.cin <= 32 and self.use_bias and hasattr(net.backend, "head_bwd")):
             return net.backend.head_bwd(self, dy)     # flow head: dw, db and the chained dz in one pass
+        if self.bn is not None and net.bn_mode == "train":
+            return self._backward_bn_train(dy, need_dx, add)
         if self.incoming_is_dz:
             dz, self.incoming_is_dz = dy, False
         else:
@@ -145,9 +195,15 @@ class ConvLayer:
         if not need_dx:
             return None
         if add is not None:
-            return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self.prev_chain,
+            return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self._chain(),
                                      add=add)
-        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self.prev_chain)
+        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self._chain())
+
+    def _chain(self):
+        """The producer whose activation derivative this layer's dgrad epilogue may apply - none when the producer's
+        activation sits behind a training-mode BatchNormalization layer."""
+        c = self.prev_chain
+        return None if (c is not None and c.bn is not None and self.net.bn_mode == "train") else c
 
 
 class Fp32Backend:
@@ -312,7 +368,12 @@ class FlowNet:
     [flow3 (H/2), flow2 (H/4), flow1 (H/8), flow0 (H/16)], finest first."""
 
     def __init__(self, height, width, pretrained_weights_path=None, max_disp=3, conv_mode="fp32",
-                 warp_mode="ref_ij", device=None, seed=42):
+                 warp_mode="ref_ij", device=None, seed=42, bn_mode="inference", bn_comm=None):
+        """bn_mode: "inference" (default = the reference: train.py:51 calls the model without training=True, SURVEY F5;
+        BN is folded into the convolutions) or "train" (opt-in, SURVEY 8f rank 4: batch statistics, moving-statistics
+        update, cross-replica sums through ``bn_comm`` - anything with world_size and allreduce_sum_)."""
+        assert bn_mode in ("inference", "train")
+        self.bn_mode, self.bn_comm = bn_mode, bn_comm
         assert torch.cuda.is_available(), "optical_flow_b200 needs a CUDA device (no CPU fallback)"
         assert height % 16 == 0 and width % 16 == 0, "height/width must be multiples of 16 (4 stride-2 stages)"
         L.load()
@@ -445,6 +506,8 @@ class FlowNet:
     def _bn_job_table(self):
         """Device table of of_bn_job, one per conv + BN pair (all buffers persistent): both folds of the whole
         model are then one launch each.  Built once."""
+        if self.bn_mode == "train":
+            return None                               # nothing is folded: BN runs as a layer
         if getattr(self, "_bn_table", None) is not None:
             return self._bn_table
         layers = [l for l in self.conv_layers if l.bn is not None]
@@ -530,8 +593,10 @@ class FlowNet:
             assert name in data, "checkpoint lacks " + name      # assert_existing_objects_matched
             self.store.p[name].copy_(torch.from_numpy(data[name]))
         for name in self.store.stats:
-            if name in data:
-                self.store.stats[name].copy_(torch.from_numpy(data[name]))
+            # BN runs in inference mode folded into the convs: a checkpoint without the moving statistics would load
+            # and silently run with mean 0 / variance 1 (the reference's assert_existing_objects_matched would raise)
+            assert name in data, "checkpoint lacks " + name
+            self.store.stats[name].copy_(torch.from_numpy(data[name]))
 
     def summary(self):
         lines = ["Model: flow_net (%dx%d, conv_mode=%s)" % (self.height, self.width, self.conv_mode)]

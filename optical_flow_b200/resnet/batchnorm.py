@@ -13,15 +13,20 @@ from .. import _lib as L
 
 
 class BatchNormalizationTraining:
-    def __init__(self, channels, momentum=0.99, epsilon=1e-3, act=L.OF_ACT_NONE, device=None, comm=None):
+    def __init__(self, channels, momentum=0.99, epsilon=1e-3, act=L.OF_ACT_NONE, device=None, comm=None, tensors=None):
+        """``tensors``: optional dict of existing f32 (C,) device tensors to use in place (FlowNet passes views of its
+        flat parameter / gradient / statistics buffers): gamma, beta, moving_mean, moving_variance, d_gamma, d_beta."""
         dev = device or torch.device("cuda", torch.cuda.current_device())
         self.C, self.momentum, self.epsilon, self.act, self.comm = int(channels), float(momentum), float(epsilon), act, comm
-        self.gamma = torch.ones(channels, device=dev)
-        self.beta = torch.zeros(channels, device=dev)
-        self.moving_mean = torch.zeros(channels, device=dev)
-        self.moving_variance = torch.ones(channels, device=dev)
-        self.d_gamma = torch.zeros(channels, device=dev)
-        self.d_beta = torch.zeros(channels, device=dev)
+        t = tensors or {}
+        self.gamma = t.get("gamma", None) if "gamma" in t else torch.ones(channels, device=dev)
+        self.beta = t["beta"] if "beta" in t else torch.zeros(channels, device=dev)
+        self.moving_mean = t["moving_mean"] if "moving_mean" in t else torch.zeros(channels, device=dev)
+        self.moving_variance = t["moving_variance"] if "moving_variance" in t else torch.ones(channels, device=dev)
+        self.d_gamma = t["d_gamma"] if "d_gamma" in t else torch.zeros(channels, device=dev)
+        self.d_beta = t["d_beta"] if "d_beta" in t else torch.zeros(channels, device=dev)
+        for v in (self.gamma, self.beta, self.moving_mean, self.moving_variance, self.d_gamma, self.d_beta):
+            assert v.dtype == torch.float32 and v.numel() == channels and v.is_contiguous()
         self._stats = torch.zeros((2, channels), device=dev)      # sum, sum of squares (about _shift)
         self._shift = torch.zeros(channels, device=dev)           # snapshot of the moving mean taken by __call__
         self._ws = torch.empty(L.load().of_bn_train_workspace_bytes(int(channels)), dtype=torch.uint8, device=dev)
@@ -52,14 +57,16 @@ class BatchNormalizationTraining:
         self._saved = (x, y, count)
         return y
 
-    def backward(self, dy):
-        """dy: gradient w.r.t. the (activated) output.  Returns dx; fills ``d_gamma`` / ``d_beta``."""
+    def backward(self, dy, act_applied=False):
+        """dy: gradient w.r.t. the (activated) output.  Returns dx; fills ``d_gamma`` / ``d_beta``.
+        ``act_applied``: dy was already multiplied by the activation's derivative (a fused upstream epilogue did it)."""
         x, y, count = self._saved
+        act = L.OF_ACT_NONE if act_applied else self.act
         assert dy.shape == x.shape and dy.dtype == x.dtype and dy.is_contiguous()
         npix = x.numel() // self.C
         lib = L.load()
         L.check(lib.of_bn_train_bwd_reduce(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]),
-                                           L.ptr(self._shift), count, self.epsilon, self.act, L.ptr(self.d_beta),
+                                           L.ptr(self._shift), count, self.epsilon, act, L.ptr(self.d_beta),
                                            L.ptr(self.d_gamma), npix, self.C, L.dtype_code(x), L.ptr(self._ws),
                                            L.stream_ptr()), "of_bn_train_bwd_reduce")
         if self.comm is not None:
@@ -67,6 +74,6 @@ class BatchNormalizationTraining:
             self.comm.allreduce_sum_(self.d_gamma)
         dx = torch.empty_like(x)
         L.check(lib.of_bn_train_bwd_apply(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(self._stats[0]), L.ptr(self._stats[1]),
-                                          L.ptr(self._shift), count, L.ptr(self.gamma), self.epsilon, self.act, L.ptr(self.d_beta), L.ptr(self.d_gamma),
+                                          L.ptr(self._shift), count, L.ptr(self.gamma), self.epsilon, act, L.ptr(self.d_beta), L.ptr(self.d_gamma),
                                           L.ptr(dx), npix, self.C, L.dtype_code(x), L.stream_ptr()), "of_bn_train_bwd_apply")
         return dx

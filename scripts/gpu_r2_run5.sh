@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, call 5: loss kernel v2.1 parity, gather-warp A/B, dissection, ncu capture
 mkdir -p gpurun_out
-( timeout 900 python -m pytest tests -m gpu -q -x -k "loss or graph_step or golden" ) > gpurun_out/r2_pytest_5.log 2>&1
+( timeout 900 python -m pytest tests -m gpu -q -x -k "loss or graph_step or golden or warp" ) > gpurun_out/r2_pytest_5.log 2>&1
 echo "pytest rc=$?" >> gpurun_out/r2_pytest_5.log
 tail -6 gpurun_out/r2_pytest_5.log
 for v in "" g13 g21; do

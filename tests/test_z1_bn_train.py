@@ -161,3 +161,56 @@ def test_bn_train_shifted_variance(cuda):
     ey, edx, eg, eb = reference(x, np.ones(64, np.float32), np.zeros(64, np.float32), g, 0)
     close(y, ey, 1e-4)         # x itself carries 100 * 2^-24 = 6e-6 of rounding on a sigma of 0.5
     close(dx, edx, 2e-4)
+
+
+@pytest.mark.parametrize("mode,tol", [("fp32", 2e-3), ("bf16", 0.25)])
+def test_flownet_bn_train_mode_matches_torch(cuda, mode, tol):
+    """FlowNet(bn_mode="train"): every BatchNormalization of the encoder (model.py:14; resnet/models.py:19,24) on batch
+    statistics, through the whole network and loss, against the torch oracle with F.batch_norm(training=True):
+    loss, flows, and the gradient of every parameter (relative L2 per tensor; bf16 tolerance stated)."""
+    from oracle import ref_torch as T
+    from optical_flow_b200.train import Trainer
+    B, H, W = 2, 64, 96
+    params, stats = T.init_params(seed=42, randomize_bn=True)
+    imgs = T.synthetic_pairs(B, H, W, seed=11)
+
+    class TrainBnRef(T.FlowNetRef):
+        def encoder(self, img):                 # the reference encodes the two frames separately: batch statistics per call
+            return super().encoder(img)
+
+        def _bn(self, x, name):
+            y = torch.nn.functional.batch_norm(x.permute(0, 3, 1, 2), None, None, self.p[name + "/gamma"],
+                                               self.p[name + "/beta"], True, 0.0, 1e-3)
+            return y.permute(0, 2, 3, 1)
+
+        def __call__(self, batch_imgs):         # FlowNet runs the shared encoder ONCE on the 2B stacked frames
+            n = batch_imgs.shape[0]
+            e = self.encoder(torch.cat([batch_imgs[..., :3], batch_imgs[..., 3:]], dim=0))
+            e1, e2 = [t[:n] for t in e], [t[n:] for t in e]
+            flow0 = self.flow_module(e1[-1], e2[-1], None, 0)
+            flow1 = self.flow_module(e1[-2], e2[-2], flow0, 1)
+            flow2 = self.flow_module(e1[-3], e2[-3], flow1, 2)
+            flow3 = self.flow_module(e1[-4], e2[-4], flow2, 3)
+            return [flow3, flow2, flow1, flow0]
+
+    r_loss, r_flows, r_grads = TrainBnRef(params, stats).loss_and_grads(torch.tensor(imgs))
+    tr = Trainer(H, W, None, conv_mode=mode, bn_mode="train")
+    tr.flow_net.store.load_numpy(params, stats)
+    mm0 = tr.flow_net.store.stats["layer1_bn/moving_mean"].clone()
+    loss, flows = tr.forward_backward(torch.tensor(imgs, device=cuda))
+    assert abs(loss.item() - r_loss.item()) < (1e-4 if mode == "fp32" else 3e-2) * abs(r_loss.item())
+    worst = ("", 0.0)
+    biggest = max(float(v.norm()) for v in r_grads.values())
+    for name, g in tr.flow_net.store.g.items():
+        e = r_grads[name].numpy().astype(np.float64).ravel()
+        got = g.detach().cpu().numpy().astype(np.float64).ravel()
+        if np.linalg.norm(e) < 1e-5 * biggest:
+            # a conv bias in front of a batch-statistics BN has an exactly-zero gradient (the mean is subtracted):
+            # both sides hold rounding noise there
+            assert np.linalg.norm(got) < 1e-3 * biggest, name
+            continue
+        rel = float(np.linalg.norm(got - e) / np.linalg.norm(e))
+        if rel > worst[1]:
+            worst = (name, rel)
+    assert worst[1] < tol, worst
+    assert not torch.equal(tr.flow_net.store.stats["layer1_bn/moving_mean"], mm0)      # moving statistics were updated
