@@ -684,7 +684,7 @@ def bench_train(args, dev, world, rank):
     h_loss = torch.empty(1).pin_memory()
 
     def run_e2e(n):
-        feed = HostFramePrefetcher((h_frames[i % nsets] for i in range(n)), dev, H, W)
+        feed = HostFramePrefetcher((h_frames[i % nsets] for i in range(n)), dev, H, W, out=tr.graph_input())
         for i, (d_in, release) in enumerate(feed):
             loss, _ = tr.train_step(d_in, i)
             release()

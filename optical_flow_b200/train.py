@@ -243,10 +243,12 @@ class HostFramePrefetcher(HostBatchPrefetcher):
     the copy of batch i+1 runs on a copy stream under the compute of batch i, and one of_preprocess_batch launch on
     the compute stream turns the frames into the (B, H, W, 6) float32 network input (resize, / 255, BGR means)."""
 
-    def __init__(self, batches, device, height, width):
+    def __init__(self, batches, device, height, width, out=None):
+        """``out``: write every batch into this (B, H, W, 6) tensor instead of two rotating buffers - pass
+        ``Trainer.graph_input()`` so a graph-captured step reads its input where the preprocessing kernel left it."""
         from .data_reader import ReaderOpts
         self.opts = ReaderOpts(img_height=height, img_width=width)
-        self.net_in = [None, None]
+        self.net_in = [out, out] if out is not None else [None, None]
         super().__init__(batches, device)
 
     def __next__(self):
