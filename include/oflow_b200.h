@@ -56,6 +56,9 @@ int of_set_option(const char* name, const char* value);
 typedef struct { char name[40]; double work; float ms; } of_prof_rec;
 int of_prof_enable(int on, void* stream);
 int of_prof_collect(of_prof_rec* out, int max_recs);
+/* Adds a boundary named `name` to the timeline without launching anything: the interval since the previous record
+ * (e.g. a delay kernel the caller queued so that the host runs ahead of the device) is booked under that name. */
+int of_prof_marker(const char* name);
 
 /* ---- sampler ------------------------------------------------------------
  * transformations.py:85-129 bilinear_interpolation (+ :70-81 gather).

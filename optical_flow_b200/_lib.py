@@ -104,6 +104,7 @@ PROTOTYPES = {
     "of_set_option": (C.c_int, [C.c_char_p, C.c_char_p]),
     "of_prof_enable": (C.c_int, [C.c_int, C.c_void_p]),
     "of_prof_collect": (C.c_int, [C.POINTER(ProfRec), C.c_int]),
+    "of_prof_marker": (C.c_int, [C.c_char_p]),
     "of_bilinear_sample_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_bilinear_sample_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "of_warp_features_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

@@ -196,7 +196,16 @@ __global__ void __launch_bounds__(256) colsum4_kernel(const TY* __restrict__ dy,
   const int g = threadIdx.x % cg, pr = threadIdx.x / cg;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (pr < ppp) {
-    for (size_t p = (size_t)blockIdx.x * ppp + pr; p < P; p += (size_t)gridDim.x * ppp) {
+    // four rows in flight per thread (independent loads, then the adds)
+    const size_t stride = (size_t)gridDim.x * ppp;
+    size_t p = (size_t)blockIdx.x * ppp + pr;
+    for (; p + 3 * stride < P; p += 4 * stride) {
+      const float4 v0 = ld4<TY>(dy + p * ld + g * 4), v1 = ld4<TY>(dy + (p + stride) * ld + g * 4);
+      const float4 v2 = ld4<TY>(dy + (p + 2 * stride) * ld + g * 4), v3 = ld4<TY>(dy + (p + 3 * stride) * ld + g * 4);
+      acc.x += (v0.x + v1.x) + (v2.x + v3.x); acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+      acc.z += (v0.z + v1.z) + (v2.z + v3.z); acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+    }
+    for (; p < P; p += stride) {
       float4 v = ld4<TY>(dy + p * ld + g * 4);
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
@@ -403,8 +412,8 @@ int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int 
     int ppp = 256 / (C / 4);
     size_t blocks = (npix + ppp - 1) / ppp;
     if (blocks > (size_t)OF_NUM_SMS * 8) blocks = (size_t)OF_NUM_SMS * 8;
-    // every CTA ends with C same-address atomics: give each thread >= 32 pixels so they stay a small share
-    size_t cap = npix / ((size_t)ppp * 32);
+    // every CTA ends with C same-address atomics: give each thread >= 16 pixels so they stay a small share
+    size_t cap = npix / ((size_t)ppp * 16);
     if (cap < 1) cap = 1;
     if (blocks > cap) blocks = cap;
     if (dtype == OF_F32)

@@ -32,10 +32,13 @@
 #define L2F_ROW_FLOATS (L2F_COLS * 6)
 #define L2F_STAGE_BYTES (L2F_ROWS * L2F_COLS * 24)      // 12288: one TMA box {96 floats, 2 segments, 16 rows}
 #define L2F_STAGES 16
+#ifndef L2F_BUILD_WARPS
 #define L2F_BUILD_WARPS 8
+#endif
 #ifndef L2F_GATHER_WARPS
 #define L2F_GATHER_WARPS 17
 #endif
+#define L2F_IMG_BARS 32          // per-image "pyramid complete" mbarriers (image b -> slot b % 32, phase b / 32)
 #define L2F_FIRST_BUILD 3
 #define L2F_FIRST_GATHER (L2F_FIRST_BUILD + L2F_BUILD_WARPS)
 #define L2F_WARPS (L2F_FIRST_GATHER + L2F_GATHER_WARPS)
@@ -79,31 +82,54 @@ __device__ __forceinline__ unsigned ld_acquire_cta_shared(const unsigned* p) {
   return v;
 }
 
+// bounded mbarrier wait: suspends the thread in hardware until the phase completes or ~`ns` have passed
+__device__ __forceinline__ bool mbar_try_wait_ns(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(tc::smem_u32(bar)), "r"(parity), "r"(ns)
+      : "memory");
+  return ok != 0;
+}
+
+// lf_mean4 on two channels at once (sm_100 packed fp32x2: FADD2 / FFMA2, each lane rounds exactly like the scalar
+// FADD / FFMA the compiler emits for lf_mean4, so the texels are bit-identical to loss_fused.cu / loss.cu)
+__device__ __forceinline__ float2 l2f_mean4_2(float2 a, float2 b, float2 c, float2 d) {
+  const float2 h = make_float2(0.5f, 0.5f);
+  const float2 top = __ffma2_rn(__fadd2_rn(b, make_float2(-a.x, -a.y)), h, a);
+  const float2 bot = __ffma2_rn(__fadd2_rn(d, make_float2(-c.x, -c.y)), h, c);
+  return __ffma2_rn(__fadd2_rn(bot, make_float2(-top.x, -top.y)), h, top);
+}
+
 // one resized pixel of BOTH frames from the staged patch: the central 2x2 block whose top-left is (r0, c0).
-// VEC: c0 is even (scale 0), so the 2 pixels x 6 floats are 16-byte aligned.  Same op order as loss_fused.cu.
+// VEC: c0 is even (scale 0), so the 2 pixels x 6 floats are 16-byte aligned.  Channel pairs (0,1) (2,3) (4,5) of the
+// left / right pixel sit in aligned register pairs of the loaded vectors.
 __device__ __forceinline__ void l2f_build_pixel(const bool VEC, const float* T, int r0, int c0, float4* o1, float4* o2) {
   const float* a = T + r0 * L2F_ROW_FLOATS + c0 * 6;
   const float* c = a + L2F_ROW_FLOATS;
-  float ra[12], rc[12];
+  float2 al[3], ar[3], cl[3], cr[3];                 // [channel pair] of the left / right pixel, rows a / c
   if (VEC) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const float4 u = reinterpret_cast<const float4*>(a)[k], v = reinterpret_cast<const float4*>(c)[k];
-      ra[4 * k] = u.x; ra[4 * k + 1] = u.y; ra[4 * k + 2] = u.z; ra[4 * k + 3] = u.w;
-      rc[4 * k] = v.x; rc[4 * k + 1] = v.y; rc[4 * k + 2] = v.z; rc[4 * k + 3] = v.w;
-    }
+    const float4 u0 = reinterpret_cast<const float4*>(a)[0], u1 = reinterpret_cast<const float4*>(a)[1],
+                 u2 = reinterpret_cast<const float4*>(a)[2];
+    const float4 v0 = reinterpret_cast<const float4*>(c)[0], v1 = reinterpret_cast<const float4*>(c)[1],
+                 v2 = reinterpret_cast<const float4*>(c)[2];
+    al[0] = make_float2(u0.x, u0.y); al[1] = make_float2(u0.z, u0.w); al[2] = make_float2(u1.x, u1.y);
+    ar[0] = make_float2(u1.z, u1.w); ar[1] = make_float2(u2.x, u2.y); ar[2] = make_float2(u2.z, u2.w);
+    cl[0] = make_float2(v0.x, v0.y); cl[1] = make_float2(v0.z, v0.w); cl[2] = make_float2(v1.x, v1.y);
+    cr[0] = make_float2(v1.z, v1.w); cr[1] = make_float2(v2.x, v2.y); cr[2] = make_float2(v2.z, v2.w);
   } else {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const float2 u = reinterpret_cast<const float2*>(a)[k], v = reinterpret_cast<const float2*>(c)[k];
-      ra[2 * k] = u.x; ra[2 * k + 1] = u.y;
-      rc[2 * k] = v.x; rc[2 * k + 1] = v.y;
+    for (int k = 0; k < 3; ++k) {
+      al[k] = reinterpret_cast<const float2*>(a)[k]; ar[k] = reinterpret_cast<const float2*>(a)[3 + k];
+      cl[k] = reinterpret_cast<const float2*>(c)[k]; cr[k] = reinterpret_cast<const float2*>(c)[3 + k];
     }
   }
-  *o1 = make_float4(lf_mean4(ra[0], ra[6], rc[0], rc[6]), lf_mean4(ra[1], ra[7], rc[1], rc[7]),
-                    lf_mean4(ra[2], ra[8], rc[2], rc[8]), 0.f);
-  *o2 = make_float4(lf_mean4(ra[3], ra[9], rc[3], rc[9]), lf_mean4(ra[4], ra[10], rc[4], rc[10]),
-                    lf_mean4(ra[5], ra[11], rc[5], rc[11]), 0.f);
+  const float2 m01 = l2f_mean4_2(al[0], ar[0], cl[0], cr[0]);
+  const float2 m23 = l2f_mean4_2(al[1], ar[1], cl[1], cr[1]);
+  const float2 m45 = l2f_mean4_2(al[2], ar[2], cl[2], cr[2]);
+  *o1 = make_float4(m01.x, m01.y, m23.x, 0.f);
+  *o2 = make_float4(m23.y, m45.x, m45.y, 0.f);
 }
 
 // gather tile index -> (image, scale, tile row, tile column)
@@ -241,6 +267,8 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
   __shared__ double s_part[L2F_GATHER_WARPS];
   __shared__ unsigned s_progress[L2F_BUILD_WARPS];   // builder warp w: 1 + index of its latest finished local patch
   __shared__ unsigned s_built;          // images whose pyramid is complete and visible (watcher -> gather warps)
+  __shared__ __align__(8) uint64_t img_bar[L2F_IMG_BARS];   // image b complete: phase b / 32 of slot b % 32 (gather warps
+                                                            // sleep on it in hardware instead of polling s_built)
   __shared__ bool s_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -250,6 +278,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       tc::mbar_init(&empty_bar[s], 1);
     }
     for (int w = 0; w < L2F_BUILD_WARPS; ++w) s_progress[w] = 0u;
+    for (int i = 0; i < L2F_IMG_BARS; ++i) tc::mbar_init(&img_bar[i], 1);
     s_built = 0u;
     tc::fence_barrier_init();
   }
@@ -284,6 +313,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(400);
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
         st_release_cta_shared(&s_built, (unsigned)(b + 1));
+        tc::mbar_arrive(&img_bar[b % L2F_IMG_BARS]);               // wakes the gather warps parked on image b
       }
     }
   } else if (warp == 2) {
@@ -322,56 +352,74 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     // ===================== BUILD =====================
     const int bw = warp - L2F_FIRST_BUILD;
     const uint64_t keep = policy_evict_last();
-    int k = bw;
-    for (int p = blockIdx.x + bw * gridDim.x; p < n_build; p += L2F_BUILD_WARPS * gridDim.x, k += L2F_BUILD_WARPS) {
+    // patch index -> (image b, band, chunk cx) incrementally: the warp's patches are `step` apart
+    const int step = L2F_BUILD_WARPS * (int)gridDim.x;
+    const int bands = P.nb / P.chunks;
+    const int step_b = step / P.nb, step_l = step - step_b * P.nb;
+    const int step_band = step_l / P.chunks, step_cx = step_l - step_band * P.chunks;
+    int p = blockIdx.x + bw * (int)gridDim.x;
+    int b = p / P.nb, band, cx;
+    { const int local = p - b * P.nb; band = local / P.chunks; cx = local - band * P.chunks; }
+    const int ocol0 = lane & 15, or0 = lane >> 4;          // scale 0: 8 x 16 resized pixels, 4 rows per lane
+    const int orow1 = lane >> 3, ocol1 = lane & 7;         // scale 1: 4 x 8, one per lane
+    for (int k = bw; p < n_build; p += step, k += L2F_BUILD_WARPS) {
       const int stage = k % L2F_STAGES;
       const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
-      const int b = p / P.nb, local = p - b * P.nb;
-      const int band = local / P.chunks, cx = local - band * P.chunks;
       const int wc = min(L2F_COLS, P.W - cx * L2F_COLS), hr = min(L2F_ROWS, P.H - band * L2F_ROWS);
+      const bool full = wc == L2F_COLS && hr == L2F_ROWS;  // interior patch: no ragged-edge predicates (warp-uniform)
       if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);
       __syncwarp();
       const float* T = reinterpret_cast<const float*>(tiles + (size_t)stage * L2F_STAGE_BYTES);
       if (!(OF_DBG(P) & 1)) {
-        // scale 0: 8 x 16 resized pixels, 4 per lane, two at a time (independent chains)
+        // scale 0: two pixels at a time (independent chains)
         if (P.ns > 0) {
           const L2fScale& S = P.sc[0];
-          const unsigned base = ((unsigned)b * S.h + band * (L2F_ROWS / 2)) * S.w + cx * (L2F_COLS / 2);
-          const int ocol = lane & 15, or0 = lane >> 4;
+          const unsigned pix0 = ((unsigned)b * S.h + band * (L2F_ROWS / 2) + or0) * S.w + cx * (L2F_COLS / 2) + ocol0;
+          float4* q1 = S.p1 + pix0;
+          float4* q2 = S.p2 + pix0;
+          const unsigned rstep = 2u * (unsigned)S.w;
+          const float* Tl = T + (2 * or0) * L2F_ROW_FLOATS + (2 * ocol0) * 6;
+          if (full) {
 #pragma unroll 2
-          for (int it = 0; it < 4; ++it) {
-            const int orow = or0 + 2 * it;
-            if (ocol * 2 < wc && orow * 2 < hr) {
+            for (int it = 0; it < 4; ++it) {
               float4 o1, o2;
-              l2f_build_pixel(true, T, 2 * orow, 2 * ocol, &o1, &o2);
-              const unsigned pix = base + orow * S.w + ocol;
-              st_f4_policy(S.p1 + pix, o1, keep);
-              st_f4_policy(S.p2 + pix, o2, keep);
+              l2f_build_pixel(true, Tl + it * (4 * L2F_ROW_FLOATS), 0, 0, &o1, &o2);
+              st_f4_policy(q1 + it * rstep, o1, keep);
+              st_f4_policy(q2 + it * rstep, o2, keep);
+            }
+          } else {
+#pragma unroll 2
+            for (int it = 0; it < 4; ++it) {
+              if (ocol0 * 2 < wc && (or0 + 2 * it) * 2 < hr) {
+                float4 o1, o2;
+                l2f_build_pixel(true, Tl + it * (4 * L2F_ROW_FLOATS), 0, 0, &o1, &o2);
+                st_f4_policy(q1 + it * rstep, o1, keep);
+                st_f4_policy(q2 + it * rstep, o2, keep);
+              }
             }
           }
         }
         // scale 1: 4 x 8 pixels, one per lane
         if (P.ns > 1) {
           const L2fScale& S = P.sc[1];
-          const int orow = lane >> 3, ocol = lane & 7;
-          if (ocol * 4 < wc && orow * 4 < hr) {
+          if (full || (ocol1 * 4 < wc && orow1 * 4 < hr)) {
             float4 o1, o2;
-            l2f_build_pixel(false, T, 4 * orow + 1, 4 * ocol + 1, &o1, &o2);
-            const unsigned pix = ((unsigned)b * S.h + band * (L2F_ROWS / 4) + orow) * S.w + cx * (L2F_COLS / 4) + ocol;
+            l2f_build_pixel(false, T, 4 * orow1 + 1, 4 * ocol1 + 1, &o1, &o2);
+            const unsigned pix = ((unsigned)b * S.h + band * (L2F_ROWS / 4) + orow1) * S.w + cx * (L2F_COLS / 4) + ocol1;
             st_f4_policy(S.p1 + pix, o1, keep);
             st_f4_policy(S.p2 + pix, o2, keep);
           }
         }
         // scales 2 and 3 in one pass: lanes 0-7 -> the 2 x 4 pixels of scale 2, lanes 8-9 -> the 1 x 2 of scale 3
         if (P.ns > 2 && lane < 10) {
-          const int s = lane < 8 ? 2 : 3;
-          if (s < P.ns) {
-            const L2fScale& S = P.sc[s];
-            const int bs = 2 << s;
+          const int sidx = lane < 8 ? 2 : 3;
+          if (sidx < P.ns) {
+            const L2fScale& S = P.sc[sidx];
+            const int bs = 2 << sidx;
             const int t = lane < 8 ? lane : lane - 8;
-            const int lc = 4 - s;                                    // log2(columns of this scale per patch)
+            const int lc = 4 - sidx;                                 // log2(columns of this scale per patch)
             const int orow = t >> lc, ocol = t & ((1 << lc) - 1);
-            if (ocol * bs < wc && orow * bs < hr) {
+            if (full || (ocol * bs < wc && orow * bs < hr)) {
               float4 o1, o2;
               l2f_build_pixel(false, T, bs * orow + (bs >> 1) - 1, bs * ocol + (bs >> 1) - 1, &o1, &o2);
               const unsigned pix = ((unsigned)b * S.h + band * (L2F_ROWS / bs) + orow) * S.w + cx * (L2F_COLS / bs) + ocol;
@@ -386,6 +434,10 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         tc::mbar_arrive(&empty_bar[stage]);                        // the ring slot refills
         st_release_cta_shared(&s_progress[bw], (unsigned)(k + 1)); // the publisher follows
       }
+      // next patch of this warp
+      b += step_b; band += step_band; cx += step_cx;
+      if (cx >= P.chunks) { cx -= P.chunks; ++band; }
+      if (band >= bands) { band -= bands; ++b; }
     }
   } else {
     // ===================== GATHER =====================
@@ -403,8 +455,11 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       const float2 f0 = n0, f1 = n1;
       if (u + tgw < total_gather) { nt = l2f_decode(P, u + tgw); l2f_load_flows<MODE>(P, nt, lane, n0, n1); }   // in flight
       if (t.b >= confirmed && !(OF_DBG(P) & 4)) {
+        // s_built is the truth; the mbarrier only parks the warp (images complete in order, so slot b % 32 is in
+        // phase b / 32 or already past it; an early return just re-reads s_built)
         unsigned v;
-        while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
+        while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b)
+          mbar_try_wait_ns(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u, 4000u);
         confirmed = (int)v;
       }
       const L2fScale& S = P.sc[t.s];

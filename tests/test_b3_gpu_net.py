@@ -120,7 +120,10 @@ def test_graph_step_equals_eager_step(cuda, small_case, mode):
     if mode == "fp32":        # same kernels; the scatter atomics of the warp backward reorder fp32 sums run to run, and
         #                       Adam's m / sqrt(v) turns a last-bit gradient change into a visible update change
         assert np.allclose(out[True][0], out[False][0], rtol=1e-6)
-        assert float((upd_e - upd_g).abs().max()) <= 1e-2 * float(upd_e.abs().max())
+        # no max-abs bound over the 4.9 M weights: where a gradient is at rounding-noise level, m / (sqrt(v) + 1e-7)
+        # amplifies a last-bit difference to a few % of lr for that one weight (seen on a driver box: 2.7 % of max)
+        assert float((upd_e - upd_g).norm()) <= 5e-3 * float(upd_e.norm())
+        assert float((upd_e - upd_g).abs().max()) <= 0.25 * float(upd_e.abs().max())
         assert float((upd_e * upd_g).sum() / (upd_e.norm() * upd_g.norm())) > 0.99999
     else:                     # split-K wgrad atomics reorder fp32 sums run to run
         assert np.allclose(out[True][0], out[False][0], rtol=2e-3)
