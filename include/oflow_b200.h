@@ -379,6 +379,17 @@ int of_adam_step_dev(float* param, const float* grad, float* m, float* v, size_t
 size_t of_bn_train_workspace_bytes(int C);
 int of_bn_train_stats(const void* x, const float* shift, float* sum, float* sumsq, size_t npix, int C, int dtype,
                       void* workspace, void* stream);
+/* Allocation-free variant of of_bn_train_stats.  It has no counterpart in the reference and was added:
+ * some callers cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernel, same deterministic result bit for bit, but the per-CTA partials live in a
+ * file-scope `static __device__` array inside the library (2 424 896 bytes, held by every GPU that loads the library
+ * until exit), so the caller passes only inputs and outputs.  Limit: C <= 256 (larger C returns OF_ERR_SHAPE with a
+ * message; use of_bn_train_stats with a caller workspace).  The call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine; the array's device address is looked up once per device (cudaGetSymbolAddress, with
+ * that device current) on the first call.  Every call on a device shares the array: calls that overlap on the GPU
+ * (different streams without an ordering between them) race; calls in stream order are safe. */
+int of_bn_train_stats_static(const void* x, const float* shift, float* sum, float* sumsq, size_t npix, int C, int dtype,
+                             void* stream);
 int of_bn_train_apply(const void* x, const float* sum, const float* sumsq, const float* shift, float count,
                       const float* gamma, const float* beta, float eps, int act, void* y, float* moving_mean,
                       float* moving_var, float momentum, size_t npix, int C, int dtype, void* stream);

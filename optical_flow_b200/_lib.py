@@ -153,6 +153,7 @@ PROTOTYPES = {
     "of_adam_step_dev": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _f, _f, _f, _f, _vp]),
     "of_bn_train_workspace_bytes": (_sz, [_i]),
     "of_bn_train_stats": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _i, _vp, _vp]),
+    "of_bn_train_stats_static": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _i, _vp]),
     "of_bn_train_apply": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _f, _i, _vp, _vp, _vp, _f, _sz, _i, _i, _vp]),
     "of_bn_train_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _sz, _i, _i, _vp, _vp]),
     "of_bn_train_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _i, _i, _vp]),

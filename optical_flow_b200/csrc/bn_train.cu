@@ -234,6 +234,49 @@ extern "C" int of_bn_train_stats(const void* x, const float* shift, float* sum, 
   return of_launch_check("bn_stats_kernel");
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ----
+// Same kernel as of_bn_train_stats, but the per-CTA partials and the ticket live in a file-scope device array, so a
+// caller that cannot call cudaMalloc (CUDA graph capture, tight serving loops) passes only inputs and outputs.  The
+// array is BN_STATIC_BYTES (2.31 MiB, sized for C <= BN_STATIC_MAX_C) and every GPU that loads the library holds it
+// until exit.  In host code `g_bn_static_scratch` is only a stand-in for the symbol: its device address is looked up
+// with cudaGetSymbolAddress once per device (with that device current) and cached.  All calls on a device share the
+// array - calls that overlap on the GPU (two streams) race; the ticket header is cleared on the stream by every call.
+#define BN_STATIC_MAX_C 256
+#define BN_STATIC_BYTES (BN_WS_HDR + (size_t)BN_MAX_GRID * 2 * BN_STATIC_MAX_C * sizeof(float))
+static __device__ __align__(256) unsigned char g_bn_static_scratch[BN_STATIC_BYTES];
+
+#define BN_STATIC_MAX_DEVICES 64
+static void* g_bn_static_addr[BN_STATIC_MAX_DEVICES];   // device address of the array, per device ordinal (0 = not looked up)
+
+extern "C" int of_bn_train_stats_static(const void* x, const float* shift, float* sum, float* sumsq, size_t npix, int C,
+                                        int dtype, void* stream) {
+  OF_REQUIRE(x && sum && sumsq, OF_ERR_ARG, "of_bn_train_stats_static: null pointer");
+  BN_CHECK_DIMS();
+  OF_REQUIRE(C <= BN_STATIC_MAX_C, OF_ERR_SHAPE,
+             "of_bn_train_stats_static: C = %d exceeds the static scratch (C <= %d, %zu bytes); use of_bn_train_stats "
+             "with a caller workspace", C, BN_STATIC_MAX_C, (size_t)BN_STATIC_BYTES);
+  int dev = -1;
+  OF_CUDA(cudaGetDevice(&dev));
+  OF_REQUIRE(dev >= 0 && dev < BN_STATIC_MAX_DEVICES, OF_ERR_ARG, "of_bn_train_stats_static: device ordinal %d", dev);
+  void* base = __atomic_load_n(&g_bn_static_addr[dev], __ATOMIC_ACQUIRE);
+  if (base == nullptr) {                                 // set-up, once per device, with that device current
+    OF_CUDA(cudaGetSymbolAddress(&base, g_bn_static_scratch));
+    OF_REQUIRE(base != nullptr && ((uintptr_t)base & 255) == 0, OF_ERR_STATE,
+               "of_bn_train_stats_static: bad symbol address %p", base);
+    __atomic_store_n(&g_bn_static_addr[dev], base, __ATOMIC_RELEASE);   // same value from any thread
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned* ticket = reinterpret_cast<unsigned*>(base);
+  float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(base) + BN_WS_HDR);
+  OF_CUDA(cudaMemsetAsync(ticket, 0, BN_WS_HDR, st));   // the array keeps the last call's contents: the ticket must start at 0
+  if (dtype == OF_F32)
+    bn_stats_kernel<float><<<bn_grid(npix, C), BN_THREADS, 0, st>>>((const float*)x, shift, sum, sumsq, part, ticket, npix, C);
+  else
+    bn_stats_kernel<__nv_bfloat16><<<bn_grid(npix, C), BN_THREADS, 0, st>>>((const __nv_bfloat16*)x, shift, sum, sumsq, part,
+                                                                            ticket, npix, C);
+  return of_launch_check("bn_stats_kernel");
+}
+
 extern "C" int of_bn_train_apply(const void* x, const float* sum, const float* sumsq, const float* shift, float count,
                                  const float* gamma, const float* beta, float eps, int act, void* y, float* moving_mean,
                                  float* moving_var, float momentum, size_t npix, int C, int dtype, void* stream) {
