@@ -38,6 +38,9 @@
 #ifndef L2F_GATHER_WARPS
 #define L2F_GATHER_WARPS 17
 #endif
+#ifndef L2F_GATHER_WAIT
+#define L2F_GATHER_WAIT 1        // how gather warps wait for an image: 0 poll s_built (nanosleep), 1 park on the image's
+#endif                           // mbarrier with a time hint, 2 lane 0 spins on try_wait (no hint), then __syncwarp
 #define L2F_IMG_BARS 32          // per-image "pyramid complete" mbarriers (image b -> slot b % 32, phase b / 32)
 #define L2F_FIRST_BUILD 3
 #define L2F_FIRST_GATHER (L2F_FIRST_BUILD + L2F_BUILD_WARPS)
@@ -125,9 +128,15 @@ __device__ __forceinline__ void l2f_build_pixel(const bool VEC, const float* T, 
       cl[k] = reinterpret_cast<const float2*>(c)[k]; cr[k] = reinterpret_cast<const float2*>(c)[3 + k];
     }
   }
+#ifdef L2F_SCALAR_BUILD
+  const float2 m01 = make_float2(lf_mean4(al[0].x, ar[0].x, cl[0].x, cr[0].x), lf_mean4(al[0].y, ar[0].y, cl[0].y, cr[0].y));
+  const float2 m23 = make_float2(lf_mean4(al[1].x, ar[1].x, cl[1].x, cr[1].x), lf_mean4(al[1].y, ar[1].y, cl[1].y, cr[1].y));
+  const float2 m45 = make_float2(lf_mean4(al[2].x, ar[2].x, cl[2].x, cr[2].x), lf_mean4(al[2].y, ar[2].y, cl[2].y, cr[2].y));
+#else
   const float2 m01 = l2f_mean4_2(al[0], ar[0], cl[0], cr[0]);
   const float2 m23 = l2f_mean4_2(al[1], ar[1], cl[1], cr[1]);
   const float2 m45 = l2f_mean4_2(al[2], ar[2], cl[2], cr[2]);
+#endif
   *o1 = make_float4(m01.x, m01.y, m23.x, 0.f);
   *o2 = make_float4(m23.y, m45.x, m45.y, 0.f);
 }
@@ -366,7 +375,11 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
       const int stage = k % L2F_STAGES;
       const uint32_t phase = (uint32_t)(k / L2F_STAGES) & 1u;
       const int wc = min(L2F_COLS, P.W - cx * L2F_COLS), hr = min(L2F_ROWS, P.H - band * L2F_ROWS);
+#ifdef L2F_NO_FULL_PATH
+      const bool full = false;
+#else
       const bool full = wc == L2F_COLS && hr == L2F_ROWS;  // interior patch: no ragged-edge predicates (warp-uniform)
+#endif
       if (lane == 0) tc::mbar_wait(&full_bar[stage], phase);
       __syncwarp();
       const float* T = reinterpret_cast<const float*>(tiles + (size_t)stage * L2F_STAGE_BYTES);
@@ -458,8 +471,19 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         // s_built is the truth; the mbarrier only parks the warp (images complete in order, so slot b % 32 is in
         // phase b / 32 or already past it; an early return just re-reads s_built)
         unsigned v;
+#if L2F_GATHER_WAIT == 0
+        while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
+#elif L2F_GATHER_WAIT == 1
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b)
           mbar_try_wait_ns(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u, 4000u);
+#else
+        if (lane == 0)
+          while (ld_acquire_cta_shared(&s_built) <= (unsigned)t.b)
+            mbar_test(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u) ? (void)0 : (void)
+                mbar_try_wait_ns(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u, 200u);
+        __syncwarp();
+        v = ld_acquire_cta_shared(&s_built);
+#endif
         confirmed = (int)v;
       }
       const L2fScale& S = P.sc[t.s];

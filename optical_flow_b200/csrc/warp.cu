@@ -203,6 +203,15 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
     float4 racc[4][VEC == 8 ? 2 : 1];                 // RUN: pending contribution per tap slot
     size_t raddr[4];
     bool rvalid[4] = {false, false, false, false};
+    // the coordinates of a pass are loaded one pass ahead: a pass then waits once (gradient + taps), not twice
+    auto load_coords = [&](int p_, float2& c_) {
+      int b_, i_, j_;
+      const bool ok = RUN ? tile_pixel_run<TJ>(tile, p_, H, W, tiles_x, tiles_y, b_, i_, j_)
+                          : tile_pixel(tile, p_, H, W, tiles_x, tiles_y, b_, i_, j_);
+      c_ = ok ? __ldg(reinterpret_cast<const float2*>(coords) + ((size_t)b_ * H + i_) * W + j_) : make_float2(0.f, 0.f);
+    };
+    float2 c_next;
+    load_coords(grp, c_next);
     for (int p0 = 0; p0 < TILE * TJ; p0 += PIX_PER_PASS) {
       int p = p0 + grp;
       int b, i, j;
@@ -210,7 +219,8 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
       bool valid = RUN ? tile_pixel_run<TJ>(tile, p, H, W, tiles_x, tiles_y, b, i, j)
                        : tile_pixel(tile, p, H, W, tiles_x, tiles_y, b, i, j);
       size_t pix = valid ? ((size_t)b * H + i) * W + j : 0;
-      float2 c = valid ? __ldg(reinterpret_cast<const float2*>(coords) + pix) : make_float2(0.f, 0.f);
+      const float2 c = c_next;
+      if (p0 + PIX_PER_PASS < TILE * TJ) load_coords(p + PIX_PER_PASS, c_next);
       Taps t = make_taps<SRC>(c.x, c.y, valid ? i : 0, valid ? j : 0, H, W);
       float w00 = t.ax * t.ay, w01 = t.ax * t.by, w10 = t.bx * t.ay, w11 = t.bx * t.by;
       size_t boff = (size_t)(valid ? b : 0) * H * W;

@@ -228,8 +228,8 @@ def test_flownet_bn_train_mode_matches_torch(cuda, mode, tol_y, tol_g):
         got = net.store.g[name].detach().cpu().numpy().astype(np.float64).ravel()
         if np.linalg.norm(e) < 1e-5 * biggest:
             # a conv bias in front of a batch-statistics BN has an exactly-zero gradient (the mean is subtracted):
-            # both sides hold rounding noise there
-            assert np.linalg.norm(got) < 1e-3 * biggest, name
+            # both sides hold rounding noise there (bf16: the summed dz carries 2^-9 relative rounding per element)
+            assert np.linalg.norm(got) < max(1e-3, 0.1 * tol_g) * biggest, name
             continue
         rel = float(np.linalg.norm(got - e) / np.linalg.norm(e))
         if rel > worst[1]:
