@@ -35,7 +35,8 @@
 #define LF_FLOW_ROW_BYTES 272   // 32 float2 + 16 B pad (bank spread; keeps 16-byte TMA alignment)
 #define LF_CTAS_PER_SM 2
 #define LF_MAX_GRID (OF_NUM_SMS * 4)
-#define LF_HDR_BYTES 32768   // [0,16K): ticket, per-image counters, per-CTA partials; [16K,32K): generic kernel's header
+#define LF_HDR_BYTES 65536   // [0,16K): ticket, per-image counters, per-CTA partials; [16K,32K): generic kernel's header;
+                             // [32K,64K): loss_fused2.cu's per-CTA relay flags (one 128-byte line per CTA)
 
 struct LfScale {
   const float* flow;

@@ -39,14 +39,16 @@
 #define L2F_GATHER_WARPS 17
 #endif
 #ifndef L2F_GATHER_WAIT
-#define L2F_GATHER_WAIT 1        // how gather warps wait for an image: 0 poll s_built (nanosleep), 1 park on the image's
-#endif                           // mbarrier with a time hint, 2 lane 0 spins on try_wait (no hint), then __syncwarp
+#define L2F_GATHER_WAIT 0        // how gather warps wait for an image: 0 poll s_built (nanosleep); 1 park on the image's
+#endif                           // mbarrier with a time hint (measured 6 us SLOWER at C2: 56.5 vs 50.1 us - late wake-ups)
 #define L2F_IMG_BARS 32          // per-image "pyramid complete" mbarriers (image b -> slot b % 32, phase b / 32)
 #define L2F_FIRST_BUILD 3
 #define L2F_FIRST_GATHER (L2F_FIRST_BUILD + L2F_BUILD_WARPS)
 #define L2F_WARPS (L2F_FIRST_GATHER + L2F_GATHER_WARPS)
 #define L2F_THREADS (L2F_WARPS * 32)
-#define L2F_HDR_BYTES 32768      // same header layout as loss_fused.cu: ticket, per-image counters, per-CTA partials
+#define L2F_FLAGS_OFF 32768      // relay flags: one 128-byte line per CTA in [32 KB, 64 KB) of the header ([16 KB, 32 KB) belongs
+#define L2F_FLAGS_BYTES 32768    // to the generic kernel and loss_fused.cu's partials reach past 12 KB)
+#define L2F_HDR_BYTES 65536      // same header layout as loss_fused.cu: ticket, per-image counters, per-CTA partials
 #define L2F_PUB_BATCH 8          // images one publisher fence can cover
 
 struct L2fScale {
@@ -67,6 +69,7 @@ struct L2fParams {
   unsigned* ticket;      // [0]
   unsigned* done;        // [B] patches built per image
   double* partials;      // [grid]
+  unsigned* flags;       // [grid][32 words = one 128-byte line]: images complete, relayed to CTA c by CTA 0's watcher
   int B, H, W;
   int chunks;            // patches per row of patches
   int nb;                // patches per image
@@ -315,15 +318,49 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
     }
   } else if (warp == 1) {
     // ===================== watcher =====================
-    if (lane == 0 && !(OF_DBG(P) & (4 | 8 | 16))) {
-      for (int b = 0; b < P.B; ++b) {
-        // 148 watchers poll ONE L2 line: keep the rate low (a poll every ~0.4 us per SM) or the slice that owns the
-        // line becomes a hot spot for the image stream that shares it
-        while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(400);
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");
-        st_release_cta_shared(&s_built, (unsigned)(b + 1));
-        tc::mbar_arrive(&img_bar[b % L2F_IMG_BARS]);               // wakes the gather warps parked on image b
+    // Every watcher polls the per-image counters itself (default).  -DL2F_RELAY: only CTA 0's watcher polls them and
+    // relays "image b complete" to one 128-byte flag line per CTA, which that CTA's watcher polls (one poller per line).
+    // Measured at C2: the relay is SLOWER (52.2 vs 50.4 us; skeleton without gather 35.2 vs 29.0 us) - the 5 us the
+    // pollers add over a run without them (24.1 us) is the completion chain's latency at the tail (fence -> counter ->
+    // poll -> fence), not an L2 hot spot, and the relay adds one more hop to that chain.
+    if (!(OF_DBG(P) & (4 | 8 | 16 | 64))) {                     // 64 (with 2): fences and counters on, nobody polls them
+#ifndef L2F_RELAY
+      if (lane == 0)
+        for (int b = 0; b < P.B; ++b) {
+          while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(400);
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          st_release_cta_shared(&s_built, (unsigned)(b + 1));
+          tc::mbar_arrive(&img_bar[b % L2F_IMG_BARS]);
+        }
+#else
+      if (blockIdx.x == 0) {
+        for (int b = 0; b < P.B; ++b) {
+          if (lane == 0) {
+            while (ld_relaxed(&P.done[b]) < (unsigned)P.nb) __nanosleep(100);
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");     // acquire the publishers' releases, release the relay
+          }
+          __syncwarp();
+          for (unsigned c = 1 + lane; c < gridDim.x; c += 32)
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(P.flags + (size_t)c * 32), "r"((unsigned)(b + 1)) : "memory");
+          if (lane == 0) {
+            st_release_cta_shared(&s_built, (unsigned)(b + 1));
+            tc::mbar_arrive(&img_bar[b % L2F_IMG_BARS]);
+          }
+          __syncwarp();
+        }
+      } else if (lane == 0) {
+        const unsigned* flag = P.flags + (size_t)blockIdx.x * 32;
+        for (int b = 0; b < P.B;) {
+          unsigned v;
+          while ((v = ld_relaxed(flag)) <= (unsigned)b) __nanosleep(200);
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          for (; b < (int)v; ++b) {                              // several images may have completed since the last look
+            st_release_cta_shared(&s_built, (unsigned)(b + 1));
+            tc::mbar_arrive(&img_bar[b % L2F_IMG_BARS]);
+          }
+        }
       }
+#endif
     }
   } else if (warp == 2) {
     // ===================== publisher =====================
@@ -473,16 +510,9 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
         unsigned v;
 #if L2F_GATHER_WAIT == 0
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b) __nanosleep(64);
-#elif L2F_GATHER_WAIT == 1
+#else
         while ((v = ld_acquire_cta_shared(&s_built)) <= (unsigned)t.b)
           mbar_try_wait_ns(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u, 4000u);
-#else
-        if (lane == 0)
-          while (ld_acquire_cta_shared(&s_built) <= (unsigned)t.b)
-            mbar_test(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u) ? (void)0 : (void)
-                mbar_try_wait_ns(&img_bar[t.b % L2F_IMG_BARS], (uint32_t)(t.b / L2F_IMG_BARS) & 1u, 200u);
-        __syncwarp();
-        v = ld_acquire_cta_shared(&s_built);
 #endif
         confirmed = (int)v;
       }
@@ -518,6 +548,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
   if (s_last) {
     // every CTA has finished: re-arm the per-image counters and the ticket, add the partials in a fixed order
     for (int b = tid; b < P.B; b += L2F_THREADS) P.done[b] = 0u;
+    for (unsigned c = tid; c < gridDim.x; c += L2F_THREADS) P.flags[(size_t)c * 32] = 0u;
     if (warp == 0) {
       __threadfence();
       double v = 0.0;
@@ -548,7 +579,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
              "workspace and images must be 16-byte aligned");
   P.ticket = reinterpret_cast<unsigned*>(wsb);
   P.done = reinterpret_cast<unsigned*>(wsb + 64);                         // B <= 2048 -> 8 KB
-  P.partials = reinterpret_cast<double*>(wsb + 64 + 2048 * 4);
+  P.partials = reinterpret_cast<double*>(wsb + 64 + 2048 * 4);            // [8256, 12288): up to 504 CTAs
   float4* pyr = reinterpret_cast<float4*>(wsb + L2F_HDR_BYTES);
   const int tile_i = mode == OF_WARP_REF_IJ ? L2fGeom<OF_WARP_REF_IJ>::TI : L2fGeom<OF_WARP_XY>::TI;
   const int tile_j = mode == OF_WARP_REF_IJ ? L2fGeom<OF_WARP_REF_IJ>::TJ : L2fGeom<OF_WARP_XY>::TJ;
@@ -568,6 +599,7 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
   }
   P.ns = num_scales;
   P.loss = loss;
+  P.flags = reinterpret_cast<unsigned*>(wsb + L2F_FLAGS_OFF);
   P.B = B; P.H = H; P.W = W;
   const int bands = (H + L2F_ROWS - 1) / L2F_ROWS;
   P.chunks = (W + L2F_COLS - 1) / L2F_COLS;
@@ -608,7 +640,8 @@ int of_lf2_run(const float* imgs, const float* const* flows, float* const* d_flo
     max_ctas = sms;                                       // one persistent CTA per SM
   }
   int grid = P.total_build < max_ctas ? P.total_build : max_ctas;
-  if (grid > (L2F_HDR_BYTES - 64 - 2048 * 4) / 8) grid = (L2F_HDR_BYTES - 64 - 2048 * 4) / 8;
+  if (grid > L2F_FLAGS_BYTES / 128) grid = L2F_FLAGS_BYTES / 128;
+  if (grid > (16384 - 64 - 2048 * 4) / 8) grid = (16384 - 64 - 2048 * 4) / 8;          // partials stay inside the first 16 KB
   // co-residency is required (gather warps wait on patches built by other CTAs): cooperative launch enforces it
   void* args[2] = {(void*)&P, (void*)&img_map};
   const void* fn = mode == OF_WARP_REF_IJ ? (const void*)loss_ws_kernel<OF_WARP_REF_IJ> : (const void*)loss_ws_kernel<OF_WARP_XY>;
