@@ -205,6 +205,10 @@ def per_gpu_batch(args, world):
 
 def train_config(B, H, W, world, conv_mode, scaling="weak"):
     tag = "configs[2]" if scaling == "weak" else "configs[3], fixed global batch"
+    if (H, W) == (1024, 2048):
+        tag = "configs[4] shape" + ("" if B == 4 else ", batch differs from its 4 per GPU")
+    elif (H, W) != (H_FULL, W_FULL) or (scaling == "weak" and B != B_PER_GPU):
+        tag = "not a BASELINE config"
     return {"workload": "full train step fwd+bwd+Adam, ResNet encoder + cost-volume decoder, batch %d/GPU at %dx%d (%s)" % (B, H, W, tag),
             "global_batch": B * world, "parallelism": "dp%d" % world, "conv_mode": conv_mode,
             "l2": "activations per step (GBs) far exceed the 126 MB L2; 2 rotating input batches"}
