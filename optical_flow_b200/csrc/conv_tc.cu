@@ -253,14 +253,15 @@ __global__ void __launch_bounds__(256) pack_weights_batch_kernel(const of_pack_j
   int j = 0;
   while (j + 1 < njobs && (int)blockIdx.x >= jobs[j + 1].block_begin) ++j;
   const of_pack_job J = jobs[j];
-  const size_t total = (size_t)J.taps * J.rows * J.cols;
-  const size_t e0 = (size_t)((int)blockIdx.x - J.block_begin) * PACK_BLOCK_ELEMS;
+  // 32-bit index arithmetic (a packing has < 2^31 elements; the host checks): the 64-bit divisions were most of this kernel
+  const unsigned total = (unsigned)J.taps * (unsigned)J.rows * (unsigned)J.cols;
+  const unsigned e0 = (unsigned)((int)blockIdx.x - J.block_begin) * PACK_BLOCK_ELEMS;
   __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(J.out);
-  for (size_t e = e0 + threadIdx.x; e < e0 + PACK_BLOCK_ELEMS && e < total; e += 256) {
-    int c = (int)(e % J.cols);
-    size_t r2 = e / J.cols;
-    int r = (int)(r2 % J.rows);
-    int tap = (int)(r2 / J.rows);
+  for (unsigned e = e0 + threadIdx.x; e < e0 + PACK_BLOCK_ELEMS && e < total; e += 256) {
+    const unsigned r2 = e / (unsigned)J.cols;
+    const int c = (int)(e - r2 * (unsigned)J.cols);
+    const int tap = (int)(r2 / (unsigned)J.rows);
+    const int r = (int)(r2 - (unsigned)tap * (unsigned)J.rows);
     int packed_ci = J.transpose ? r : c;
     int co = J.transpose ? c : r;
     int ci = -1;
@@ -468,7 +469,8 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   }
   int grid = P.m_tiles < ctas * OF_NUM_SMS ? P.m_tiles : ctas * OF_NUM_SMS;
   OF_CUDA(of_launch_pdl(conv_tc_kernel, dim3(grid), dim3(TC_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
-  return of_launch_check("conv_tc_kernel");
+  // timeline names: the stem (strided view of the packed image, Cin = 3) is reported apart from the Cin >= 64 layers
+  return of_launch_check(view ? "conv_tc_kernel<stem>" : "conv_tc_kernel");
 }
 
 }  // extern "C"

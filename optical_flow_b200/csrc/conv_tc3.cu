@@ -159,6 +159,16 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             tc::fence_after_sync();
             const uint64_t bdesc = tc::desc_sw128_kmajor(tc::smem_u32(b_ring + (size_t)bs * P.btile_bytes));
             const int tap_row = P.sign > 0 ? kh : 2 - kh;
+            if (OF_DBG(P) & 128) {
+              // timing experiment (profile-hooks build, results are garbage): operands SWAPPED - the weight tile is the
+              // A operand (M = Cout rows), the 256 pixels of the super-tile are ONE N = 256 B operand (the two halves are
+              // contiguous in the slab): half the MMA instructions, each twice as wide
+              const uint32_t idesc_sw = tc::idesc_bf16_f32(P.n_mma <= 64 ? 64 : 128, 256, 0, 0);
+              const uint64_t pdesc = tc::desc_sw128_kmajor(slab + (uint32_t)(tap_row * P.TW * 128));
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc::mma_bf16(d0, bdesc + (uint64_t)(2 * k), pdesc + (uint64_t)(2 * k), idesc_sw, (sl | kh | k) ? 1u : 0u);
+            } else
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
               const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
@@ -507,6 +517,6 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   } else
   if (P.coal) OF_CUDA(of_launch_pdl(conv_tc3_kernel<true>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
-  if (int r = of_launch_check("conv_tc3_kernel")) return r;
+  if (int r = of_launch_check(c->n_valid < 16 ? "conv_tc3_kernel<head>" : "conv_tc3_kernel")) return r;   // Cout = 2 flow heads apart
   return 1;
 }

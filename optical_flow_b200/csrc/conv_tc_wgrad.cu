@@ -483,7 +483,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
   dim3 grid(jobs, splits);
   OF_CUDA(of_launch_pdl(conv_tc_wgrad_kernel, grid, dim3(WG_THREADS), smem, st, tmX[0], tmX[1], tmDY, P));
-  if (int r = of_launch_check("conv_tc_wgrad_kernel")) return r;
+  if (int r = of_launch_check(view ? "conv_tc_wgrad_kernel<stem>" : "conv_tc_wgrad_kernel")) return r;
   return 0;
 }
 
