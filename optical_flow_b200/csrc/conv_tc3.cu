@@ -167,7 +167,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               const uint64_t pdesc = tc::desc_sw128_kmajor(slab + (uint32_t)(tap_row * P.TW * 128));
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                tc::mma_bf16(d0, bdesc + (uint64_t)(2 * k), pdesc + (uint64_t)(2 * k), idesc_sw, (sl | kh | k) ? 1u : 0u);
+                tc::mma_bf16(tmem_base + (uint32_t)(buf * 256), bdesc + (uint64_t)(2 * k), pdesc + (uint64_t)(2 * k), idesc_sw,
+                             (sl | kh | k) ? 1u : 0u);
             } else
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
@@ -472,11 +473,12 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     if (b_ > T3_MAX_B) b_ = T3_MAX_B;
     const char* e = of_tune_env("OF_T3_2CTA");                  // 0 = never, 1 = every layer with n_mma <= 64
     const bool want = e ? (atoi(e) > 0 && c->n_mma <= 64) : (c->n_mma <= 32 || (c->n_mma <= 64 && kch >= 2));
-    if (want && !P.coal && b_ >= 3 && P.m_tiles > OF_NUM_SMS) { two = 1; P.na = 2; P.nb = b_; }
+    if (want && !P.coal && b_ >= 3 && P.m_tiles > OF_NUM_SMS && !(OF_DBG(P) & 128)) { two = 1; P.na = 2; P.nb = b_; }
   }
   if (P.nb < 3) return 0;
   int cols = 4 * c->n_mma;
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+  if (OF_DBG(P) & 128) P.tmem_cols = 512;              // swapped-operand timing hook: two 256-column accumulators
   P.E.out = c->out; P.E.out_dtype = c->out_dtype; P.E.out_stride = c->out_stride;
   P.E.bias = c->bias; P.E.act = c->act;
   P.E.add = c->add; P.E.add_dtype = c->add_dtype; P.E.add_stride = c->add_stride;

