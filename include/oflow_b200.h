@@ -211,6 +211,10 @@ typedef struct {
    * column - out_split) - the dgrad of a conv whose input is a concat writes each segment's gradient tensor from
    * ONE launch (model.py:100-104). */
   void* out2; int out2_stride; int out_split;
+  /* add_mode 0 (default): y = act(conv + bias + add).  add_mode 1 (3x3 / stride-1 layers, bf16 out, Cout %% 16 == 0):
+   * y = relu(act(conv + bias) + add) - resnet/models.py:24-35 applies ReLU to conv2 + BN BEFORE the residual add and
+   * again after it; sign_out (if given) records the INNER activation's sign, which is what conv2's backward needs. */
+  int add_mode;
 } of_tc_conv;
 #define OF_MASK_BITS 2
 int of_conv_tc_run(const of_tc_conv* c, void* stream);
@@ -269,6 +273,9 @@ int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int 
 
 /* dz = dy * act'(y)  (y = stored activation output) */
 int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int dtype, void* stream);
+/* the same from a sign-bit mask (of_tc_conv.sign_out: 16 bytes per pixel, bit c = activated channel c > 0) instead
+ * of the activation tensor: dz[p][c] = dy[p][c] * (bit ? 1 : slope(act)); C %% 8 == 0, C <= 128; dy / dz dtype. */
+int of_act_bwd_bits(const void* bits, const void* dy, void* dz, size_t npix, int C, int act, int dtype, void* stream);
 
 /* ---- glue -------------------------------------------------------------------
  * model.py:122-123,131-132: split (B,H,W,6) into the two frames stacked on the

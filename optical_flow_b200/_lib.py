@@ -43,7 +43,7 @@ class TcConv(C.Structure):
                 ("add", C.c_void_p), ("add_dtype", C.c_int), ("add_stride", C.c_int),
                 ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("mask_stride", C.c_int), ("mask_act", C.c_int),
                 ("sign_out", C.c_void_p),
-                ("out2", C.c_void_p), ("out2_stride", C.c_int), ("out_split", C.c_int)]
+                ("out2", C.c_void_p), ("out2_stride", C.c_int), ("out_split", C.c_int), ("add_mode", C.c_int)]
 
 
 class TcWgrad(C.Structure):
@@ -130,6 +130,7 @@ PROTOTYPES = {
     "of_add_relu_fwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "of_relu_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "of_act_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),
+    "of_act_bwd_bits": (_i, [_vp, _vp, _vp, _sz, _i, _i, _i, _vp]),
     "of_conv2d_fprop": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_conv2d_dgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_conv2d_wgrad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

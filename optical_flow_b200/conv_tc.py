@@ -114,8 +114,10 @@ def pack_weights(w_hwio, segs, rows, cols, transpose, out=None, cache=None):
 
 
 def tc_run(sources, wpacked, n_mma, n_valid, N, H, W, Ho, Wo, KH, KW, stride, pad_t, pad_l, sign, out,
-           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE, sign_out=None, mask_bits=None, out2=None, out_split=0):
+           bias=None, act=L.OF_ACT_NONE, add=None, mask=None, mask_act=L.OF_ACT_NONE, sign_out=None, mask_bits=None, out2=None, out_split=0,
+           add_mode=0):
     d = L.TcConv()
+    d.add_mode = add_mode
     for k, s in enumerate(sources):
         d.src[k] = s.t.data_ptr()
         d.src_c[k] = s.t.shape[-1]
@@ -153,7 +155,7 @@ def sign_bits_ok(ksize, stride, cout):
 
 
 def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torch.bfloat16, add=None, sign_out=None,
-                    cache=None):
+                    cache=None, add_mode=0):
     """Keras Conv2D(padding='same') forward on tensor cores.  x: bf16 tensor or MultiSource."""
     srcs = _sources_of(x)
     N, H, W = srcs[0].t.shape[:3]
@@ -168,7 +170,7 @@ def conv2d_fprop_tc(x, w_hwio, bias, stride=1, act=L.OF_ACT_NONE, out_dtype=torc
     wp = pack_weights(w_hwio, segs, n_mma, kb, transpose=False, cache=cache)
     out = torch.empty((N, Ho, Wo, Cout), dtype=out_dtype, device=w_hwio.device)
     return tc_run(srcs, wp, n_mma, Cout, N, H, W, Ho, Wo, KH, KW, stride, pt, pl, +1, out, bias=bias, act=act, add=add,
-                  sign_out=sign_out)
+                  sign_out=sign_out, add_mode=add_mode)
 
 
 def zero_upsample2(dy, H, W, cache=None, key=None):
@@ -324,7 +326,13 @@ class Bf16Backend:
         self.img_hw = (batch_imgs.shape[1], batch_imgs.shape[2])
         return pack_image_pair8(batch_imgs)
 
-    def fprop(self, layer, x, w, b):
+    def can_post_add(self, layer):
+        """resnet/models.py:24-35 in one launch: relu(relu(bn2(conv2(.))) + shortcut) from the conv's epilogue (the inner
+        activation survives as the sign-bit mask its backward reads)."""
+        return (self.net.fuse_residual_epilogues and layer.act == L.OF_ACT_RELU
+                and sign_bits_ok(layer.k, layer.stride, layer.cout) and layer.cin >= 32)
+
+    def fprop(self, layer, x, w, b, post_add=None):
         if layer.cin < 32:          # conv1 (Cin = 3, 7x7/2): 4-tap (row pair) tensor-core conv over the packed image
             return conv1_fprop_tc(x, self.img_hw[0], self.img_hw[1], w, b, act=layer.act)
         out_dtype = torch.float32 if layer.cout < 16 else torch.bfloat16     # flow heads stay fp32
@@ -332,12 +340,20 @@ class Bf16Backend:
         if layer.act != L.OF_ACT_NONE and sign_bits_ok(layer.k, layer.stride, layer.cout) and layer.cin >= 32:
             t0 = x.sources[0].t if isinstance(x, MultiSource) else x
             layer.ybits = torch.empty((t0.shape[0], t0.shape[1], t0.shape[2], 16), dtype=torch.uint8, device=t0.device)
+        if post_add is not None:
+            assert layer.ybits is not None and self.can_post_add(layer)
+            return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype, sign_out=layer.ybits,
+                                   cache=self.pack_cache, add=post_add, add_mode=1)
         return conv2d_fprop_tc(x, w, b, stride=layer.stride, act=layer.act, out_dtype=out_dtype, sign_out=layer.ybits,
                                cache=self.pack_cache)
 
     def act_bwd(self, layer, y, dy):
         if layer.act == L.OF_ACT_NONE:
             return dy
+        bits = getattr(layer, "ybits", None)
+        if bits is not None and dy.shape[-1] % 8 == 0 and tuple(bits.shape[:3]) == tuple(dy.shape[:3]):
+            return F.act_bwd_bits(bits, dy, layer.act)  # 1/16 of the mask bytes (and all there is after a fused post-add)
+        assert y is not None
         return F.act_bwd(y, dy, layer.act)
 
     def wgrad(self, layer, x, dz, dw, db):

@@ -75,6 +75,7 @@ struct ConvEpi {
   int n_valid;
   void* out2; long long out2_stride; int split;   // split > 0: output columns >= split go to out2 (column - split)
   void* sign_out;      // nullable: 16 bytes per pixel, bit c = (output channel c > 0) - a later dgrad's activation mask
+  int add_post;        // 1: y = relu(act(acc + bias) + add) instead of act(acc + bias + add) (conv_tc3 only)
 };
 #define OF_MASK_BITS 2   // mask_dtype: `mask` is such a sign-bit buffer (conv_tc3 only)
 

@@ -80,7 +80,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 
   if (warp == 4) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x) {
         int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
@@ -106,7 +106,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
   } else if (warp == 5) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 0, 0);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
@@ -391,6 +391,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
                c->KH * c->KW);
   if (int r = of_conv_tc3_try(c, stream)) return r < 0 || r > 1 ? r : 0;    // 3x3 / stride-1 fast path
   OF_REQUIRE(c->out2 == nullptr, OF_ERR_UNSUPPORTED, "split outputs are a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
+  OF_REQUIRE(c->add_mode == 0, OF_ERR_UNSUPPORTED, "add_mode 1 is a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
   OF_REQUIRE(c->sign_out == nullptr && !(c->mask != nullptr && c->mask_dtype == 2), OF_ERR_UNSUPPORTED,
              "sign-bit activation masks are a feature of the 3x3 / stride-1 kernel (Cout <= 128)");
   OF_REQUIRE(c->num_src == 1 || c->num_src == 2, OF_ERR_ARG, "num_src must be 1 or 2");

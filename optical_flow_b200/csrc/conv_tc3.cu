@@ -100,7 +100,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 
   if (warp == 8) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
       for (int tile = blockIdx.x; tile < P.m_tiles; tile += gridDim.x) {
         int tw_i = tile % P.tiles_w; int r = tile / P.tiles_w;
@@ -139,7 +139,9 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     }
   } else if (warp == 9) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // (skipping the all-zero K steps of a 32- / 96-channel source was tried: the extra predicate per MMA in THIS thread's
+    //  instruction stream made every layer 6-15 % slower - the issuing thread is on the critical path)
+    if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 0, 0);
       const int slabs_per_tile = 3 * (P.kchunks[0] + (P.num_src > 1 ? P.kchunks[1] : 0));
       int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
@@ -319,7 +321,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             float v[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c0 + j];
-            if (P.E.add) {
+            if (P.E.add && !P.E.add_post) {
               float t[16];
               unpack16(araw[slot], P.E.add_dtype, t);
 #pragma unroll
@@ -332,6 +334,12 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 #pragma unroll
               for (int j = 0; j < 16; ++j) m16 |= (v[j] > 0.f ? 1u : 0u) << j;
               if (c < 4) sb_lo |= (uint64_t)m16 << (16 * c); else sb_hi |= (uint64_t)m16 << (16 * (c - 4));
+            }
+            if (P.E.add && P.E.add_post) {               // resnet/models.py:30-35: relu(relu(bn2(conv2)) + shortcut)
+              float t[16];
+              unpack16(araw[slot], P.E.add_dtype, t);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + t[j], 0.f);
             }
             if (mask_bits) {
               const uint32_t m16 = (uint32_t)((c < 4 ? mb_lo >> (16 * c) : mb_hi >> (16 * (c - 4))) & 0xffffu);
@@ -485,6 +493,13 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   P.E.mask = c->mask; P.E.mask_dtype = c->mask_dtype; P.E.mask_stride = c->mask_stride; P.E.mask_act = c->mask_act;
   P.E.n_valid = c->n_valid;
   P.E.sign_out = c->sign_out;
+  P.E.add_post = c->add_mode == 1 ? 1 : 0;
+  if (P.E.add_post) {
+    OF_REQUIRE(c->add != nullptr && c->out_dtype == OF_BF16 && (c->n_valid % 16) == 0 && (c->out_stride % 8) == 0 &&
+                   (c->add_stride % 8) == 0 && c->mask == nullptr && c->out2 == nullptr,
+               OF_ERR_UNSUPPORTED, "add_mode 1 needs bf16 output, Cout %% 16 == 0, aligned rows, no mask / split output");
+    P.coal = 0;
+  }
   if (c->out2 != nullptr) {
     OF_REQUIRE(c->out_split > 0 && (c->out_split % 16) == 0 && c->out_split < c->n_valid && (c->n_valid % 16) == 0 &&
                    c->out_dtype == OF_BF16 && (c->out_stride % 8) == 0 && (c->out2_stride % 8) == 0 &&

@@ -113,7 +113,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   const int tx_bytes = a_bytes + (P.nstack ? P.n_chunks * P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
 
   if (warp == 4) {
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0;
       for (int kt = k_begin; kt < k_end; ++kt) {
         int tw_i = kt % P.tiles_w; int r = kt / P.tiles_w;
@@ -168,7 +168,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 1, 1);
       int stage = 0; uint32_t phase = 0;
       for (int kt = k_begin; kt < k_end; ++kt) {

@@ -96,7 +96,7 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
 
   if (warp == 0) {
     // ===================== TMA producer: one feature-row window per step =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x) {
         int b, y, x0; ct_decode(P, tile, b, y, x0);
@@ -113,7 +113,7 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.C, 0, 1);
       int stage = 0; uint32_t phase = 0; int it = 0;
       for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x, ++it) {
@@ -315,7 +315,7 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0; int it = 0;
       for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x, ++it) {
         int b, y, x0; ct_decode(P, tile, b, y, x0);
@@ -335,7 +335,7 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, CT_NB, 0, 0);
       int stage = 0; uint32_t phase = 0; int it = 0; uint32_t step = 0;
       for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x, ++it) {

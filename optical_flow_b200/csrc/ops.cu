@@ -234,6 +234,31 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const T* __restrict__ y, c
   }
 }
 
+// activation derivative from a sign-bit mask (16 B per pixel, bit c = activated channel c > 0): one thread per 8
+// channels of a pixel (16 bytes of bf16 / 32 bytes of fp32), the mask word is a broadcast within the pixel's threads
+template <typename T>
+__global__ void __launch_bounds__(256) act_bwd_bits_kernel(const uint32_t* __restrict__ bits, const T* __restrict__ dy,
+                                                           T* __restrict__ dz, size_t n8, int c8, float slope) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n8; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t pix = e / c8;
+    const int g = (int)(e - pix * c8);                       // group of 8 channels within the pixel
+    const uint32_t m = (__ldg(bits + pix * 4 + (g >> 2)) >> ((g & 3) * 8)) & 0xffu;
+    float v[8];
+    if constexpr (sizeof(T) == 2) ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(dy) + e * 8, v);
+    else {
+      const float4 a = ld4<T>(dy + e * 8), b = ld4<T>(dy + e * 8 + 4);
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] *= ((m >> k) & 1u) ? 1.f : slope;
+    if constexpr (sizeof(T) == 2) st8_bf16(reinterpret_cast<__nv_bfloat16*>(dz) + e * 8, v);
+    else {
+      st4<T>(dz + e * 8, make_float4(v[0], v[1], v[2], v[3]));
+      st4<T>(dz + e * 8 + 4, make_float4(v[4], v[5], v[6], v[7]));
+    }
+  }
+}
+
 // ---- Adam (train.py:34,56; Keras epsilon 1e-7, TF update form) ----------------
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, size_t n,
@@ -399,6 +424,21 @@ int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int d
     act_bwd_kernel<__nv_bfloat16><<<ew_grid(n / 4), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dz, n / 4, act);
   return of_launch_check("act_bwd");
+}
+
+int of_act_bwd_bits(const void* bits, const void* dy, void* dz, size_t npix, int C, int act, int dtype, void* stream) {
+  OF_REQUIRE(bits && dy && dz, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(dtype) && C >= 8 && C <= 128 && C % 8 == 0 && npix > 0, OF_ERR_ARG, "bad dtype / C (C %% 8 == 0, <= 128)");
+  OF_REQUIRE(act >= OF_ACT_NONE && act <= OF_ACT_LEAKY, OF_ERR_ARG, "bad activation %d", act);
+  OF_REQUIRE((((uintptr_t)bits | (uintptr_t)dy | (uintptr_t)dz) & 15) == 0, OF_ERR_ARG, "16-byte alignment");
+  const float slope = act == OF_ACT_RELU ? 0.f : (act == OF_ACT_LEAKY ? 0.3f : 1.f);
+  const size_t n8 = npix * (size_t)(C / 8);
+  if (dtype == OF_F32)
+    act_bwd_bits_kernel<float><<<ew_grid(n8), 256, 0, (cudaStream_t)stream>>>((const uint32_t*)bits, (const float*)dy, (float*)dz, n8, C / 8, slope);
+  else
+    act_bwd_bits_kernel<__nv_bfloat16><<<ew_grid(n8), 256, 0, (cudaStream_t)stream>>>(
+        (const uint32_t*)bits, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dz, n8, C / 8, slope);
+  return of_launch_check("act_bwd_bits");
 }
 
 int of_relu_bwd(const void* out, const void* d_out, void* d, size_t n, int dtype, void* stream) {

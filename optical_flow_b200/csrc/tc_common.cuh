@@ -93,6 +93,21 @@ __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// one lane of a CONVERGED warp (elect.sync): unlike `lane == 0`, the compiler knows that exactly one thread executes
+// the guarded region, so tcgen05 / TMA operands go to uniform registers without a per-instruction waterfall loop
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred)::"memory");
+  return pred != 0;
+}
+// guard of a single-thread warp role (TMA producer, MMA issuer); the warp must be converged where it is evaluated
+#ifdef OF_LANE0_ROLES
+#define OF_ONE_LANE() (lane == 0)
+#else
+#define OF_ONE_LANE() tc::elect_one()
+#endif
 // all previously issued MMAs of this thread arrive on the mbarrier when complete
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))

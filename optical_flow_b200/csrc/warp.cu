@@ -184,8 +184,12 @@ __device__ __forceinline__ float combine_peers(unsigned peers, int rank, int lan
 // RUN tiles are TILE rows x RUN_TJ columns: the longer the walk along j, the longer the runs that merge (in the clamped
 // region one flush per tile instead of one per 16 pixels: 4x fewer atomics on the hot row at RUN_TJ = 64)
 #define RUN_TJ 64
+#ifndef WARP_BWD_MINB
+#define WARP_BWD_MINB 2          // resident CTAs per SM asked of the compiler: 2 = 128 registers (1 lets it take 164 -> ONE CTA per SM: 427 -> 530 us;
+                                 // 3 / 4 spill: 629 / 729 us at level 3 bf16)
+#endif
 template <typename T, int VEC, int TPP, int SRC, typename G = float, bool RUN = false>
-__global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ in,
+__global__ void __launch_bounds__(256, WARP_BWD_MINB) sample_bwd_kernel(const T* __restrict__ in,
                                                          const float* __restrict__ coords,
                                                          const G* __restrict__ d_out,
                                                          float* __restrict__ d_in,
@@ -203,15 +207,6 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
     float4 racc[4][VEC == 8 ? 2 : 1];                 // RUN: pending contribution per tap slot
     size_t raddr[4];
     bool rvalid[4] = {false, false, false, false};
-    // the coordinates of a pass are loaded one pass ahead: a pass then waits once (gradient + taps), not twice
-    auto load_coords = [&](int p_, float2& c_) {
-      int b_, i_, j_;
-      const bool ok = RUN ? tile_pixel_run<TJ>(tile, p_, H, W, tiles_x, tiles_y, b_, i_, j_)
-                          : tile_pixel(tile, p_, H, W, tiles_x, tiles_y, b_, i_, j_);
-      c_ = ok ? __ldg(reinterpret_cast<const float2*>(coords) + ((size_t)b_ * H + i_) * W + j_) : make_float2(0.f, 0.f);
-    };
-    float2 c_next;
-    load_coords(grp, c_next);
     for (int p0 = 0; p0 < TILE * TJ; p0 += PIX_PER_PASS) {
       int p = p0 + grp;
       int b, i, j;
@@ -219,8 +214,8 @@ __global__ void __launch_bounds__(256) sample_bwd_kernel(const T* __restrict__ i
       bool valid = RUN ? tile_pixel_run<TJ>(tile, p, H, W, tiles_x, tiles_y, b, i, j)
                        : tile_pixel(tile, p, H, W, tiles_x, tiles_y, b, i, j);
       size_t pix = valid ? ((size_t)b * H + i) * W + j : 0;
-      const float2 c = c_next;
-      if (p0 + PIX_PER_PASS < TILE * TJ) load_coords(p + PIX_PER_PASS, c_next);
+      // (loading the coordinates one pass ahead was tried in round 2: 427 -> 530 us at level 3 bf16, more live registers)
+      float2 c = valid ? __ldg(reinterpret_cast<const float2*>(coords) + pix) : make_float2(0.f, 0.f);
       Taps t = make_taps<SRC>(c.x, c.y, valid ? i : 0, valid ? j : 0, H, W);
       float w00 = t.ax * t.ay, w01 = t.ax * t.by, w10 = t.bx * t.ay, w11 = t.bx * t.by;
       size_t boff = (size_t)(valid ? b : 0) * H * W;

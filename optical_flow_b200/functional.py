@@ -251,6 +251,17 @@ def act_bwd(y, dy, act, out=None):
     return out
 
 
+def act_bwd_bits(bits, dy, act, out=None):
+    """act_bwd from the 16 B / pixel sign-bit mask a conv fprop left (bits: uint8 (..., 16)); dy (..., C)."""
+    C = dy.shape[-1]
+    assert bits.dtype == torch.uint8 and bits.shape[-1] == 16 and bits.numel() // 16 == dy.numel() // C
+    if out is None:
+        out = torch.empty_like(dy)
+    L.check(L.load().of_act_bwd_bits(L.ptr(bits), L.ptr(dy), L.ptr(out), dy.numel() // C, C, act, L.dtype_code(dy),
+                                     L.stream_ptr()), "of_act_bwd_bits")
+    return out
+
+
 # -------------------------------------------------------------- convolution --
 
 def same_pad(in_size, k, s):

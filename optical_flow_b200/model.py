@@ -18,6 +18,8 @@ Two convolution back-ends share this graph:
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -105,11 +107,17 @@ class ConvLayer:
                                         K, self.cout, L.stream_ptr()), "of_bn_fold_fwd")
         return wf, bf
 
-    def forward(self, x):
+    def forward(self, x, post_add=None):
+        """``post_add`` (back-ends with ``can_post_add``): returns relu(act(conv(x)) + post_add) from the conv's own
+        epilogue (resnet/models.py:24-35); the layer's activation then exists only as its sign-bit mask."""
         self.x = x
         if not self.weights_ready:
             self.w_eff, self.b_eff = self.effective_weights()
         self.weights_ready = False
+        if post_add is not None:
+            assert not (self.bn is not None and self.net.bn_mode == "train")
+            self.y = None
+            return self.net.backend.fprop(self, x, self.w_eff, self.b_eff, post_add=post_add)
         if self.bn is not None and self.net.bn_mode == "train":
             # conv (no activation) -> BatchNormalization(training=True) + activation (resnet/batchnorm.py)
             lin = self._linear_view()
@@ -161,10 +169,13 @@ class ConvLayer:
             return net.backend.dgrad(lin, dz, self.w_eff, in_hw, chain=None, add=add)
         return net.backend.dgrad(lin, dz, self.w_eff, in_hw, chain=None)
 
-    def backward(self, dy, need_dx=True, add=None):
+    def backward(self, dy, need_dx=True, add=None, out_mask=None):
         """dy: gradient w.r.t. the layer output (after activation).  Returns dx or None.
-        ``add`` (back-ends with ``dgrad_can_add``): a tensor summed into dx by the dgrad epilogue."""
+        ``add`` (back-ends with ``dgrad_can_add``): a tensor summed into dx by the dgrad epilogue.
+        ``out_mask``: a post-ReLU tensor shaped like the layer input whose derivative mask the dgrad epilogue applies to
+        dx + add (the producer of the input is not a ConvLayer this layer chains to, e.g. the previous residual block)."""
         net = self.net
+        assert out_mask is None or (self.prev_chain is None and not (self.bn is not None and net.bn_mode == "train"))
         if (need_dx and self.bn is None and self.act == L.OF_ACT_NONE and self.k == 3 and self.stride == 1
                 and self.cout == 2 and self.cin <= 32 and self.use_bias and hasattr(net.backend, "head_bwd")):
             return net.backend.head_bwd(self, dy)     # flow head: dw, db and the chained dz in one pass
@@ -194,16 +205,23 @@ class ConvLayer:
                     "of_bn_fold_bwd")
         if not need_dx:
             return None
+        chain = self._chain() if out_mask is None else _OutMask(out_mask)
         if add is not None:
-            return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self._chain(),
-                                     add=add)
-        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=self._chain())
+            return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=chain, add=add)
+        return net.backend.dgrad(self, dz, self.w_eff, (self.x.shape[1], self.x.shape[2]), chain=chain)
 
     def _chain(self):
         """The producer whose activation derivative this layer's dgrad epilogue may apply - none when the producer's
         activation sits behind a training-mode BatchNormalization layer."""
         c = self.prev_chain
         return None if (c is not None and c.bn is not None and self.net.bn_mode == "train") else c
+
+
+class _OutMask:
+    """Stand-in for a chained producer: a post-ReLU tensor whose derivative mask a dgrad epilogue applies."""
+
+    def __init__(self, y):
+        self.y, self.act, self.ybits, self.incoming_is_dz = y, L.OF_ACT_RELU, None, False
 
 
 class Fp32Backend:
@@ -243,17 +261,27 @@ class ResnetBlock:
 
     def forward(self, x):
         self.x = x
-        y = self.conv2.forward(self.conv1.forward(x))
+        h1 = self.conv1.forward(x)
         sc = self.shortcut.forward(x) if self.down else x
-        self.out = F.add_relu_fwd(y, sc)
+        be = self.net.backend
+        if self.net.bn_mode != "train" and hasattr(be, "can_post_add") and be.can_post_add(self.conv2):
+            self.out = self.conv2.forward(h1, post_add=sc)        # relu(relu(bn2(conv2)) + shortcut) in conv2's epilogue
+        else:
+            self.out = F.add_relu_fwd(self.conv2.forward(h1), sc)
         return self.out
 
-    def backward(self, d_out):
-        d_pre = F.act_bwd(self.out, d_out, L.OF_ACT_RELU)        # relu3
+    def backward(self, d_out, d_is_pre=False, dx_mask=None, skip_add=None):
+        """``d_is_pre``: d_out already carries this block's last ReLU derivative (the next block's dgrad epilogue applied
+        it).  ``dx_mask``: the previous block's output - its ReLU derivative is applied to the returned gradient.
+        ``skip_add`` (downsample blocks): a gradient that reaches the block input from elsewhere (the decoder), summed
+        in by the shortcut's dgrad epilogue."""
+        d_pre = d_out if d_is_pre else F.act_bwd(self.out, d_out, L.OF_ACT_RELU)        # relu3
         d_y1 = self.conv2.backward(d_pre)
-        skip = self.shortcut.backward(d_pre) if self.down else d_pre
+        assert skip_add is None or self.down
+        skip = self.shortcut.backward(d_pre, add=skip_add) if self.down else d_pre
         if getattr(self.net.backend, "dgrad_can_add", False):
-            return self.conv1.backward(d_y1, add=skip)            # residual sum in the dgrad epilogue
+            return self.conv1.backward(d_y1, add=skip, out_mask=dx_mask)   # residual sum (+ mask) in the dgrad epilogue
+        assert dx_mask is None and skip_add is None
         d_x = self.conv1.backward(d_y1)
         _accumulate(d_x, skip)
         return d_x
@@ -291,9 +319,19 @@ class Encoder:
     def backward(self, d_outs):
         """d_outs: gradients w.r.t. the 4 outputs (same dtype as the activations)."""
         d = d_outs[3]
+        # inside a stage the second block's dgrad epilogue also applies the first block's last ReLU derivative
+        fuse = (self.net.fuse_residual_epilogues and self.net.bn_mode != "train"
+                and getattr(self.net.backend, "dgrad_can_add", False))
+        # ... and at a stage boundary the decoder's gradient of the previous stage's output rides the shortcut's dgrad
+        # epilogue, so every block but the last receives its gradient with its own ReLU derivative already applied
+        pre = False
         for k in range(5, -1, -1):
-            d = self.blocks[k].backward(d)
-            if k % 2 == 0 and k > 0:
+            boundary = k % 2 == 0 and k > 0
+            dx_mask = self.blocks[k - 1].out if (fuse and k > 0) else None
+            skip_add = d_outs[k // 2] if (fuse and boundary) else None
+            d = self.blocks[k].backward(d, d_is_pre=pre, dx_mask=dx_mask, skip_add=skip_add)
+            pre = dx_mask is not None
+            if boundary and skip_add is None:
                 _accumulate(d, d_outs[k // 2])       # output of the previous stage also feeds the decoder
         # pool backward + the finest decoder level's gradient + the stem's ReLU derivative, one pass
         dz0 = F.maxpool2_bwd_add_act(self.out0, d, d_outs[0], self.conv1.act)
@@ -368,12 +406,18 @@ class FlowNet:
     [flow3 (H/2), flow2 (H/4), flow1 (H/8), flow0 (H/16)], finest first."""
 
     def __init__(self, height, width, pretrained_weights_path=None, max_disp=3, conv_mode="fp32",
-                 warp_mode="ref_ij", device=None, seed=42, bn_mode="inference", bn_comm=None):
+                 warp_mode="ref_ij", device=None, seed=42, bn_mode="inference", bn_comm=None,
+                 fuse_residual_epilogues=False):
         """bn_mode: "inference" (default = the reference: train.py:51 calls the model without training=True, SURVEY F5;
         BN is folded into the convolutions) or "train" (opt-in, SURVEY 8f rank 4: batch statistics, moving-statistics
         update, cross-replica sums through ``bn_comm`` - anything with world_size and allreduce_sum_)."""
         assert bn_mode in ("inference", "train")
         self.bn_mode, self.bn_comm = bn_mode, bn_comm
+        # bf16 back-end, off by default: the residual blocks' element-wise passes move into conv epilogues - conv2's
+        # epilogue computes relu(relu(.) + shortcut), the dgrad epilogues apply the previous block's ReLU mask and take
+        # the decoder's gradient at stage boundaries.  Measured at C3 (call 20): step 10.27 -> 10.19 ms, but the conv
+        # kernels pay for the extra epilogue operands (conv_tc3 +0.27 ms, the in-step tensor figure 0.51 -> 0.49)
+        self.fuse_residual_epilogues = bool(fuse_residual_epilogues)
         assert torch.cuda.is_available(), "optical_flow_b200 needs a CUDA device (no CPU fallback)"
         assert height % 16 == 0 and width % 16 == 0, "height/width must be multiples of 16 (4 stride-2 stages)"
         L.load()

@@ -185,6 +185,37 @@ def test_tc3_sign_bit_mask(cuda, cfg):
     assert torch.equal(a, bq)
 
 
+@pytest.mark.parametrize("cfg", [(2, 24, 32, 64, 3, 64, 1), (1, 16, 48, 128, 3, 128, 1), (1, 9, 13, 64, 3, 32, 1)])
+def test_tc3_post_add_relu_epilogue(cuda, cfg):
+    """of_tc_conv.add_mode = 1 (resnet/models.py:24-35): y = relu(relu(conv + bias) + add) from one launch; the sign
+    bits record the INNER activation, and of_act_bwd_bits on them equals of_act_bwd on the inner activation."""
+    from optical_flow_b200 import conv_tc, functional as F, _lib as L
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 8)
+    r = np.random.default_rng(9)
+    add = bf16_round(r.standard_normal((N, H, W, Cout)).astype(np.float32))
+    inner = torch.relu(T.conv2d_same(torch.tensor(x), torch.tensor(w), torch.tensor(b), s))
+    ref = torch.relu(inner + torch.tensor(add)).numpy()
+    xd = torch.tensor(x, device=cuda).bfloat16()
+    addd = torch.tensor(add, device=cuda).bfloat16()
+    bits = torch.zeros((N, H, W, 16), dtype=torch.uint8, device=cuda)
+    y = conv_tc.conv2d_fprop_tc(xd, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), act=L.OF_ACT_RELU,
+                                sign_out=bits, add=addd, add_mode=1)
+    assert rel_err(y, ref) <= 2 ** -7, rel_err(y, ref)
+    # the same conv without the post-add gives the inner activation: its sign pattern is what the bits must hold
+    y_in = conv_tc.conv2d_fprop_tc(xd, torch.tensor(w, device=cuda), torch.tensor(b, device=cuda), act=L.OF_ACT_RELU)
+    got = np.unpackbits(bits.cpu().numpy(), axis=-1, bitorder="little")[..., :Cout].astype(bool)
+    assert np.array_equal(got, (y_in.float() > 0).cpu().numpy())
+    # and the fused output is exactly add_relu of the unfused pair (same bf16 rounding of the inner value is NOT applied
+    # in the fused form, so compare within one bf16 ulp of the result)
+    unfused = F.add_relu_fwd(y_in, addd)
+    assert rel_err(y, unfused.float().cpu().numpy()) <= 2 ** -7
+    g = torch.tensor(bf16_round(r.standard_normal((N, H, W, Cout)).astype(np.float32)), device=cuda).bfloat16()
+    assert torch.equal(F.act_bwd_bits(bits, g, L.OF_ACT_RELU), F.act_bwd(y_in, g, L.OF_ACT_RELU))
+    g32 = g.float()
+    assert torch.equal(F.act_bwd_bits(bits, g32, L.OF_ACT_LEAKY), F.act_bwd(y_in.float(), g32, L.OF_ACT_LEAKY))
+
+
 def test_tc_dgrad_split_output_equals_per_segment_launches(cuda):
     """of_tc_conv.out2 / out_split: both concat segments' gradients from one launch == one launch per segment."""
     from optical_flow_b200 import conv_tc, functional as F

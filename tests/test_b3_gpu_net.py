@@ -193,3 +193,55 @@ def test_opt_in_l2_regularizer(cuda, small_case):
             # atomics-free fp32 path: the untouched gradients are reproduced by the second run
             assert np.abs(g1 - g0).max() <= 1e-5 * max(np.abs(g0).max(), 1e-30), n
     assert abs((out[True][0] - out[False][0]) - penalty) <= 1e-4 * penalty + 1e-6
+
+
+def test_residual_epilogue_fusions_equal_separate_passes(cuda, small_case):
+    """FlowNet(fuse_residual_epilogues=True) (bf16 back-end; off by default): conv2's epilogue computes
+    relu(relu(bn2(conv2)) + shortcut) (resnet/models.py:24-35), the dgrad epilogues apply the previous block's ReLU mask
+    and carry the decoder's gradient across stage boundaries.  Against the default (separate add_relu / act_bwd /
+    accumulate passes) on the same weights, at the encoder (no warp index flip or L1 sign flip behind the difference):
+      (1) forward: the four encoder outputs within 2^-6 (the fused form skips one bf16 rounding of the inner activation);
+      (2) backward fusions alone, on the SAME forward tensors (so no ReLU mask can flip): every encoder gradient within
+          1e-2 relative L2 (one bf16 rounding less per fused sum);
+      (3) everything fused vs nothing fused: a loose 0.2 - a one-ulp difference of a stage-3 activation flips ~2^-8 of the
+          ReLU masks on the 4 x 6 stage-4 maps of this small case, and each flip moves a gradient element fully."""
+    from optical_flow_b200.model import FlowNet
+    r = np.random.default_rng(3)
+    imgs = torch.tensor(small_case["imgs"], device=cuda)
+    d_np = None
+
+    def run(fwd_fused, bwd_fused):
+        nonlocal d_np
+        net = FlowNet(small_case["H"], small_case["W"], None, conv_mode="bf16", fuse_residual_epilogues=fwd_fused)
+        net.store.load_numpy(small_case["params"], small_case["stats"])
+        net.B = small_case["B"]
+        net.prepare_weights()
+        outs = net.encoder(net.backend_split(imgs))
+        if d_np is None:
+            d_np = [r.standard_normal(tuple(o.shape)).astype(np.float32) for o in outs]
+        net.store.grad.zero_()
+        net._bn_bwd_deferred = False
+        net.fuse_residual_epilogues = bwd_fused          # the backward fusions are decided at backward time
+        net.encoder.backward([torch.tensor(d, device=cuda).bfloat16() for d in d_np])
+        grads = {n: net.store.g[n].detach().float().cpu().numpy().copy() for n in net.store.specs if not n.startswith("flow")}
+        return [o.float().cpu().numpy() for o in outs], grads
+
+    def worst_rel(ga, gb):
+        worst = ("", 0.0)
+        for name, a in ga.items():
+            rel = float(np.linalg.norm(a - gb[name]) / max(np.linalg.norm(a), 1e-30))
+            if rel > worst[1]:
+                worst = (name, rel)
+        return worst
+
+    o_plain, g_plain = run(False, False)
+    o_bwd, g_bwd = run(False, True)
+    o_all, g_all = run(True, True)
+    for k, (a, b) in enumerate(zip(o_plain, o_all)):
+        assert np.abs(a - b).max() <= 2 ** -6 * np.abs(a).max(), (k, float(np.abs(a - b).max() / np.abs(a).max()))
+    for a, b in zip(o_plain, o_bwd):
+        assert np.array_equal(a, b)
+    w = worst_rel(g_plain, g_bwd)
+    assert w[1] < 1e-2, w
+    w = worst_rel(g_plain, g_all)
+    assert w[1] < 0.2, w
