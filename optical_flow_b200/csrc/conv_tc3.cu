@@ -28,7 +28,7 @@
 #define T3_THREADS 320
 #define T3_EPI_WARPS 8
 #define T3_WSTG_BYTES 4096
-#define T3_MAX_A 3
+#define T3_MAX_A 5
 #define T3_MAX_B 12
 
 int of_tc_make_view_map(CUtensorMap* m, const void* base, int c_used, long long w_stride, long long h_stride,
@@ -38,6 +38,7 @@ int of_tc_make_weight_map(CUtensorMap* m, const void* base, int taps, int rows, 
 struct Conv3Params {
   int num_src;
   int kchunks[2], kbase[2];
+  int klast_slab, klast_n;                 // -DT3_KSKIP: slabs sl with sl % slabs_per_tile >= klast_slab issue klast_n K steps
   int pad_t, pad_l, sign;
   int NB, Ho, Wo;
   int TW, TH, tiles_w, tiles_h, m_tiles;   // super-tile = TW x 2*TH output pixels
@@ -172,6 +173,21 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 tc::mma_bf16(tmem_base + (uint32_t)(buf * 256), bdesc + (uint64_t)(2 * k), pdesc + (uint64_t)(2 * k), idesc_sw,
                              (sl | kh | k) ? 1u : 0u);
             } else
+#pragma unroll
+#ifdef T3_KSKIP
+            // the LAST 64-channel chunk of a single-source layer whose channel count is 32 or 96 (mod 64) holds zeros in
+            // its upper K steps (TMA zero fill): a separate, equally unrolled path issues only the real ones
+            if (sl >= P.klast_slab) {
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh) {
+                const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                  tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                               (sl | kh | k) ? 1u : 0u);
+              }
+            } else
+#endif
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
               const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
@@ -422,6 +438,9 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     kb += P.kchunks[s] * 64;
   }
   OF_REQUIRE(kb <= c->k_pad, OF_ERR_SHAPE, "packed K %d smaller than the sources' %d", c->k_pad, kb);
+  // (T3_KSKIP) single source whose last chunk holds exactly 32 real channels: its 3 slabs (kw) issue 2 K steps
+  P.klast_slab = 1 << 30; P.klast_n = 4;
+  if (c->num_src == 1 && c->src_c[0] - (P.kchunks[0] - 1) * 64 <= 32) { P.klast_slab = 3 * (P.kchunks[0] - 1); P.klast_n = 2; }
   P.pad_t = c->pad_t; P.pad_l = c->pad_l; P.sign = c->sign >= 0 ? 1 : -1;
   P.NB = c->N; P.Ho = c->Ho; P.Wo = c->Wo;
   // narrow tiles keep the halo overhead (2*TH + 2) / (2*TH) small; TW must be a multiple of 8 rows
@@ -480,7 +499,11 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     int b_ = (100 * 1024 - stg_bytes - 2 * P.slab_bytes) / P.btile_bytes;
     if (b_ > T3_MAX_B) b_ = T3_MAX_B;
     const char* e = of_tune_env("OF_T3_2CTA");                  // 0 = never, 1 = every layer with n_mma <= 64
-    const bool want = e ? (atoi(e) > 0 && c->n_mma <= 64) : (c->n_mma <= 32 || (c->n_mma <= 64 && kch >= 2));
+    // (round 2, after the elect.sync issuer: the multi-chunk n_mma <= 64 layers are faster with ONE CTA - 96->64 at N8
+    //  192x640 139 vs 145 us, at 96x320 40.4 vs 45.8 us - so only n_mma <= 32 takes two; ring depths 2..5 x 3..12 move
+    //  no layer by more than 3 %, scripts/gpu_r2_run19.sh)
+    const bool want = e ? (atoi(e) > 0 && c->n_mma <= 64) : (c->n_mma <= 32);
+    (void)kch;
     if (want && !P.coal && b_ >= 3 && P.m_tiles > OF_NUM_SMS && !(OF_DBG(P) & 128)) { two = 1; P.na = 2; P.nb = b_; }
   }
   if (P.nb < 3) return 0;

@@ -301,7 +301,7 @@ loss_ws_kernel(const __grid_constant__ L2fParams P, const __grid_constant__ CUte
   float acc = 0.f;
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (OF_ONE_LANE()) {
       tc::prefetch_tmap(&img_map);
       const uint64_t pol = policy_evict_first();
       int k = 0;

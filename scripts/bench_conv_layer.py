@@ -24,6 +24,10 @@ def run(N, H, W, Cin, Cout, iters=20):
     fl = 2.0 * N * H * W * Cin * Cout * 9
     print("N%d %dx%d %d->%d: %.1f us  %.0f TFLOP/s" % (N, H, W, Cin, Cout, us, fl / us / 1e6))
 if __name__ == "__main__":
+    for opt in ("OF_T3_RINGS", "OF_T3_2CTA"):          # ring depths "na,nb" / two CTAs per SM policy, through of_set_option
+        if os.environ.get("X_" + opt):
+            L.check(L.load().of_set_option(opt.encode(), os.environ["X_" + opt].encode()), "of_set_option")
+            print("option", opt, os.environ["X_" + opt])
     shapes = ((128, 128), (128, 96), (96, 64), (64, 32), (32, 64), (64, 64))
     if os.environ.get("OF_CONV_SHAPES") == "pow2":      # the swapped-operand timing hook over-reads a 96-row weight tile
         shapes = ((128, 128), (128, 64), (64, 64), (64, 32), (32, 64))
