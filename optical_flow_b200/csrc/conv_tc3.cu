@@ -54,7 +54,14 @@ struct Conv3Params {
 
 // MINB = 2: two CTAs per SM (narrow layers, <= 256 TMEM columns and half the rings each): the second CTA's TMA
 // stream and MMAs fill the first one's bubbles
-template <bool COAL, int MINB = 1>
+// SPEC >= 0: the epilogue's options are COMPILE-TIME constants (bit field below) - the run-time-flagged epilogue spent
+// 37 uniform branches per 16-column chunk and the eight epilogue warps were busy for the whole kernel (ncu, round 2:
+// 83 % of the warp samples in epilogue code, tensor pipe 61 % active at 128->128); the host picks a specialisation when
+// the launch matches one and falls back to SPEC = -1 otherwise.
+//   bits 0-1 activation, bit 2 pre-activation add (bf16), bit 3 sign_out, bits 4-5 mask kind (1 = sign bits),
+//   bits 6-7 mask activation, bit 8 split output;  always: bf16 output, full 16-channel chunks, 32-byte aligned rows
+#define T3_SPEC(act, add, sign, mkind, mact, split) ((act) | ((add) << 2) | ((sign) << 3) | ((mkind) << 4) | ((mact) << 6) | ((split) << 8))
+template <bool COAL, int MINB = 1, int SPEC = -1>
 __global__ void __launch_bounds__(T3_THREADS, MINB)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ Conv3Params P) {
@@ -256,6 +263,69 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 
       tc::mbar_wait(&tmem_full[buf], use & 1);
       tc::fence_after_sync();
+      if constexpr (SPEC >= 0) {
+        constexpr int ACT = SPEC & 3, MACT = (SPEC >> 6) & 3;
+        constexpr bool ADD = (SPEC >> 2) & 1, SIGN = (SPEC >> 3) & 1, MBITS = ((SPEC >> 4) & 3) == 1, SPLIT = (SPEC >> 8) & 1;
+        uint32_t rr[2][16];
+        uint4 araw[2][2];
+        const int nchunks = P.n_mma >> 4;
+        const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(P.E.add) + pix * P.E.add_stride;
+        auto issue = [&](int c, int slot) {
+          __syncwarp();                                  // tcgen05.ld is .sync.aligned: reconverge first
+          tc::tmem_ld16(taddr + (uint32_t)(c * 16), rr[slot]);
+          if (ADD && valid) ld_global_256(addp + c * 16, araw[slot][0], araw[slot][1]);
+        };
+        auto finish = [&](int c, int slot) {
+          __syncwarp();
+          tc::tmem_ld_wait();
+          if (c + 1 < nchunks) issue(c + 1, slot ^ 1);
+          if (!valid) return;
+          const int c0 = c * 16;
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c0 + j];
+          if (ADD) {
+            float t[16];
+            const uint4 a4[4] = {araw[slot][0], araw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            unpack16(a4, OF_BF16, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] += t[j];
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], ACT);
+          if (SIGN) {
+            uint32_t m16 = 0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) m16 |= (v[j] > 0.f ? 1u : 0u) << j;
+            if (c < 4) sb_lo |= (uint64_t)m16 << (16 * c); else sb_hi |= (uint64_t)m16 << (16 * (c - 4));
+          }
+          if (MBITS) {
+            const uint32_t m16 = (uint32_t)((c < 4 ? mb_lo >> (16 * c) : mb_hi >> (16 * (c - 4))) & 0xffffu);
+            constexpr float s0 = MACT == OF_ACT_RELU ? 0.f : (MACT == OF_ACT_LEAKY ? 0.3f : 1.f);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] *= ((m16 >> j) & 1u) ? 1.f : s0;
+          }
+          uint32_t pk[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            pk[j] = *reinterpret_cast<uint32_t*>(&t2);
+          }
+          __nv_bfloat16* o = (SPLIT && c0 >= P.E.split)
+                                 ? reinterpret_cast<__nv_bfloat16*>(P.E.out2) + pix * P.E.out2_stride + (c0 - P.E.split)
+                                 : reinterpret_cast<__nv_bfloat16*>(P.E.out) + pix * P.E.out_stride + c0;
+          st_global_256(o, pk);
+        };
+        issue(0, 0);
+#pragma unroll 1
+        for (int c = 0; c < nchunks; c += 2) {
+          finish(c, 0);
+          if (c + 1 < nchunks) finish(c + 1, 1);
+        }
+        if (SIGN && valid)
+          reinterpret_cast<uint4*>(P.E.sign_out)[pix] = make_uint4((uint32_t)sb_lo, (uint32_t)(sb_lo >> 32), (uint32_t)sb_hi,
+                                                                    (uint32_t)(sb_hi >> 32));
+      } else
       if (!(OF_DBG(P) & 2)) {
         // software pipeline over 16-column chunks: the TMEM load of chunk c+1 and the global loads of
         // its add (and row-wise mask) operands are in flight while chunk c is finished
@@ -543,20 +613,47 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
 
   size_t smem = 1024 + (size_t)P.na * P.slab_bytes + (size_t)P.nb * P.btile_bytes + stg_bytes +
                 (2 * T3_MAX_A + 2 * T3_MAX_B + 4) * sizeof(uint64_t) + 16;
+  // compile-time epilogue specialisations the train step uses (anything else runs the run-time-flagged epilogue)
+  constexpr int S_FL = T3_SPEC(OF_ACT_LEAKY, 0, 1, 0, 0, 0), S_FR = T3_SPEC(OF_ACT_RELU, 0, 1, 0, 0, 0);   // fprop + sign bits
+  constexpr int S_DML = T3_SPEC(0, 0, 0, 1, OF_ACT_LEAKY, 0), S_DMR = T3_SPEC(0, 0, 0, 1, OF_ACT_RELU, 0);  // dgrad * act'(bits)
+  constexpr int S_DA = T3_SPEC(0, 1, 0, 0, 0, 0), S_D0 = T3_SPEC(0, 0, 0, 0, 0, 0), S_DS = T3_SPEC(0, 0, 0, 0, 0, 1);
+  int spec = -1;
+  if (!P.coal && !P.E.add_post && P.dbg == 0 && c->out_dtype == OF_BF16 && c->n_valid == c->n_mma && (c->out_stride % 16) == 0 &&
+      ((uintptr_t)c->out & 31) == 0 &&
+      (c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 16) == 0 && ((uintptr_t)c->add & 31) == 0)) &&
+      (c->mask == nullptr || c->mask_dtype == OF_MASK_BITS) &&
+      (c->out2 == nullptr || ((c->out2_stride % 16) == 0 && ((uintptr_t)c->out2 & 31) == 0 && (c->out_split % 16) == 0)) &&
+      !of_tune_env("OF_T3_NO_SPEC"))
+    spec = T3_SPEC(c->act, c->add != nullptr ? 1 : 0, c->sign_out != nullptr ? 1 : 0, c->mask != nullptr ? 1 : 0,
+                   c->mask != nullptr ? c->mask_act : 0, c->out2 != nullptr ? 1 : 0);
   static bool attr_set = false;
   if (!attr_set) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, S_FL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+#define T3_ATTR(S) OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
+    T3_ATTR(S_FL); T3_ATTR(S_FR); T3_ATTR(S_DML); T3_ATTR(S_DMR); T3_ATTR(S_DA); T3_ATTR(S_D0); T3_ATTR(S_DS);
+#undef T3_ATTR
     attr_set = true;
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
+#define T3_GO(MINB_, S) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, MINB_, S>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P))
   if (two) {
     grid = P.m_tiles < 2 * OF_NUM_SMS ? P.m_tiles : 2 * OF_NUM_SMS;
-    OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+    if (spec == S_FL) T3_GO(2, S_FL);
+    else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   } else
   if (P.coal) OF_CUDA(of_launch_pdl(conv_tc3_kernel<true>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+  else if (spec == S_FL) T3_GO(1, S_FL);
+  else if (spec == S_FR) T3_GO(1, S_FR);
+  else if (spec == S_DML) T3_GO(1, S_DML);
+  else if (spec == S_DMR) T3_GO(1, S_DMR);
+  else if (spec == S_DA) T3_GO(1, S_DA);
+  else if (spec == S_D0) T3_GO(1, S_D0);
+  else if (spec == S_DS) T3_GO(1, S_DS);
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+#undef T3_GO
   if (int r = of_launch_check(c->n_valid < 16 ? "conv_tc3_kernel<head>" : "conv_tc3_kernel")) return r;   // Cout = 2 flow heads apart
   return 1;
 }

@@ -164,6 +164,14 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
 #pragma unroll
           for (int q = 0; q < 28; ++q) w[q] = 0;
         }
+        // the NEXT tile's row of this thread (one 128-byte line) into L1 now: its loads, issued when the 7 steps below
+        // are done, were a full L2 round trip at the head of every tile (ncu: 12 % of the kernel in that wait)
+        const int nt = tile + (int)gridDim.x;
+        if (nt < P.ntiles) {
+          int nb_, ny_, nx0_; ct_decode(P, nt, nb_, ny_, nx0_);
+          if (nx0_ + tb < P.W)
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(P.d_cv + (((size_t)nb_ * P.H + ny_) * P.W + nx0_ + tb) * P.cv_stride));
+        }
       } else {
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
