@@ -40,6 +40,10 @@ struct ConvTcParams {
   const void* mask; int mask_dtype; long long mask_stride; int mask_act;
 };
 
+// SPEC >= 0: compile-time epilogue (same reason as conv_tc3_kernel's): bits 0-1 activation, bit 2 add (bf16), bit 3 mask
+// (bf16 tensor), bits 4-5 mask activation; always bf16 output, n_valid == n_mma, 32-byte aligned rows, bias from shared memory
+#define TC_SPEC(act, add, mask, mact) ((act) | ((add) << 2) | ((mask) << 3) | ((mact) << 4))
+template <int SPEC = -1>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvTcParams P) {
@@ -71,6 +75,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   }
   if (threadIdx.x == 0) OF_PDL_TRIGGER();
   OF_PDL_WAIT();                                     // nothing above touches global memory
+  __shared__ float s_bias[256];
+  if (SPEC >= 0)
+    for (int i = threadIdx.x; i < 256; i += TC_THREADS) s_bias[i] = (P.bias && i < P.n_valid) ? P.bias[i] : 0.f;
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -149,6 +156,60 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       tc::mbar_wait(&tmem_full[buf], use & 1);
       tc::fence_after_sync();
       uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * P.n_mma);
+      if constexpr (SPEC >= 0) {
+        constexpr int ACT = SPEC & 3, MACT = (SPEC >> 4) & 3;
+        constexpr bool ADD = (SPEC >> 2) & 1, MASK = (SPEC >> 3) & 1;
+        const int nchunks = P.n_mma >> 4;
+        uint32_t rr[2][16];
+        uint4 araw[2][2], mraw[2][2];
+        const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(P.add) + pix * P.add_stride;
+        const __nv_bfloat16* maskp = reinterpret_cast<const __nv_bfloat16*>(P.mask) + pix * P.mask_stride;
+        __nv_bfloat16* outp = reinterpret_cast<__nv_bfloat16*>(P.out) + pix * P.out_stride;
+        auto issue = [&](int c, int slot) {
+          __syncwarp();
+          tc::tmem_ld16(taddr + (uint32_t)(c * 16), rr[slot]);
+          if (ADD && valid) ld_global_256(addp + c * 16, araw[slot][0], araw[slot][1]);
+          if (MASK && valid) ld_global_256(maskp + c * 16, mraw[slot][0], mraw[slot][1]);
+        };
+        auto finish = [&](int c, int slot) {
+          __syncwarp();
+          tc::tmem_ld_wait();
+          if (c + 1 < nchunks) issue(c + 1, slot ^ 1);
+          if (!valid) return;
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c * 16 + j];
+          if (ADD) {
+            float t[16];
+            const uint4 a4[4] = {araw[slot][0], araw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            unpack16(a4, OF_BF16, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] += t[j];
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], ACT);
+          if (MASK) {
+            float t[16];
+            const uint4 m4[4] = {mraw[slot][0], mraw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            unpack16(m4, OF_BF16, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], MACT);
+          }
+          uint32_t pk[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            pk[j] = *reinterpret_cast<uint32_t*>(&t2);
+          }
+          st_global_256(outp + c * 16, pk);
+        };
+        issue(0, 0);
+#pragma unroll 1
+        for (int c = 0; c < nchunks; c += 2) {
+          finish(c, 0);
+          if (c + 1 < nchunks) finish(c + 1, 1);
+        }
+      } else
       for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
         __syncwarp();                                   // tcgen05.ld is .sync.aligned: reconverge first
         uint32_t rr[16];
@@ -463,13 +524,31 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   if (int r = of_tc_make_weight_map(&tmB, c->wpacked, P.taps, c->n_rows, c->k_pad, c->n_mma)) return r;
 
   size_t smem = 1024 + (size_t)P.stages * stage_bytes + (2 * MAX_STAGES + 4) * sizeof(uint64_t) + 16;
+  constexpr int G_R = TC_SPEC(OF_ACT_RELU, 0, 0, 0), G_0 = TC_SPEC(0, 0, 0, 0), G_A = TC_SPEC(0, 1, 0, 0),
+                G_MR = TC_SPEC(0, 0, 1, OF_ACT_RELU);
+  int spec = -1;
+  if (c->out_dtype == OF_BF16 && c->n_valid == c->n_mma && (c->out_stride % 16) == 0 && ((uintptr_t)c->out & 31) == 0 &&
+      (c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 16) == 0 && ((uintptr_t)c->add & 31) == 0)) &&
+      (c->mask == nullptr || (c->mask_dtype == OF_BF16 && (c->mask_stride % 16) == 0 && ((uintptr_t)c->mask & 31) == 0)) &&
+      !(c->add != nullptr && c->mask != nullptr) && !of_tune_env("OF_TC_NO_SPEC"))
+    spec = TC_SPEC(c->act, c->add != nullptr ? 1 : 0, c->mask != nullptr ? 1 : 0, c->mask != nullptr ? c->mask_act : 0);
   static bool attr_set = false;
   if (!attr_set) {
-    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_A>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_MR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
     attr_set = true;
   }
   int grid = P.m_tiles < ctas * OF_NUM_SMS ? P.m_tiles : ctas * OF_NUM_SMS;
-  OF_CUDA(of_launch_pdl(conv_tc_kernel, dim3(grid), dim3(TC_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+#define TC_GO(S) OF_CUDA(of_launch_pdl(conv_tc_kernel<S>, dim3(grid), dim3(TC_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P))
+  if (spec == G_R) TC_GO(G_R);
+  else if (spec == G_0) TC_GO(G_0);
+  else if (spec == G_A) TC_GO(G_A);
+  else if (spec == G_MR) TC_GO(G_MR);
+  else TC_GO(-1);
+#undef TC_GO
   // timeline names: the stem (strided view of the packed image, Cin = 3) is reported apart from the Cin >= 64 layers
   return of_launch_check(view ? "conv_tc_kernel<stem>" : "conv_tc_kernel");
 }

@@ -76,7 +76,7 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&g_full[s], 128); tc::mbar_init(&empty[s], 1); }
+    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&g_full[s], 4); tc::mbar_init(&empty[s], 1); }
     for (int k = 0; k < 2; ++k) { tc::mbar_init(&tmem_full[k], 1); tc::mbar_init(&tmem_empty[k], 4); }
     tc::fence_barrier_init();
   }
@@ -200,7 +200,10 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
       }
 #pragma unroll
       for (int i = 0; i < 7; ++i) {
-        tc::mbar_wait(&empty[stage], phase ^ 1);
+        // one waiter and one arrival per builder warp (128 threads spinning on try_wait and 128 arrivals per step were
+        // a visible part of the step: the builders, not the MMAs, pace this kernel)
+        if (lane == 0) tc::mbar_wait(&empty[stage], phase ^ 1);
+        __syncwarp();
         uint8_t* G = base + (size_t)stage * P.stage_bytes;
         if (P.from_f2) {
 #pragma unroll
@@ -224,7 +227,8 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
           }
         }
         tc::fence_proxy_async();                                    // generic-proxy stores -> visible to the MMA
-        tc::mbar_arrive(&g_full[stage]);
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&g_full[stage]);
         if (++stage == P.stages) { stage = 0; phase ^= 1; }
       }
     }

@@ -68,7 +68,8 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
           for (int rr = 0; rr < 3; ++rr) c2[rr] = cn[k][rr];
           const float xv = xin[k];
           const float2 xv2 = make_float2(xv, xv);
-          float2 d2 = make_float2(0.f, 0.f);
+          // three independent partial sums (one per kh): a single 9-deep FFMA2 chain per pixel was the walk's critical path
+          float2 d2k[3] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
           // tap (kh,kw) pairs with dy[q - (kh-1, kw-1)] = window[row 2-kh][col 2-kw]
 #pragma unroll
           for (int kh = 0; kh < 3; ++kh) {
@@ -78,10 +79,10 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
               const float2 g = wc[2 - kw];
               const int t = kh * 3 + kw;
               acc[t] = __ffma2_rn(xv2, g, acc[t]);
-              d2 = __ffma2_rn(wr[t], g, d2);
+              d2k[kh] = __ffma2_rn(wr[t], g, d2k[kh]);
             }
           }
-          const float d = d2.x + d2.y;
+          const float d = ((d2k[0].x + d2k[1].x) + d2k[2].x) + ((d2k[0].y + d2k[1].y) + d2k[2].y);
           bsum[0] += c1[1].x; bsum[1] += c1[1].y;
           if (dz != nullptr && ch_ok) {
             float slope = 1.f;
