@@ -269,6 +269,8 @@ def main():
                     help="train workload: replay the whole step from one CUDA graph (Trainer.enable_graph) or launch eagerly")
     ap.add_argument("--dump-timeline", default=None, metavar="PATH",
                     help="train workload: write the per-launch records (kernel, us, FLOPs) of the timeline pass as JSON")
+    ap.add_argument("--no-fuse-residual", action="store_true",
+                    help="FlowNet(fuse_residual_epilogues=False): separate add_relu / act_bwd / accumulate launches (A/B)")
     ap.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
                     help="kernel-variant option passed to of_set_option (A/B runs; recorded in config.options)")
     args = ap.parse_args()
@@ -644,7 +646,7 @@ def bench_train(args, dev, world, rank):
     if world > 1:
         from optical_flow_b200 import parallel
         comm = parallel.CAbiComm.from_torch_dist(dev)          # the library's own NCCL communicator
-    tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm)
+    tr = Trainer(H, W, None, conv_mode=args.conv_mode, comm=comm, fuse_residual_epilogues=not args.no_fuse_residual)
     nsets = 2
     batches = [synthetic_batch(B, H, W, 1234 + rank * 100 + k, dev) for k in range(nsets)]
     launch_mode = "eager (one ctypes call per kernel)"

@@ -525,12 +525,12 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
 
   size_t smem = 1024 + (size_t)P.stages * stage_bytes + (2 * MAX_STAGES + 4) * sizeof(uint64_t) + 16;
   constexpr int G_R = TC_SPEC(OF_ACT_RELU, 0, 0, 0), G_0 = TC_SPEC(0, 0, 0, 0), G_A = TC_SPEC(0, 1, 0, 0),
-                G_MR = TC_SPEC(0, 0, 1, OF_ACT_RELU);
+                G_MR = TC_SPEC(0, 0, 1, OF_ACT_RELU), G_AMR = TC_SPEC(0, 1, 1, OF_ACT_RELU);
   int spec = -1;
   if (c->out_dtype == OF_BF16 && c->n_valid == c->n_mma && (c->out_stride % 16) == 0 && ((uintptr_t)c->out & 31) == 0 &&
       (c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 16) == 0 && ((uintptr_t)c->add & 31) == 0)) &&
       (c->mask == nullptr || (c->mask_dtype == OF_BF16 && (c->mask_stride % 16) == 0 && ((uintptr_t)c->mask & 31) == 0)) &&
-      !(c->add != nullptr && c->mask != nullptr) && !of_tune_env("OF_TC_NO_SPEC"))
+      !of_tune_env("OF_TC_NO_SPEC"))
     spec = TC_SPEC(c->act, c->add != nullptr ? 1 : 0, c->mask != nullptr ? 1 : 0, c->mask != nullptr ? c->mask_act : 0);
   static bool attr_set = false;
   if (!attr_set) {
@@ -539,6 +539,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
     OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_A>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
     OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_MR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));   // + 1 KB static (bias)
+    OF_CUDA(cudaFuncSetAttribute(conv_tc_kernel<G_AMR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
   int grid = P.m_tiles < ctas * OF_NUM_SMS ? P.m_tiles : ctas * OF_NUM_SMS;
@@ -547,6 +548,7 @@ int of_conv_tc_run(const of_tc_conv* c, void* stream) {
   else if (spec == G_0) TC_GO(G_0);
   else if (spec == G_A) TC_GO(G_A);
   else if (spec == G_MR) TC_GO(G_MR);
+  else if (spec == G_AMR) TC_GO(G_AMR);
   else TC_GO(-1);
 #undef TC_GO
   // timeline names: the stem (strided view of the packed image, Cin = 3) is reported apart from the Cin >= 64 layers

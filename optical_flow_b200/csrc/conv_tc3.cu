@@ -58,9 +58,11 @@ struct Conv3Params {
 // 37 uniform branches per 16-column chunk and the eight epilogue warps were busy for the whole kernel (ncu, round 2:
 // 83 % of the warp samples in epilogue code, tensor pipe 61 % active at 128->128); the host picks a specialisation when
 // the launch matches one and falls back to SPEC = -1 otherwise.
-//   bits 0-1 activation, bit 2 pre-activation add (bf16), bit 3 sign_out, bits 4-5 mask kind (1 = sign bits),
-//   bits 6-7 mask activation, bit 8 split output;  always: bf16 output, full 16-channel chunks, 32-byte aligned rows
+//   bits 0-1 activation, bit 2 add (bf16), bit 3 sign_out, bits 4-5 mask kind (1 = sign bits, 2 = bf16 tensor),
+//   bits 6-7 mask activation, bit 8 split output, bit 9 the add comes AFTER the activation and is followed by ReLU
+//   (add_mode 1);  always: bf16 output, full 16-channel chunks, 32-byte aligned rows
 #define T3_SPEC(act, add, sign, mkind, mact, split) ((act) | ((add) << 2) | ((sign) << 3) | ((mkind) << 4) | ((mact) << 6) | ((split) << 8))
+#define T3_SPEC_POST (1 << 9)
 template <bool COAL, int MINB = 1, int SPEC = -1>
 __global__ void __launch_bounds__(T3_THREADS, MINB)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -266,14 +268,17 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       if constexpr (SPEC >= 0) {
         constexpr int ACT = SPEC & 3, MACT = (SPEC >> 6) & 3;
         constexpr bool ADD = (SPEC >> 2) & 1, SIGN = (SPEC >> 3) & 1, MBITS = ((SPEC >> 4) & 3) == 1, SPLIT = (SPEC >> 8) & 1;
+        constexpr bool MTEN = ((SPEC >> 4) & 3) == 2, POST = (SPEC >> 9) & 1;
         uint32_t rr[2][16];
-        uint4 araw[2][2];
+        uint4 araw[2][2], mraw[2][2];
         const int nchunks = P.n_mma >> 4;
         const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(P.E.add) + pix * P.E.add_stride;
+        const __nv_bfloat16* maskp = reinterpret_cast<const __nv_bfloat16*>(P.E.mask) + pix * P.E.mask_stride;
         auto issue = [&](int c, int slot) {
           __syncwarp();                                  // tcgen05.ld is .sync.aligned: reconverge first
           tc::tmem_ld16(taddr + (uint32_t)(c * 16), rr[slot]);
           if (ADD && valid) ld_global_256(addp + c * 16, araw[slot][0], araw[slot][1]);
+          if (MTEN && valid) ld_global_256(maskp + c * 16, mraw[slot][0], mraw[slot][1]);
         };
         auto finish = [&](int c, int slot) {
           __syncwarp();
@@ -284,12 +289,14 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
           float v[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rr[slot][j]) + s_bias[c0 + j];
+          float ta[16];
           if (ADD) {
-            float t[16];
             const uint4 a4[4] = {araw[slot][0], araw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-            unpack16(a4, OF_BF16, t);
+            unpack16(a4, OF_BF16, ta);
+          }
+          if (ADD && !POST) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] += t[j];
+            for (int j = 0; j < 16; ++j) v[j] += ta[j];
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) v[j] = apply_act(v[j], ACT);
@@ -298,6 +305,17 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 16; ++j) m16 |= (v[j] > 0.f ? 1u : 0u) << j;
             if (c < 4) sb_lo |= (uint64_t)m16 << (16 * c); else sb_hi |= (uint64_t)m16 << (16 * (c - 4));
+          }
+          if (ADD && POST) {                             // resnet/models.py:30-35: relu(relu(bn2(conv2)) + shortcut)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + ta[j], 0.f);
+          }
+          if (MTEN) {
+            float t[16];
+            const uint4 m4[4] = {mraw[slot][0], mraw[slot][1], make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            unpack16(m4, OF_BF16, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] *= act_slope(t[j], MACT);
           }
           if (MBITS) {
             const uint32_t m16 = (uint32_t)((c < 4 ? mb_lo >> (16 * c) : mb_hi >> (16 * (c - 4))) & 0xffffu);
@@ -617,15 +635,19 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   constexpr int S_FL = T3_SPEC(OF_ACT_LEAKY, 0, 1, 0, 0, 0), S_FR = T3_SPEC(OF_ACT_RELU, 0, 1, 0, 0, 0);   // fprop + sign bits
   constexpr int S_DML = T3_SPEC(0, 0, 0, 1, OF_ACT_LEAKY, 0), S_DMR = T3_SPEC(0, 0, 0, 1, OF_ACT_RELU, 0);  // dgrad * act'(bits)
   constexpr int S_DA = T3_SPEC(0, 1, 0, 0, 0, 0), S_D0 = T3_SPEC(0, 0, 0, 0, 0, 0), S_DS = T3_SPEC(0, 0, 0, 0, 0, 1);
+  constexpr int S_FRP = T3_SPEC(OF_ACT_RELU, 1, 1, 0, 0, 0) | T3_SPEC_POST;      // conv2 + shortcut + ReLU (fuse_residual_epilogues)
+  constexpr int S_DAMR = T3_SPEC(0, 1, 0, 2, OF_ACT_RELU, 0);                   // dgrad + skip, * relu'(previous block's output)
   int spec = -1;
-  if (!P.coal && !P.E.add_post && P.dbg == 0 && c->out_dtype == OF_BF16 && c->n_valid == c->n_mma && (c->out_stride % 16) == 0 &&
+  if (!P.coal && P.dbg == 0 && c->out_dtype == OF_BF16 && c->n_valid == c->n_mma && (c->out_stride % 16) == 0 &&
       ((uintptr_t)c->out & 31) == 0 &&
       (c->add == nullptr || (c->add_dtype == OF_BF16 && (c->add_stride % 16) == 0 && ((uintptr_t)c->add & 31) == 0)) &&
-      (c->mask == nullptr || c->mask_dtype == OF_MASK_BITS) &&
+      (c->mask == nullptr || c->mask_dtype == OF_MASK_BITS ||
+       (c->mask_dtype == OF_BF16 && (c->mask_stride % 16) == 0 && ((uintptr_t)c->mask & 31) == 0)) &&
       (c->out2 == nullptr || ((c->out2_stride % 16) == 0 && ((uintptr_t)c->out2 & 31) == 0 && (c->out_split % 16) == 0)) &&
       !of_tune_env("OF_T3_NO_SPEC"))
-    spec = T3_SPEC(c->act, c->add != nullptr ? 1 : 0, c->sign_out != nullptr ? 1 : 0, c->mask != nullptr ? 1 : 0,
-                   c->mask != nullptr ? c->mask_act : 0, c->out2 != nullptr ? 1 : 0);
+    spec = T3_SPEC(c->act, c->add != nullptr ? 1 : 0, c->sign_out != nullptr ? 1 : 0,
+                   c->mask == nullptr ? 0 : (c->mask_dtype == OF_MASK_BITS ? 1 : 2), c->mask != nullptr ? c->mask_act : 0,
+                   c->out2 != nullptr ? 1 : 0) | (P.E.add_post ? T3_SPEC_POST : 0);
   static bool attr_set = false;
   if (!attr_set) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
@@ -634,6 +656,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, S_FL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
 #define T3_ATTR(S) OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
     T3_ATTR(S_FL); T3_ATTR(S_FR); T3_ATTR(S_DML); T3_ATTR(S_DMR); T3_ATTR(S_DA); T3_ATTR(S_D0); T3_ATTR(S_DS);
+    T3_ATTR(S_FRP); T3_ATTR(S_DAMR);
 #undef T3_ATTR
     attr_set = true;
   }
@@ -652,6 +675,8 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   else if (spec == S_DA) T3_GO(1, S_DA);
   else if (spec == S_D0) T3_GO(1, S_D0);
   else if (spec == S_DS) T3_GO(1, S_DS);
+  else if (spec == S_FRP) T3_GO(1, S_FRP);
+  else if (spec == S_DAMR) T3_GO(1, S_DAMR);
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
 #undef T3_GO
   if (int r = of_launch_check(c->n_valid < 16 ? "conv_tc3_kernel<head>" : "conv_tc3_kernel")) return r;   // Cout = 2 flow heads apart

@@ -76,7 +76,7 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&g_full[s], 4); tc::mbar_init(&empty[s], 1); }
+    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&g_full[s], 128); tc::mbar_init(&empty[s], 1); }
     for (int k = 0; k < 2; ++k) { tc::mbar_init(&tmem_full[k], 1); tc::mbar_init(&tmem_empty[k], 4); }
     tc::fence_barrier_init();
   }
@@ -164,14 +164,6 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
 #pragma unroll
           for (int q = 0; q < 28; ++q) w[q] = 0;
         }
-        // the NEXT tile's row of this thread (one 128-byte line) into L1 now: its loads, issued when the 7 steps below
-        // are done, were a full L2 round trip at the head of every tile (ncu: 12 % of the kernel in that wait)
-        const int nt = tile + (int)gridDim.x;
-        if (nt < P.ntiles) {
-          int nb_, ny_, nx0_; ct_decode(P, nt, nb_, ny_, nx0_);
-          if (nx0_ + tb < P.W)
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(P.d_cv + (((size_t)nb_ * P.H + ny_) * P.W + nx0_ + tb) * P.cv_stride));
-        }
       } else {
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
@@ -200,10 +192,9 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
       }
 #pragma unroll
       for (int i = 0; i < 7; ++i) {
-        // one waiter and one arrival per builder warp (128 threads spinning on try_wait and 128 arrivals per step were
-        // a visible part of the step: the builders, not the MMAs, pace this kernel)
-        if (lane == 0) tc::mbar_wait(&empty[stage], phase ^ 1);
-        __syncwarp();
+        // (one waiter + one arrival per builder warp instead of 128 was tried in round 2: d_f1 355 -> 451 us, d_f2 481 ->
+        //  578 us - the extra __syncwarp pair per step costs more than the spinning it saves)
+        tc::mbar_wait(&empty[stage], phase ^ 1);
         uint8_t* G = base + (size_t)stage * P.stage_bytes;
         if (P.from_f2) {
 #pragma unroll
@@ -227,8 +218,7 @@ cvtc_bwd_kernel(const __grid_constant__ CUtensorMap tmF, const __grid_constant__
           }
         }
         tc::fence_proxy_async();                                    // generic-proxy stores -> visible to the MMA
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&g_full[stage]);
+        tc::mbar_arrive(&g_full[stage]);
         if (++stage == P.stages) { stage = 0; phase ^= 1; }
       }
     }

@@ -407,16 +407,17 @@ class FlowNet:
 
     def __init__(self, height, width, pretrained_weights_path=None, max_disp=3, conv_mode="fp32",
                  warp_mode="ref_ij", device=None, seed=42, bn_mode="inference", bn_comm=None,
-                 fuse_residual_epilogues=False):
+                 fuse_residual_epilogues=True):
         """bn_mode: "inference" (default = the reference: train.py:51 calls the model without training=True, SURVEY F5;
         BN is folded into the convolutions) or "train" (opt-in, SURVEY 8f rank 4: batch statistics, moving-statistics
         update, cross-replica sums through ``bn_comm`` - anything with world_size and allreduce_sum_)."""
         assert bn_mode in ("inference", "train")
         self.bn_mode, self.bn_comm = bn_mode, bn_comm
-        # bf16 back-end, off by default: the residual blocks' element-wise passes move into conv epilogues - conv2's
-        # epilogue computes relu(relu(.) + shortcut), the dgrad epilogues apply the previous block's ReLU mask and take
-        # the decoder's gradient at stage boundaries.  Measured at C3 (call 20): step 10.27 -> 10.19 ms, but the conv
-        # kernels pay for the extra epilogue operands (conv_tc3 +0.27 ms, the in-step tensor figure 0.51 -> 0.49)
+        # bf16 back-end: the residual blocks' element-wise passes move into conv epilogues - conv2's epilogue computes
+        # relu(relu(.) + shortcut), the dgrad epilogues apply the previous block's ReLU mask and take the decoder's
+        # gradient at stage boundaries.  With the run-time-flagged epilogue this was a wash (call 20: step 10.27 -> 10.19 ms,
+        # conv_tc3 +0.27 ms); with its own compile-time specialisations (call 32, same box) 9.17 -> 8.98 ms, the conv
+        # kernels paying 0.14 ms for 0.32 ms of removed element-wise launches - on by default
         self.fuse_residual_epilogues = bool(fuse_residual_epilogues)
         assert torch.cuda.is_available(), "optical_flow_b200 needs a CUDA device (no CPU fallback)"
         assert height % 16 == 0 and width % 16 == 0, "height/width must be multiples of 16 (4 stride-2 stages)"

@@ -37,7 +37,7 @@ def regularized_parameters(specs):
 class Trainer:
     def __init__(self, height=img_height, width=img_width, pretrained_weights_path=None, lr=learning_rate,
                  conv_mode="bf16", warp_mode="ref_ij", comm=None, seed=42, apply_l2=False, l2_reg=1e-4,
-                 bn_mode="inference"):
+                 bn_mode="inference", fuse_residual_epilogues=True):
         """``comm``: None (single replica) or a parallel.CAbiComm / parallel.TorchDistComm; every
         replica must be built with the same ``seed`` so the weights start identical.
         ``apply_l2`` (opt-in, default off = the reference's behaviour): add the L2 penalty the reference
@@ -47,7 +47,8 @@ class Trainer:
         batch statistics (old/train.py:59 ``training=True`` semantics) with cross-replica sums over ``comm``."""
         self.flow_net = build_flow_net(height, width, pretrained_weights_path, conv_mode=conv_mode,
                                        warp_mode=warp_mode, seed=seed, bn_mode=bn_mode,
-                                       bn_comm=comm if bn_mode == "train" else None)
+                                       bn_comm=comm if bn_mode == "train" else None,
+                                       fuse_residual_epilogues=fuse_residual_epilogues)
         self.loss_layer = LossLayer(warp_mode=warp_mode)
         self._lr = float(lr)
         self.step = 0

@@ -196,7 +196,7 @@ def test_opt_in_l2_regularizer(cuda, small_case):
 
 
 def test_residual_epilogue_fusions_equal_separate_passes(cuda, small_case):
-    """FlowNet(fuse_residual_epilogues=True) (bf16 back-end; off by default): conv2's epilogue computes
+    """FlowNet(fuse_residual_epilogues=True) (bf16 back-end; the default since the epilogues are compile-time specialised): conv2's epilogue computes
     relu(relu(bn2(conv2)) + shortcut) (resnet/models.py:24-35), the dgrad epilogues apply the previous block's ReLU mask
     and carry the decoder's gradient across stage boundaries.  Against the default (separate add_relu / act_bwd /
     accumulate passes) on the same weights, at the encoder (no warp index flip or L1 sign flip behind the difference):
