@@ -635,6 +635,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   constexpr int S_FL = T3_SPEC(OF_ACT_LEAKY, 0, 1, 0, 0, 0), S_FR = T3_SPEC(OF_ACT_RELU, 0, 1, 0, 0, 0);   // fprop + sign bits
   constexpr int S_DML = T3_SPEC(0, 0, 0, 1, OF_ACT_LEAKY, 0), S_DMR = T3_SPEC(0, 0, 0, 1, OF_ACT_RELU, 0);  // dgrad * act'(bits)
   constexpr int S_DA = T3_SPEC(0, 1, 0, 0, 0, 0), S_D0 = T3_SPEC(0, 0, 0, 0, 0, 0), S_DS = T3_SPEC(0, 0, 0, 0, 0, 1);
+  constexpr int S_FL0 = T3_SPEC(OF_ACT_LEAKY, 0, 0, 0, 0, 0), S_FR0 = T3_SPEC(OF_ACT_RELU, 0, 0, 0, 0, 0);   // fprop, no sign bits
   constexpr int S_FRP = T3_SPEC(OF_ACT_RELU, 1, 1, 0, 0, 0) | T3_SPEC_POST;      // conv2 + shortcut + ReLU (fuse_residual_epilogues)
   constexpr int S_DAMR = T3_SPEC(0, 1, 0, 2, OF_ACT_RELU, 0);                   // dgrad + skip, * relu'(previous block's output)
   int spec = -1;
@@ -656,7 +657,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, S_FL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
 #define T3_ATTR(S) OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
     T3_ATTR(S_FL); T3_ATTR(S_FR); T3_ATTR(S_DML); T3_ATTR(S_DMR); T3_ATTR(S_DA); T3_ATTR(S_D0); T3_ATTR(S_DS);
-    T3_ATTR(S_FRP); T3_ATTR(S_DAMR);
+    T3_ATTR(S_FRP); T3_ATTR(S_DAMR); T3_ATTR(S_FL0); T3_ATTR(S_FR0);
 #undef T3_ATTR
     attr_set = true;
   }
@@ -675,6 +676,8 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   else if (spec == S_DA) T3_GO(1, S_DA);
   else if (spec == S_D0) T3_GO(1, S_D0);
   else if (spec == S_DS) T3_GO(1, S_DS);
+  else if (spec == S_FL0) T3_GO(1, S_FL0);
+  else if (spec == S_FR0) T3_GO(1, S_FR0);
   else if (spec == S_FRP) T3_GO(1, S_FRP);
   else if (spec == S_DAMR) T3_GO(1, S_DAMR);
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));

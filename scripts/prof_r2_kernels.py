@@ -11,8 +11,10 @@ def conv_case(N, H, W, Cin, Cout):
     w = torch.randn((3, 3, Cin, Cout), device=dev) * 0.05
     b = torch.randn((Cout,), device=dev)
     dz = torch.randn((N, H, W, Cout), device=dev).bfloat16()
+    bits = torch.zeros((N, H, W, 16), dtype=torch.uint8, device=dev)
     for _ in range(2):
-        conv_tc.conv2d_fprop_tc(x, w, b, act=L.OF_ACT_LEAKY)
+        conv_tc.conv2d_fprop_tc(x, w, b, act=L.OF_ACT_LEAKY, sign_out=bits)     # as the train step launches it
+        conv_tc.conv2d_dgrad_tc(dz, w, (H, W), 1, mask_bits=bits, mask_act=L.OF_ACT_LEAKY)
         conv_tc.conv2d_wgrad_tc(x, dz, (3, 3))
     torch.cuda.synchronize()
 
