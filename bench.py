@@ -762,7 +762,7 @@ def bench_train(args, dev, world, rank):
             # best single layer, timed alone (burst peak): decoder level-3 128 -> 128
             dom = time_dominant_conv(torch, dev, B, H // 2, W // 2, 128, 128, iters=max(args.steps, 10))
             traffic = None                               # DRAM bytes per launch of that kernel, from the committed ncu capture
-            tpath = os.path.join(ROOT, "profiles", "r01_roofline_traffic.json")
+            tpath = os.path.join(ROOT, "profiles", "r02_roofline_traffic.json")
             if (B, H, W) == (8, 384, 1280) and os.path.exists(tpath):
                 traffic = json.load(open(tpath))["conv_tc3_fprop_N8_192x640_128_128"]["traffic_bytes"]
             roof["traffic"] = traffic
