@@ -38,7 +38,7 @@ struct WgradParams {
   int job_mt[WG_MAX_JOBS], job_tap0[WG_MAX_JOBS], job_ntaps[WG_MAX_JOBS];
   int KW, pad_t, pad_l, stride_w, stride_h;
   int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
-  int ktiles, ktiles_per_split;
+  int ktiles, ktiles_per_split, kt_step;
   int n_mma, n_valid, n_chunks;   // dy: MMA N, real Cout, 64-channel chunks
   int Cin, Cout;
   int stages, stage_bytes, tmem_cols;
@@ -86,8 +86,15 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     tc::fence_barrier_init();
   }
   if (warp == 4 && lane == 0) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
-  // the bias gradient of a pixel range is computed by ONE of its jobs, rotating so the extra MMAs spread over the SMs
-  const bool do_bias = P.db != nullptr && blockIdx.x == (blockIdx.y % gridDim.x);
+  // the bias gradient of a K tile is computed by ONE of the jobs that walk it, rotating PER K TILE: every CTA carries
+  // 1 / jobs of the extra MMAs.  (Rotating per pixel range gave a third of the CTAs all of them: with one wave the
+  // kernel ends with its slowest CTA - ncu, 128->128: SM active cycles avg 342k, max 461k.)
+  const bool do_bias = P.db != nullptr;
+#ifdef WG_BIAS_PER_RANGE
+#define WG_BIAS_NOW(it_) (blockIdx.x == (blockIdx.y % gridDim.x))
+#else
+#define WG_BIAS_NOW(it_) ((((it_) + (int)blockIdx.y) % (int)gridDim.x) == (int)blockIdx.x)
+#endif
   if (do_bias) {
     // bf16 1.0 = 0x3f80; all-ones is invariant under the 128-byte swizzle
     for (int i = threadIdx.x; i < WG_ONES_BYTES / 16; i += WG_THREADS)
@@ -106,8 +113,12 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   // scheduled together, so x and dy come from HBM once and from L2 for the other jobs
   const int job = blockIdx.x;
   const int mt = P.job_mt[job], tap0 = P.job_tap0[job], ntaps = P.job_ntaps[job];
-  const int k_begin = blockIdx.y * P.ktiles_per_split;
-  const int k_end = min(P.ktiles, k_begin + P.ktiles_per_split);
+  // split-K ranges: contiguous by default; P.kt_step > 1 = INTERLEAVED (split s walks K tiles s, s + splits, ...), so
+  // every CTA's pixels are spread over the whole tensor (both dies' memory) instead of one contiguous 1/splits of it -
+  // ncu showed equal-work CTAs finishing 35 % apart with contiguous ranges (SM active min / avg / max 0 / 342k / 461k cycles)
+  const int kt_step = P.kt_step;
+  const int k_begin = kt_step > 1 ? (int)blockIdx.y : blockIdx.y * P.ktiles_per_split;
+  const int k_end = kt_step > 1 ? P.ktiles : min(P.ktiles, k_begin + P.ktiles_per_split);
   const int a_bytes = P.nstack ? (P.nstack_one ? (P.one_split ? (tap0 == 0 ? 2 : 1) : 3) : 2) * WG_CHUNK_BYTES
                       : P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : ntaps * 2 * WG_CHUNK_BYTES;
   const int tx_bytes = a_bytes + (P.nstack ? P.n_chunks * P.slab_bytes : P.n_chunks * WG_CHUNK_BYTES);
@@ -115,7 +126,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   if (warp == 4) {
     if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0;
-      for (int kt = k_begin; kt < k_end; ++kt) {
+      for (int kt = k_begin; kt < k_end; kt += kt_step) {
         int tw_i = kt % P.tiles_w; int r = kt / P.tiles_w;
         int th_i = r % P.tiles_h; int n = r / P.tiles_h;
         int w0 = tw_i * P.TW, h0 = th_i * P.TH;
@@ -171,7 +182,9 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 1, 1);
       int stage = 0; uint32_t phase = 0;
-      for (int kt = k_begin; kt < k_end; ++kt) {
+      int it = 0; bool bias_acc = false;
+      for (int kt = k_begin; kt < k_end; kt += kt_step, ++it) {
+        const bool bias_now = do_bias && WG_BIAS_NOW(it);
         tc::mbar_wait(&full_bar[stage], phase);
         tc::fence_after_sync();
         uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
@@ -189,7 +202,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
                              (kt > k_begin || k > 0) ? 1u : 0u);
               }
             }
-          if (do_bias) {
+          if (bias_now) {
             // kh = 1 (one row into the slab) is dy unshifted; the chunks are one slab apart
             const uint32_t idesc_b = tc::idesc_bf16_f32(128, P.n_chunks * 64, 1, 1);
             const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
@@ -197,8 +210,9 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             for (int k = 0; k < 4; ++k) {
               uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + row + k * 2048, (uint32_t)P.slab_bytes);
               tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_chunks * 192), odesc, bdesc, idesc_b,
-                           (kt > k_begin || k > 0) ? 1u : 0u);
+                           (bias_acc || k > 0) ? 1u : 0u);
             }
+            bias_acc = true;
           }
           tc::mma_commit(&empty_bar[stage]);
           if (++stage == P.stages) { stage = 0; phase ^= 1; }
@@ -222,13 +236,14 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
           }
         }
-        if (do_bias) {
+        if (bias_now) {
           const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
-            tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma), odesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
+            tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma), odesc, bdesc, idesc, (bias_acc || k > 0) ? 1u : 0u);
           }
+          bias_acc = true;
         }
         tc::mma_commit(&empty_bar[stage]);
         if (++stage == P.stages) { stage = 0; phase ^= 1; }
@@ -304,7 +319,13 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
           }
         }
       }
-      if (do_bias && warp == 0) {
+      // did this CTA run any bias tile?  (iterations it = 0 .. n_it - 1; the first one with WG_BIAS_NOW)
+      bool had_bias = false;
+      if (do_bias) {
+        const int n_it = (k_end - k_begin + kt_step - 1) / kt_step;
+        for (int i = 0; i < n_it && i < (int)gridDim.x; ++i) had_bias = had_bias || WG_BIAS_NOW(i);
+      }
+      if (had_bias && warp == 0) {
         // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
         uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? P.n_chunks * 192 : P.n_mma));
         for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
@@ -469,6 +490,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (splits < 1) splits = 1;
   P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
+  P.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : splits;     // interleaved K tiles (every split has >= 1 tile: splits <= ktiles)
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
   if (P.nstack) P.stage_bytes = ((P.nstack_one && !P.one_split) ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
