@@ -263,10 +263,18 @@ __global__ void __launch_bounds__(256, WARP_BWD_MINB) sample_bwd_kernel(const T*
             // bf16 features and bf16 incoming gradient, 16-byte accesses: 8 threads per 64-channel pixel
             float g[8], v00[8], v01[8], v10[8], v11[8];
             ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(d_out) + pix * C + ch, g);
+            // both taps of a column on ONE source row (y0 == y1: the clamped region, ~70 % of a 192 x 640 level under
+            // model.py:65-71's row / column swap): two loads and two scatter slots instead of four
+            const bool same_row = t.y0 == t.y1;
             ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o00 + ch, v00);
-            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o01 + ch, v01);
             ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o10 + ch, v10);
-            ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o11 + ch, v11);
+            if (same_row) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) { v01[k] = v00[k]; v11[k] = v10[k]; }
+            } else {
+              ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o01 + ch, v01);
+              ld8_bf16(reinterpret_cast<const __nv_bfloat16*>(in) + o11 + ch, v11);
+            }
             // same summation order as the VEC == 4 path over the two 4-channel halves
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -282,9 +290,10 @@ __global__ void __launch_bounds__(256, WARP_BWD_MINB) sample_bwd_kernel(const T*
             }
             if (d_in != nullptr) {
               const size_t offs[4] = {o00 + ch, o01 + ch, o10 + ch, o11 + ch};
-              const float ws[4] = {w00, w01, w10, w11};
+              const float ws[4] = {same_row ? w00 + w01 : w00, w01, same_row ? w10 + w11 : w10, w11};
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
+                if (same_row && (k & 1)) continue;           // folded into slot k - 1 (same address)
                 const float4 lo = make_float4(ws[k] * g[0], ws[k] * g[1], ws[k] * g[2], ws[k] * g[3]);
                 const float4 hi = make_float4(ws[k] * g[4], ws[k] * g[5], ws[k] * g[6], ws[k] * g[7]);
                 if (RUN) {
