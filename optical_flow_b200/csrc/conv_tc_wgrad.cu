@@ -39,6 +39,7 @@ struct WgradParams {
   int KW, pad_t, pad_l, stride_w, stride_h;
   int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
   int ktiles, ktiles_per_split, kt_step;
+  int dbg;                        // -DOF_PROFILE_HOOKS only (OF_WG_DBG): 1 = the epilogue reads TMEM but issues no atomics
   int n_mma, n_valid, n_chunks;   // dy: MMA N, real Cout, 64-channel chunks
   int Cin, Cout;
   int stages, stage_bytes, tmem_cols;
@@ -272,7 +273,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             uint32_t rr[16];
             tc::tmem_ld16(taddr + (uint32_t)c0, rr);
             tc::tmem_ld_wait();
-            if (!valid) continue;
+            if (!valid || (OF_DBG(P) & 1)) continue;
             float* dst = P.dw + ((size_t)(kh * 3 + kw) * P.Cin + cin) * P.Cout + co0;
             const int nv = min(16, P.n_valid - co0);
             if ((P.Cout % 4) == 0 && nv == 16) {
@@ -303,7 +304,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
           uint32_t rr[16];
           tc::tmem_ld16(taddr + (uint32_t)c0, rr);
           tc::tmem_ld_wait();
-          if (valid && c0 < P.n_valid) {
+          if (valid && c0 < P.n_valid && !(OF_DBG(P) & 1)) {
             int nv = min(16, P.n_valid - c0);
             if (vec4 && nv == 16) {
 #pragma unroll
@@ -490,6 +491,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (splits < 1) splits = 1;
   P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
+  if (const char* e = of_tune_env("OF_WG_DBG")) P.dbg = atoi(e);
   P.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : splits;     // interleaved K tiles (every split has >= 1 tile: splits <= ktiles)
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
