@@ -487,12 +487,6 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
                           !of_tune_env("OF_WG_NO_2CTA");
   if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
   if (const char* e = of_tune_env("OF_WG_WAVES")) splits = (atoi(e) * OF_NUM_SMS) / jobs;
-  if (splits > P.ktiles) splits = P.ktiles;
-  if (splits < 1) splits = 1;
-  P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
-  splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
-  if (const char* e = of_tune_env("OF_WG_DBG")) P.dbg = atoi(e);
-  P.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : splits;     // interleaved K tiles (every split has >= 1 tile: splits <= ktiles)
   P.stage_bytes = (P.slab2 ? 3 * P.slab_bytes : P.slab ? 2 * P.slab_bytes : tpp * 2 * WG_CHUNK_BYTES) +
                   P.n_chunks * WG_CHUNK_BYTES;
   if (P.nstack) P.stage_bytes = ((P.nstack_one && !P.one_split) ? 3 : 2) * WG_CHUNK_BYTES + P.n_chunks * P.slab_bytes;
@@ -505,8 +499,40 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
-  dim3 grid(jobs, splits);
-  OF_CUDA(of_launch_pdl(conv_tc_wgrad_kernel, grid, dim3(WG_THREADS), smem, st, tmX[0], tmX[1], tmDY, P));
+
+  // The jobs of one pixel range (kw columns / M tiles) read the same dy slabs and nearly the same x tiles; ncu shows 1 018 MB
+  // of DRAM reads per 128->128 launch against 504 MB of operands and an L2 read hit rate of 40 %.  Option OF_WG_CLUSTER
+  // launches them as a thread-block CLUSTER (jobs, 1, 1) - co-scheduled on one GPC, same L2 partition, same start time.
+  // Measured (round 2, call 41): SLOWER - wgrad 2.39 -> 2.55 ms per step, 128->128 255 -> 262 us, 96->64 131 -> 187 us -
+  // so it is off by default.
+  cudaLaunchAttribute at[2];
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(WG_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = of_tune_env("OF_NO_PDL") ? 0 : 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  int cluster = (jobs >= 2 && jobs <= 8 && of_tune_env("OF_WG_CLUSTER")) ? jobs : 1;
+  if (cluster > 1) {
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = (unsigned)cluster; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+    cfg.gridDim = dim3(jobs, splits);
+    int max_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_clusters, conv_tc_wgrad_kernel, &cfg) == cudaSuccess && max_clusters >= 1) {
+      if (splits > max_clusters) splits = max_clusters;            // still ONE wave
+    } else {
+      cudaGetLastError();
+      cluster = 1; cfg.numAttrs = 1;
+    }
+  }
+  if (splits > P.ktiles) splits = P.ktiles;
+  if (splits < 1) splits = 1;
+  P.ktiles_per_split = (P.ktiles + splits - 1) / splits;
+  splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
+  if (const char* e = of_tune_env("OF_WG_DBG")) P.dbg = atoi(e);
+  P.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : splits;     // interleaved K tiles (every split has >= 1 tile: splits <= ktiles)
+  cfg.gridDim = dim3(jobs, splits);
+  OF_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_wgrad_kernel, tmX[0], tmX[1], tmDY, P));
   if (int r = of_launch_check(view ? "conv_tc_wgrad_kernel<stem>" : "conv_tc_wgrad_kernel")) return r;
   return 0;
 }
