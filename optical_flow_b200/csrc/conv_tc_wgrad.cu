@@ -16,6 +16,8 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 
+#include <atomic>
+
 #define WG_THREADS 192
 #define WG_CHUNK_BYTES 8192   // 64 pixels x 64 bf16
 #define WG_MAX_TAPS 9
@@ -39,6 +41,9 @@ struct WgradParams {
   int KW, pad_t, pad_l, stride_w, stride_h;
   int NB, Ho, Wo, TW, TH, tiles_w, tiles_h;
   int ktiles, ktiles_per_split, kt_step;
+  // dynamic K-tile scheduling: the CTAs of a job claim `claim` consecutive K tiles at a time from the job's counter in
+  // g_wg_ctr[ctr_set] (0 = static ranges as described by ktiles_per_split / kt_step)
+  int dyn, claim, ctr_set;
   int dbg;                        // -DOF_PROFILE_HOOKS only (OF_WG_DBG): 1 = the epilogue reads TMEM but issues no atomics
   int n_mma, n_valid, n_chunks;   // dy: MMA N, real Cout, 64-channel chunks
   int Cin, Cout;
@@ -69,6 +74,21 @@ struct WgradParams {
   int one_split;
 };
 
+// Dynamic K-tile scheduling (option OF_WG_DYNAMIC; OFF by default - measured slower).  With static, equal pixel ranges the
+// equal-work CTAs of a launch finish up to 35 % apart (ncu, 128->128: SM-active cycles avg 342k, max 461k).  Hypothesis:
+// the kernel ends with its slowest CTA and the jobs of a range drift so far apart that the later ones miss L2.  Test: hand
+// the K tiles out at run time - one counter per job, a CTA claims `claim` consecutive tiles per atomic (the next claim is in
+// flight while the current tiles load), every CTA works at the same frontier of the tensor and all finish together.
+// Result (round 2, call 44, same box): wgrad per step 2 409 us static -> 2 510 us dynamic (claim 1 / 2 / 4 alike, 8 worse);
+// 128->128 254 -> 261 us, 16 x 96 x 320 64->64 66 -> 75 us.  So the spread is not lost time: a CTA that finishes early
+// leaves its share of the L2 / shared-memory / tensor throughput to the others, the launch is bound by the aggregate.
+// The sums are added with red.global.add in either mode, so which CTA takes which tile does not change the result beyond
+// the summation order.  Counter sets: one per launch, round robin (concurrent launches on different streams never share
+// one); the last CTA to finish zeroes the set for its next use.
+#define WG_CTR_SETS 256
+#define WG_CTR_STRIDE (WG_MAX_JOBS + 1)          // [0, WG_MAX_JOBS): next K tile of the job; [WG_MAX_JOBS]: finished CTAs
+static __device__ unsigned g_wg_ctr[WG_CTR_SETS * WG_CTR_STRIDE];
+
 __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                      const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ WgradParams P) {
@@ -78,24 +98,23 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ones + WG_ONES_BYTES);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* acc_full = empty_bar + 8;
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  uint64_t* meta_bar = acc_full + 1;                       // producer -> epilogue: s_meta is written
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(meta_bar + 1);
+  int* s_kt = reinterpret_cast<int*>(tmem_base_slot + 2);   // K tile held by each stage (-1: no more tiles)
+  int* s_meta = s_kt + 8;                                   // [0] tiles this CTA processed, [1] any of them with the bias MMAs
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
     tc::mbar_init(acc_full, 1);
+    tc::mbar_init(meta_bar, 1);
     tc::fence_barrier_init();
   }
   if (warp == 4 && lane == 0) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
-  // the bias gradient of a K tile is computed by ONE of the jobs that walk it, rotating PER K TILE: every CTA carries
-  // 1 / jobs of the extra MMAs.  (Rotating per pixel range gave a third of the CTAs all of them: with one wave the
-  // kernel ends with its slowest CTA - ncu, 128->128: SM active cycles avg 342k, max 461k.)
+  // the bias gradient of a K tile is computed by ONE of the jobs that walk it, rotating PER K TILE (tile kt: job
+  // kt % jobs): every CTA carries 1 / jobs of the extra MMAs.  (Rotating per pixel range gave a third of the CTAs all of them.)
   const bool do_bias = P.db != nullptr;
-#ifdef WG_BIAS_PER_RANGE
-#define WG_BIAS_NOW(it_) (blockIdx.x == (blockIdx.y % gridDim.x))
-#else
-#define WG_BIAS_NOW(it_) ((((it_) + (int)blockIdx.y) % (int)gridDim.x) == (int)blockIdx.x)
-#endif
+#define WG_BIAS_TILE(kt_) (((kt_) % (int)gridDim.x) == (int)blockIdx.x)
   if (do_bias) {
     // bf16 1.0 = 0x3f80; all-ones is invariant under the 128-byte swizzle
     for (int i = threadIdx.x; i < WG_ONES_BYTES / 16; i += WG_THREADS)
@@ -127,11 +146,31 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   if (warp == 4) {
     if (OF_ONE_LANE()) {
       int stage = 0; uint32_t phase = 0;
-      for (int kt = k_begin; kt < k_end; kt += kt_step) {
+      unsigned* ctr = g_wg_ctr + (size_t)P.ctr_set * WG_CTR_STRIDE;
+      int cur = k_begin, cur_end = k_end;                  // static: [k_begin, k_end) in steps of kt_step
+      unsigned nxt = 0;
+      if (P.dyn) { cur = cur_end = 0; nxt = atomicAdd(&ctr[job], (unsigned)P.claim); }
+      int n_tiles = 0, any_bias = 0;
+      for (;;) {
+        int kt;
+        if (P.dyn) {
+          if (cur == cur_end) {                            // take the claim that was in flight, put the next one in flight
+            cur = (int)min(nxt, (unsigned)P.ktiles);
+            cur_end = min(cur + P.claim, P.ktiles);
+            if (cur < P.ktiles) nxt = atomicAdd(&ctr[job], (unsigned)P.claim);
+          }
+          kt = cur < cur_end ? cur++ : -1;
+        } else {
+          kt = cur < cur_end ? cur : -1;
+          cur += kt_step;
+        }
+        tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+        s_kt[stage] = kt;                                  // read by the issuer after its full_bar wait (arrive = release)
+        if (kt < 0) { tc::mbar_arrive(&full_bar[stage]); break; }
+        ++n_tiles; any_bias |= WG_BIAS_TILE(kt) ? 1 : 0;
         int tw_i = kt % P.tiles_w; int r = kt / P.tiles_w;
         int th_i = r % P.tiles_h; int n = r / P.tiles_h;
         int w0 = tw_i * P.TW, h0 = th_i * P.TH;
-        tc::mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
         if (P.nstack) {
@@ -178,15 +217,27 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
           tc::tma_load_4d(base + a_bytes + (size_t)c * WG_CHUNK_BYTES, &tmDY, &full_bar[stage], c * 64, w0, h0, n);
         if (++stage == P.stages) { stage = 0; phase ^= 1; }
       }
+      s_meta[0] = n_tiles; s_meta[1] = any_bias;
+      tc::mbar_arrive(meta_bar);
+      if (P.dyn) {
+        // every claim of this CTA has returned (its value decided the loop's end); the last CTA to get here resets the set
+        __threadfence();
+        if (atomicAdd(&ctr[WG_MAX_JOBS], 1u) == gridDim.x * gridDim.y - 1) {
+          for (int j = 0; j < (int)gridDim.x; ++j) ctr[j] = 0;
+          ctr[WG_MAX_JOBS] = 0;
+        }
+      }
     }
   } else if (warp == 5) {
     if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 1, 1);
       int stage = 0; uint32_t phase = 0;
-      int it = 0; bool bias_acc = false;
-      for (int kt = k_begin; kt < k_end; kt += kt_step, ++it) {
-        const bool bias_now = do_bias && WG_BIAS_NOW(it);
+      bool bias_acc = false, first = true;
+      for (;; first = false) {
         tc::mbar_wait(&full_bar[stage], phase);
+        const int kt = s_kt[stage];
+        if (kt < 0) break;
+        const bool bias_now = do_bias && WG_BIAS_TILE(kt);
         tc::fence_after_sync();
         uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
         uint32_t b_addr = base + (uint32_t)a_bytes;
@@ -200,7 +251,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
                 uint64_t adesc = tc::desc_sw128_mnmajor(base + (uint32_t)(a * 2 * WG_CHUNK_BYTES) + k * 2048, WG_CHUNK_BYTES);
                 uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + (uint32_t)(c * P.slab_bytes) + k * 2048, row);
                 tc::mma_bf16(tmem_base + (uint32_t)((a * P.n_chunks + c) * 192), adesc, bdesc, idesc_n,
-                             (kt > k_begin || k > 0) ? 1u : 0u);
+                             (!first || k > 0) ? 1u : 0u);
               }
             }
           if (bias_now) {
@@ -234,7 +285,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             // 16 pixels (K) per MMA = 16 rows of 128 B = 2048 B
             uint64_t adesc = tc::desc_sw128_mnmajor(a_addr + k * 2048, a_lbo);
             uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
-            tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (kt > k_begin || k > 0) ? 1u : 0u);
+            tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
           }
         }
         if (bias_now) {
@@ -253,7 +304,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
     }
   } else {
     // epilogue: row = input channel (M), columns = output channels
-    const bool has_work = k_end > k_begin;
+    tc::mbar_wait(meta_bar, 0);
+    const bool has_work = s_meta[0] > 0;
     if (has_work) {
       tc::mbar_wait(acc_full, 0);
       tc::fence_after_sync();
@@ -320,12 +372,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
           }
         }
       }
-      // did this CTA run any bias tile?  (iterations it = 0 .. n_it - 1; the first one with WG_BIAS_NOW)
-      bool had_bias = false;
-      if (do_bias) {
-        const int n_it = (k_end - k_begin + kt_step - 1) / kt_step;
-        for (int i = 0; i < n_it && i < (int)gridDim.x; ++i) had_bias = had_bias || WG_BIAS_NOW(i);
-      }
+      const bool had_bias = do_bias && s_meta[1] != 0;     // did this CTA run any bias tile?
       if (had_bias && warp == 0) {
         // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
         uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? P.n_chunks * 192 : P.n_mma));
@@ -373,6 +420,12 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.TW = 16; P.TH = 4;
   for (int k = 0; k < 4; ++k)
     if (c->Wo % cands[k] == 0) { P.TW = cands[k]; P.TH = 64 / cands[k]; break; }
+  // A/B of the slab halo (same MMAs, different L2 -> SM bytes per K tile: 8x8 36 KB, 16x4 40 KB, 32x2 48 KB at 128->128).
+  // Round 2, call 45: 258.7 / 254.0 / 268.1 us - +20 % bytes cost 5 %, -10 % bytes nothing: not the L2 -> SM path.
+  if (const char* e = of_tune_env("OF_WG_TW")) {
+    int v = atoi(e);
+    if ((v == 8 || v == 16 || v == 32) && c->Wo % v == 0 && c->Ho % (64 / v) == 0) { P.TW = v; P.TH = 64 / v; }
+  }
   P.tiles_w = (c->Wo + P.TW - 1) / P.TW;
   P.tiles_h = (c->Ho + P.TH - 1) / P.TH;
   long long kt = (long long)c->N * P.tiles_w * P.tiles_h;
@@ -498,7 +551,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
   if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
-  size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 17 * sizeof(uint64_t) + 16;
+  size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 256;   // barriers, TMEM slot, s_kt, s_meta
 
   // The jobs of one pixel range (kw columns / M tiles) read the same dy slabs and nearly the same x tiles; ncu shows 1 018 MB
   // of DRAM reads per 128->128 launch against 504 MB of operands and an L2 read hit rate of 40 %.  Option OF_WG_CLUSTER
@@ -531,6 +584,14 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   splits = (P.ktiles + P.ktiles_per_split - 1) / P.ktiles_per_split;
   if (const char* e = of_tune_env("OF_WG_DBG")) P.dbg = atoi(e);
   P.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : splits;     // interleaved K tiles (every split has >= 1 tile: splits <= ktiles)
+  // dynamic K-tile scheduling (see g_wg_ctr; opt-in): ~16 claims per CTA, at most 4 tiles each
+  static std::atomic<unsigned> launch_seq{0};
+  P.dyn = of_tune_env("OF_WG_DYNAMIC") ? 1 : 0;
+  P.ctr_set = (int)(launch_seq.fetch_add(1) % WG_CTR_SETS);
+  P.claim = P.ktiles / (splits * 16);
+  if (P.claim < 1) P.claim = 1;
+  if (P.claim > 4) P.claim = 4;
+  if (const char* e = of_tune_env("OF_WG_CLAIM")) { int v = atoi(e); if (v >= 1 && v <= 64) P.claim = v; }
   cfg.gridDim = dim3(jobs, splits);
   OF_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_wgrad_kernel, tmX[0], tmX[1], tmDY, P));
   if (int r = of_launch_check(view ? "conv_tc_wgrad_kernel<stem>" : "conv_tc_wgrad_kernel")) return r;

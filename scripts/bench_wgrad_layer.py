@@ -24,8 +24,12 @@ def run(N, H, W, Cin, Cout, iters=20, tag=""):
 if __name__ == "__main__":
     shapes = [(8, 192, 640, 64, 32), (16, 96, 320, 64, 64), (8, 96, 320, 64, 32), (8, 192, 640, 96, 64),
               (8, 192, 640, 128, 96), (8, 192, 640, 128, 128)]
-    for env in ("", "OF_WG_NO_SLAB2"):
-        if env: os.environ[env] = "1"
-        for s in shapes[:3] if env else shapes:
+    # variants from the command line ("OF_WG_STATIC=1" ...), default first
+    variants = [""] + sys.argv[1:]
+    from optical_flow_b200 import _lib as L
+    for env in variants:
+        opts = [o.partition("=") for o in env.split(",") if o]
+        for k, _, v in opts: L.check(L.load().of_set_option(k.encode(), (v or "1").encode()), "of_set_option")
+        for s in shapes:
             run(*s, tag=env or "default")
-        if env: del os.environ[env]
+        for k, _, v in opts: L.load().of_set_option(k.encode(), None)
