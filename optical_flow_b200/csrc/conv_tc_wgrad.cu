@@ -50,6 +50,10 @@ struct WgradParams {
   int stages, stage_bytes, tmem_cols;
   float* dw;
   float* db;                      // nullable: fused bias gradient (one job per pixel range)
+  int k_outer;                    // N-stacked main loop: K slice outermost (option OF_WG_KOUTER)
+  int bias_t;                     // 1: transposed bias MMAs - A = the dy tile (M = its channels), B = ones, N = 16
+  int bias_m;                     // M of the ones-MMAs of the bias gradient (64 or 128; only row 0 is read)
+  int bias_range;                 // 1: ONE job per split-K range computes the bias gradient of all its tiles (static ranges only)
   // Cin <= 64 (one chunk): the two 64-row halves of an accumulator hold two different TAPS of that chunk
   // instead of two channel chunks - no zero half, half the MMAs.  job_tap0 / job_ntaps then count accumulators.
   int pack2, taps;
@@ -114,7 +118,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   // the bias gradient of a K tile is computed by ONE of the jobs that walk it, rotating PER K TILE (tile kt: job
   // kt % jobs): every CTA carries 1 / jobs of the extra MMAs.  (Rotating per pixel range gave a third of the CTAs all of them.)
   const bool do_bias = P.db != nullptr;
-#define WG_BIAS_TILE(kt_) (((kt_) % (int)gridDim.x) == (int)blockIdx.x)
+#define WG_BIAS_TILE(kt_) (P.bias_range ? (blockIdx.x == blockIdx.y % gridDim.x) : (((kt_) % (int)gridDim.x) == (int)blockIdx.x))
   if (do_bias) {
     // bf16 1.0 = 0x3f80; all-ones is invariant under the 128-byte swizzle
     for (int i = threadIdx.x; i < WG_ONES_BYTES / 16; i += WG_THREADS)
@@ -172,6 +176,11 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         int th_i = r % P.tiles_h; int n = r / P.tiles_h;
         int w0 = tw_i * P.TW, h0 = th_i * P.TH;
         uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
+        if ((OF_DBG(P) & 2) && n_tiles > P.stages) {       // profile hook: MMAs only (stages keep their first tiles)
+          tc::mbar_arrive(&full_bar[stage]);
+          if (++stage == P.stages) { stage = 0; phase ^= 1; }
+          continue;
+        }
         tc::mbar_expect_tx(&full_bar[stage], (uint32_t)tx_bytes);
         if (P.nstack) {
           const int nbox = P.nstack_one ? (P.one_split ? (tap0 == 0 ? 2 : 1) : 3) : 2;
@@ -244,7 +253,21 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         if (P.nstack) {
           const uint32_t idesc_n = tc::idesc_bf16_f32(128, 192, 1, 1);
           const uint32_t row = (uint32_t)(P.TW * 128);
-          for (int a = 0; a < ntaps; ++a)
+          if (P.k_outer && !((OF_DBG(P) & 4) && !first)) {
+            // K slice outermost: consecutive MMAs go to DIFFERENT accumulators (A/B of the accumulate dependency)
+            for (int a = 0; a < ntaps; ++a) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                uint64_t adesc = tc::desc_sw128_mnmajor(base + (uint32_t)(a * 2 * WG_CHUNK_BYTES) + k * 2048, WG_CHUNK_BYTES);
+                for (int c = 0; c < P.n_chunks; ++c) {
+                  uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + (uint32_t)(c * P.slab_bytes) + k * 2048, row);
+                  tc::mma_bf16(tmem_base + (uint32_t)((a * P.n_chunks + c) * 192), adesc, bdesc, idesc_n,
+                               (!first || k > 0) ? 1u : 0u);
+                }
+              }
+            }
+          } else
+          for (int a = 0; a < ((OF_DBG(P) & 4) && !first ? 0 : ntaps); ++a)      // profile hook 4: loads only
             for (int c = 0; c < P.n_chunks; ++c) {
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
@@ -254,9 +277,25 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
                              (!first || k > 0) ? 1u : 0u);
               }
             }
-          if (bias_now) {
+          if (bias_now && P.bias_t) {
+            // transposed: D[channel][0..15] += dy tile^T (A, MN-major: M = 2 x 64 channels, one slab apart) x ones (B, N = 16);
+            // an odd last chunk is paired with the ones tile (rows 64..127 are not read back)
+            const uint32_t idesc_t = tc::idesc_bf16_f32(128, 16, 1, 1);
+            const uint32_t ones_a = tc::smem_u32(ones);
+            const uint64_t odesc = tc::desc_sw128_mnmajor(ones_a, 2048);
+            for (int p = 0; 2 * p < P.n_chunks; ++p) {
+              const uint32_t a0 = b_addr + (uint32_t)(2 * p * P.slab_bytes) + row;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t lbo = (2 * p + 1 < P.n_chunks) ? (uint32_t)P.slab_bytes : ones_a - (a0 + k * 2048);
+                tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_chunks * 192 + 16 * p),
+                             tc::desc_sw128_mnmajor(a0 + k * 2048, lbo), odesc, idesc_t, (bias_acc || k > 0) ? 1u : 0u);
+              }
+            }
+            bias_acc = true;
+          } else if (bias_now) {
             // kh = 1 (one row into the slab) is dy unshifted; the chunks are one slab apart
-            const uint32_t idesc_b = tc::idesc_bf16_f32(128, P.n_chunks * 64, 1, 1);
+            const uint32_t idesc_b = tc::idesc_bf16_f32(P.bias_m, P.n_chunks * 64, 1, 1);
             const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -288,12 +327,27 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
             tc::mma_bf16(tmem_base + (uint32_t)(t * P.n_mma), adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
           }
         }
-        if (bias_now) {
+        if (bias_now && P.bias_t) {
+          const uint32_t idesc_t = tc::idesc_bf16_f32(128, 16, 1, 1);
+          const uint32_t ones_a = tc::smem_u32(ones);
+          const uint64_t odesc = tc::desc_sw128_mnmajor(ones_a, 2048);
+          for (int p = 0; 2 * p < P.n_chunks; ++p) {
+            const uint32_t a0 = b_addr + (uint32_t)(2 * p * WG_CHUNK_BYTES);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint32_t lbo = (2 * p + 1 < P.n_chunks) ? (uint32_t)WG_CHUNK_BYTES : ones_a - (a0 + k * 2048);
+              tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma + 16 * p), tc::desc_sw128_mnmajor(a0 + k * 2048, lbo), odesc,
+                           idesc_t, (bias_acc || k > 0) ? 1u : 0u);
+            }
+          }
+          bias_acc = true;
+        } else if (bias_now) {
           const uint64_t odesc = tc::desc_sw128_mnmajor(tc::smem_u32(ones), 2048);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             uint64_t bdesc = tc::desc_sw128_mnmajor(b_addr + k * 2048, WG_CHUNK_BYTES);
-            tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma), odesc, bdesc, idesc, (bias_acc || k > 0) ? 1u : 0u);
+            tc::mma_bf16(tmem_base + (uint32_t)(ntaps * P.n_mma), odesc, bdesc, tc::idesc_bf16_f32(P.bias_m, P.n_mma, 1, 1),
+                         (bias_acc || k > 0) ? 1u : 0u);
           }
           bias_acc = true;
         }
@@ -373,7 +427,19 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
         }
       }
       const bool had_bias = do_bias && s_meta[1] != 0;     // did this CTA run any bias tile?
-      if (had_bias && warp == 0) {
+      if (had_bias && P.bias_t) {
+        // transposed accumulators: row = channel (chunk pair p: 2 x 64 rows), every column holds the sum
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) +
+                               (uint32_t)(ntaps * (P.nstack ? P.n_chunks * 192 : P.n_mma));
+        for (int p = 0; 2 * p < P.n_chunks; ++p) {
+          __syncwarp();
+          uint32_t rr[16];
+          tc::tmem_ld16(taddr + (uint32_t)(16 * p), rr);
+          tc::tmem_ld_wait();
+          const int ch = 2 * p + (row >> 6), co = ch * 64 + (row & 63);
+          if (ch < P.n_chunks && co < P.n_valid) red_add(P.db + co, __uint_as_float(rr[0]));
+        }
+      } else if (had_bias && warp == 0) {
         // every row of the ones-accumulator holds the column sums; row 0 (lane 0) reduces them into db
         uint32_t taddr = tmem_base + (uint32_t)(ntaps * (P.nstack ? P.n_chunks * 192 : P.n_mma));
         for (int c0 = 0; c0 < P.n_mma; c0 += 16) {
@@ -393,6 +459,136 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_cons
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 5) tc::tmem_dealloc(tmem_base, (uint32_t)P.tmem_cols);
+}
+
+// ---- CTA-pair variant (cta_group::2) of the N-stacked mode with two dy chunks (Cout 65..128, Cin > 64) ----------------
+// Two jobs (M tile, kw) of one pixel range run as a CTA pair on the two SMs of a TPC: each CTA loads its own x tile
+// (A, 128 rows = 128 input channels, 16 KB per K tile) and ONE of the two dy slabs (CTA r: output channels 64 r ..); an
+// MMA of M = 256 takes B's columns half from each CTA.  Per K slice of 16 pixels: N = 256 (per CTA the kh = 2 and kh = 1
+// views of its slab) and N = 128 (kh = 0).  Accumulator columns of BOTH CTAs (rows = the CTA's own input channels):
+//   [  0, 256): [kh2 | kh1] of chunk 0, [kh2 | kh1] of chunk 1  (64 columns each)     [256, 384): kh0 of chunk 0 | chunk 1
+// Per SM and K tile 28 KB of loads / 14 KB of MMA operand reads per K slice instead of 40 KB / 20 KB.  No bias gradient
+// here: the launch that handles the unpaired job(s) of the layer computes it.
+__global__ void __launch_bounds__(WG_THREADS, 1)
+conv_tc_wgrad_pair_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                          const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ WgradParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + (size_t)P.stages * P.stage_bytes);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* acc_full = empty_bar + 8;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  int* s_kt = reinterpret_cast<int*>(tmem_base_slot + 2);
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = tc::cluster_ctarank();               // cluster (2, 1, 1): rank = blockIdx.x & 1
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P.stages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    tc::mbar_init(acc_full, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 4 && tc::elect_one()) { tc::prefetch_tmap(&tmX0); tc::prefetch_tmap(&tmX1); tc::prefetch_tmap(&tmDY); }
+  if (warp == 5) { tc::tmem_alloc_2cta(tmem_base_slot, 512u); tc::tmem_relinquish_2cta(); }
+  if (threadIdx.x == 0) OF_PDL_TRIGGER();
+  OF_PDL_WAIT();
+  tc::fence_before_sync();
+  tc::cluster_sync();                                        // both CTAs' barriers are initialised, TMEM is allocated
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  const int job = (int)(blockIdx.x & ~1u) + (int)rank;
+  const int mt = P.job_mt[job], kw = P.job_tap0[job];
+  const int kt_step = P.kt_step;
+  const int k_begin = kt_step > 1 ? (int)blockIdx.y : blockIdx.y * P.ktiles_per_split;
+  const int k_end = kt_step > 1 ? P.ktiles : min(P.ktiles, k_begin + P.ktiles_per_split);
+  const int a_bytes = 2 * WG_CHUNK_BYTES;
+  const uint32_t tx_pair = 2u * (uint32_t)(a_bytes + P.slab_bytes);
+
+  if (warp == 4) {
+    if (tc::elect_one()) {
+      int stage = 0; uint32_t phase = 0;
+      for (int kt = k_begin;; kt += kt_step) {
+        tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (kt >= k_end) {
+          if (rank == 0) { s_kt[stage] = -1; tc::mbar_arrive(&full_bar[stage]); }
+          break;
+        }
+        if (rank == 0) { s_kt[stage] = kt; tc::mbar_expect_tx(&full_bar[stage], tx_pair); }
+        int tw_i = kt % P.tiles_w; int r = kt / P.tiles_w;
+        int th_i = r % P.tiles_h; int n = r / P.tiles_h;
+        int w0 = tw_i * P.TW, h0 = th_i * P.TH;
+        uint8_t* base = tiles + (size_t)stage * P.stage_bytes;
+        for (int c = 0; c < 2; ++c) {
+          const int chunk = mt * 2 + c;
+          const int cm = P.chunk_map[chunk];
+          const CUtensorMap* tm = (cm == 1) ? &tmX1 : &tmX0;
+          int cc = cm < 0 ? (1 << 20) : P.chunk_c0[chunk];
+          tc::tma_load_4d_2cta(base + (size_t)c * WG_CHUNK_BYTES, tm, &full_bar[stage], cc, w0 + kw - P.pad_l, h0, n);
+        }
+        tc::tma_load_4d_2cta(base + a_bytes, &tmDY, &full_bar[stage], (int)rank * 64, w0, h0 - 1, n);
+        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 5) {
+    if (rank == 0 && tc::elect_one()) {
+      const uint32_t idesc1 = tc::idesc_bf16_f32(256, 256, 1, 1), idesc2 = tc::idesc_bf16_f32(256, 128, 1, 1);
+      const uint32_t row = (uint32_t)(P.TW * 128);
+      int stage = 0; uint32_t phase = 0;
+      for (bool first = true;; first = false) {
+        tc::mbar_wait(&full_bar[stage], phase);
+        if (s_kt[stage] < 0) break;
+        tc::fence_after_sync();
+        const uint32_t base = tc::smem_u32(tiles + (size_t)stage * P.stage_bytes);
+        const uint32_t b_addr = base + (uint32_t)a_bytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          tc::mma_bf16_2cta(tmem_base, tc::desc_sw128_mnmajor(base + k * 2048, WG_CHUNK_BYTES),
+                            tc::desc_sw128_mnmajor(b_addr + k * 2048, row), idesc1, (!first || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          tc::mma_bf16_2cta(tmem_base + 256u, tc::desc_sw128_mnmajor(base + k * 2048, WG_CHUNK_BYTES),
+                            tc::desc_sw128_mnmajor(b_addr + 2 * row + k * 2048, row), idesc2, (!first || k > 0) ? 1u : 0u);
+        tc::mma_commit_2cta(&empty_bar[stage]);
+        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+      }
+      tc::mma_commit_2cta(acc_full);
+    }
+  } else {
+    tc::mbar_wait(acc_full, 0);
+    tc::fence_after_sync();
+    const int lane = threadIdx.x & 31;
+    const int row = warp * 32 + lane;
+    const int chunk = mt * 2 + (row >> 6), rcn = row & 63;
+    const bool valid = P.chunk_map[chunk] >= 0 && rcn < P.chunk_cnt[chunk];
+    const int cin = P.chunk_ci[chunk] + rcn;
+    const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    for (int c0 = 0; c0 < 384; c0 += 16) {
+      int kh, co0;
+      if (c0 < 256) { kh = 2 - ((c0 & 127) >> 6); co0 = (c0 >> 7) * 64 + (c0 & 63); }
+      else          { kh = 0; co0 = ((c0 - 256) >> 6) * 64 + (c0 & 63); }
+      if (co0 >= P.n_valid) continue;                        // warp-uniform
+      __syncwarp();
+      uint32_t rr[16];
+      tc::tmem_ld16(taddr + (uint32_t)c0, rr);
+      tc::tmem_ld_wait();
+      if (!valid) continue;
+      float* dst = P.dw + ((size_t)(kh * 3 + kw) * P.Cin + cin) * P.Cout + co0;
+      const int nv = min(16, P.n_valid - co0);
+      if ((P.Cout % 4) == 0 && nv == 16) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          red_add_v4(dst + 4 * j, make_float4(__uint_as_float(rr[4 * j]), __uint_as_float(rr[4 * j + 1]),
+                                              __uint_as_float(rr[4 * j + 2]), __uint_as_float(rr[4 * j + 3])));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < nv) red_add(dst + j, __uint_as_float(rr[j]));
+      }
+    }
+  }
+  tc::fence_before_sync();
+  tc::cluster_sync();                                        // both epilogues have read their TMEM, no arrive is in flight
+  if (warp == 5) tc::tmem_dealloc_2cta(tmem_base, 512u);
 }
 
 extern "C" {
@@ -437,10 +633,26 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.Cin = c->Cin; P.Cout = c->Cout;
   P.dw = c->dw;
   P.db = c->db;
-  OF_REQUIRE(c->db == nullptr || 2 * P.n_mma <= 512, OF_ERR_UNSUPPORTED,
+  // Bias gradient: MMAs against an all-ones tile into a spare accumulator.  Default (round 2, call 53): TRANSPOSED - A = the
+  // unshifted dy tile (MN-major, M = its channels, two 64-channel chunks per MMA), B = ones, N = 16: 1 / 8 of the tensor
+  // time of the first form (A = ones with 128 identical rows, B = dy, N = Cout; option OF_WG_BIAS_ONES_A).  Measured:
+  // 16 x 96 x 320 64->64 69.0 -> 62.4 us (no bias gradient at all: 61.0), 96->64 140.6 -> 131.7 (126.4), 128->128
+  // 261 -> 262 (236: with one CTA per SM the cost is the switch of accumulator, not the MMA's size); step: wgrad
+  // 2 514 -> 2 452 us.  The bias MMAs still cost 3-10 % of the kernel.  Three SIMT replacements by the four epilogue warps,
+  // which idle during the main loop, were built and measured (calls 48-50) - all slower, none kept: column sums from the
+  // shared-memory ring (stage released by MMA commit + 4 warp arrives): 128->128 261 -> 247 us but 96->64 136 -> 166 us,
+  // 64->64 66 -> 79 us, wgrad per step 2 433 -> 2 541 us; the same with one polling lane per warp or one bias job per
+  // range: no better; column sums read once more through L2 with __ldg: 2-3x slower (one tile's loads in flight at a time).
+  // M = 64 for the ones-A form (OF_WG_BIAS_M64): no change.
+  const bool mma_bias = c->db != nullptr;
+  P.bias_m = of_tune_env("OF_WG_BIAS_M64") ? 64 : 128;
+  P.bias_t = of_tune_env("OF_WG_BIAS_ONES_A") ? 0 : 1;
+  P.k_outer = of_tune_env("OF_WG_KOUTER") ? 1 : 0;
+  const int bias_cols_t = 32;                                   // 16 columns per pair of dy chunks, n_chunks <= 4
+  OF_REQUIRE(!mma_bias || P.n_mma + (P.bias_t ? bias_cols_t : P.n_mma) <= 512, OF_ERR_UNSUPPORTED,
              "fused bias gradient needs a spare TMEM accumulator (Cout <= 256 -> n_mma <= 256)");
   // taps per pass: one TMEM accumulator (n_mma columns) per tap, one more for the fused bias gradient
-  int tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
+  int tpp = (512 - (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0)) / P.n_mma;
   if (tpp > taps) tpp = taps;
   // keep >= 2 pipeline stages inside 200 KB of shared memory
   while (tpp > 1 && 2 * (tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES) > 200 * 1024) --tpp;
@@ -451,12 +663,12 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   int x_chunks = 0;
   for (int s_ = 0; s_ < c->num_src; ++s_) x_chunks += (c->x_valid[s_] + 63) / 64;
   P.slab = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view && x_chunks >= 2 &&
-            (512 - (c->db ? P.n_mma : 0)) / P.n_mma >= 3 && P.TW >= 8 && P.TW <= 32 && !of_tune_env("OF_WG_NO_SLAB"))
+            (512 - (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0)) / P.n_mma >= 3 && P.TW >= 8 && P.TW <= 32 && !of_tune_env("OF_WG_NO_SLAB"))
                ? 1 : 0;
   P.slab_bytes = (P.TH + 2) * P.TW * 128;
   if (P.slab) { tpp = 3; passes = 3; }
   P.slab2 = (x_chunks == 1 && !of_tune_env("OF_WG_NO_PACK2") && c->KH == 3 && c->KW == 3 && P.stride_w == 1 &&
-             P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && (5 + (c->db ? 1 : 0)) * P.n_mma <= 512 &&
+             P.stride_h == 1 && !view && P.TW >= 8 && P.TW <= 32 && 5 * P.n_mma + (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0) <= 512 &&
              !of_tune_env("OF_WG_NO_SLAB2"))
                 ? 1 : 0;
   P.nstack = (c->KH == 3 && c->KW == 3 && P.stride_w == 1 && P.stride_h == 1 && !view &&
@@ -502,7 +714,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   P.pack2 = (nch == 1 && taps > 1 && !P.nstack && !of_tune_env("OF_WG_NO_PACK2")) ? 1 : 0;
   const int units = P.pack2 ? (taps + 1) / 2 : taps;       // accumulators needed per M tile
   if (P.pack2) {
-    tpp = (512 - (c->db ? P.n_mma : 0)) / P.n_mma;
+    tpp = (512 - (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0)) / P.n_mma;
     if (tpp > units) tpp = units;
     while (tpp > 1 && 2 * (tpp * 2 * WG_CHUNK_BYTES + P.n_chunks * WG_CHUNK_BYTES) > 200 * 1024) --tpp;
     passes = (units + tpp - 1) / tpp;
@@ -529,13 +741,66 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
       P.job_mt[jobs] = mt; P.job_tap0[jobs] = t0; P.job_ntaps[jobs] = nt;
       ++jobs;
     }
+  // CTA pairs (conv_tc_wgrad_pair_kernel) for the wide N-stacked layers at the large levels: the jobs are paired two by
+  // two in one launch; the unpaired job (and, when the bias gradient is wanted, at least one job) goes through the
+  // one-CTA kernel below, which also computes the bias gradient.
+  const int pair_min = of_tune_env("OF_WG_PAIR_MIN") ? atoi(of_tune_env("OF_WG_PAIR_MIN")) : 4096;
+  if (P.nstack && !P.nstack_one && P.n_chunks == 2 && P.ktiles >= pair_min && of_tune_env("OF_WG_PAIR")) {
+    const int n_single = (jobs & 1) ? 1 : (c->db ? 2 : 0);
+    const int n_pairjobs = (jobs - n_single) / 2;
+    if (n_pairjobs >= 1) {
+      static bool pair_attr_set = false;
+      if (!pair_attr_set) {
+        OF_CUDA(cudaFuncSetAttribute(conv_tc_wgrad_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        pair_attr_set = true;
+      }
+      WgradParams PP = P;
+      PP.db = nullptr;
+      PP.stage_bytes = 2 * WG_CHUNK_BYTES + P.slab_bytes;
+      PP.stages = (200 * 1024) / PP.stage_bytes;
+      if (PP.stages > 8) PP.stages = 8;
+      PP.tmem_cols = 512;
+      cudaLaunchAttribute pat[2];
+      cudaLaunchConfig_t pcfg = {};
+      pcfg.blockDim = dim3(WG_THREADS);
+      pcfg.dynamicSmemBytes = 1024 + (size_t)PP.stages * PP.stage_bytes + 256;
+      pcfg.stream = st;
+      pat[0].id = cudaLaunchAttributeClusterDimension;
+      pat[0].val.clusterDim.x = 2; pat[0].val.clusterDim.y = 1; pat[0].val.clusterDim.z = 1;
+      pat[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      pat[1].val.programmaticStreamSerializationAllowed = of_tune_env("OF_NO_PDL") ? 0 : 1;
+      pcfg.attrs = pat; pcfg.numAttrs = 2;
+      int psplits = (OF_NUM_SMS / 2) / n_pairjobs;               // one wave of CTA pairs
+      pcfg.gridDim = dim3(2 * n_pairjobs, psplits);
+      int max_clusters = 0;
+      if (cudaOccupancyMaxActiveClusters(&max_clusters, conv_tc_wgrad_pair_kernel, &pcfg) == cudaSuccess && max_clusters >= 1) {
+        if (psplits * n_pairjobs > max_clusters) psplits = max_clusters / n_pairjobs;
+      } else {
+        cudaGetLastError();
+      }
+      if (psplits > PP.ktiles) psplits = PP.ktiles;
+      if (psplits < 1) psplits = 1;
+      PP.ktiles_per_split = (PP.ktiles + psplits - 1) / psplits;
+      psplits = (PP.ktiles + PP.ktiles_per_split - 1) / PP.ktiles_per_split;
+      PP.kt_step = of_tune_env("OF_WG_CONTIGUOUS") ? 1 : psplits;
+      pcfg.gridDim = dim3(2 * n_pairjobs, psplits);
+      OF_CUDA(cudaLaunchKernelEx(&pcfg, conv_tc_wgrad_pair_kernel, tmX[0], tmX[1], tmDY, PP));
+      if (int r = of_launch_check("conv_tc_wgrad_pair_kernel")) return r;
+      if (n_single == 0) return 0;
+      for (int j = 0; j < n_single; ++j) {
+        P.job_mt[j] = P.job_mt[jobs - n_single + j]; P.job_tap0[j] = P.job_tap0[jobs - n_single + j];
+        P.job_ntaps[j] = P.job_ntaps[jobs - n_single + j];
+      }
+      jobs = n_single;
+    }
+  }
   // ONE wave of one CTA per SM (never round up: 99 x 3 = 297 CTAs leaves one CTA for a wave of its own); a second
   // wave only repeats the prologue and doubles the split-K atomics (measured 3-15 % slower)
   int splits = OF_NUM_SMS / jobs;
   // N-stacked, several input chunks, Cout <= 64: 256 TMEM columns and a 28 KB stage - TWO CTAs fit an SM and fill
   // each other's bubbles (96->64 at N8 192x640: 198 -> 150 us)
   // (also the stem's strided-view wgrad: its overlapping-window boxes fill shared memory at ~20 B/clk per CTA)
-  const int acc_cols = P.nstack ? tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0) : (tpp + (c->db ? 1 : 0)) * P.n_mma;
+  const int acc_cols = P.nstack ? tpp * P.n_chunks * 192 + (mma_bias ? (P.bias_t ? bias_cols_t : P.n_chunks * 64) : 0) : (tpp * P.n_mma + (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0));
   const bool two_per_sm = ((P.nstack && (!P.nstack_one || P.one_split) && P.n_chunks == 1) || (view && acc_cols <= 256)) &&
                           !of_tune_env("OF_WG_NO_2CTA");
   if (two_per_sm) splits = (2 * OF_NUM_SMS) / jobs;
@@ -548,8 +813,8 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   if (two_per_sm) { int cap = (100 * 1024) / P.stage_bytes; if (cap < 2) cap = 2; if (P.stages > cap) P.stages = cap; }
   if (const char* e = of_tune_env("OF_WG_STAGES")) { int v = atoi(e); if (v >= 1 && v < P.stages) P.stages = v; }
   OF_REQUIRE(P.stages >= 1, OF_ERR_SHAPE, "wgrad stage does not fit shared memory");
-  int cols = (tpp + (c->db ? 1 : 0)) * P.n_mma;
-  if (P.nstack) cols = tpp * P.n_chunks * 192 + (c->db ? P.n_chunks * 64 : 0);
+  int cols = (tpp * P.n_mma + (mma_bias ? (P.bias_t ? bias_cols_t : P.n_mma) : 0));
+  if (P.nstack) cols = tpp * P.n_chunks * 192 + (mma_bias ? (P.bias_t ? bias_cols_t : P.n_chunks * 64) : 0);
   P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
   size_t smem = 1024 + (size_t)P.stages * P.stage_bytes + WG_ONES_BYTES + 256;   // barriers, TMEM slot, s_kt, s_meta
 
@@ -587,6 +852,7 @@ int of_conv_tc_wgrad(const of_tc_wgrad* c, void* stream) {
   // dynamic K-tile scheduling (see g_wg_ctr; opt-in): ~16 claims per CTA, at most 4 tiles each
   static std::atomic<unsigned> launch_seq{0};
   P.dyn = of_tune_env("OF_WG_DYNAMIC") ? 1 : 0;
+  P.bias_range = (!P.dyn && of_tune_env("OF_WG_BIAS_RANGE")) ? 1 : 0;
   P.ctr_set = (int)(launch_seq.fetch_add(1) % WG_CTR_SETS);
   P.claim = P.ktiles / (splits * 16);
   if (P.claim < 1) P.claim = 1;

@@ -4,12 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from optical_flow_b200 import conv_tc
 
 
-def run(N, H, W, Cin, Cout, iters=20, tag=""):
+def run(N, H, W, Cin, Cout, iters=20, tag="", bias=True):
     dev = torch.device("cuda", 0)
     xs = [torch.randn((N, H, W, Cin), device=dev).bfloat16() for _ in range(3)]
     gs = [torch.randn((N, H, W, Cout), device=dev).bfloat16() for _ in range(3)]
     def f(i):
-        conv_tc.conv2d_wgrad_tc(xs[i % 3], gs[i % 3], (3, 3), stride=1)
+        conv_tc.conv2d_wgrad_tc(xs[i % 3], gs[i % 3], (3, 3), stride=1, need_bias_grad=bias)
     for i in range(3): f(i)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -28,8 +28,8 @@ if __name__ == "__main__":
     variants = [""] + sys.argv[1:]
     from optical_flow_b200 import _lib as L
     for env in variants:
-        opts = [o.partition("=") for o in env.split(",") if o]
+        opts = [o.partition("=") for o in env.split(",") if o and o != "NOBIAS"]
         for k, _, v in opts: L.check(L.load().of_set_option(k.encode(), (v or "1").encode()), "of_set_option")
         for s in shapes:
-            run(*s, tag=env or "default")
+            run(*s, tag=env or "default", bias="NOBIAS" not in env)
         for k, _, v in opts: L.load().of_set_option(k.encode(), None)

@@ -286,6 +286,40 @@ def test_tc_wgrad(cuda, cfg):
     assert rel_err(db, bt.grad.numpy()) <= 5e-5
 
 
+WGRAD_VARIANTS = [
+    {"OF_WG_BIAS_ONES_A": "1"},                         # bias gradient: ones as the A operand (round-1 form)
+    {"OF_WG_DYNAMIC": "1"},                             # K tiles claimed from per-job counters
+    {"OF_WG_DYNAMIC": "1", "OF_WG_CLAIM": "1"},
+    {"OF_WG_PAIR": "1", "OF_WG_PAIR_MIN": "1"},         # CTA pairs (cta_group::2) + one-CTA launch for the unpaired job
+    {"OF_WG_KOUTER": "1"},
+    {"OF_WG_TW": "8"},
+]
+
+
+@pytest.mark.parametrize("opts", WGRAD_VARIANTS, ids=lambda o: "+".join(sorted(o)))
+@pytest.mark.parametrize("cfg", [(1, 16, 48, 128, 3, 96, 1), (2, 24, 32, 160, 3, 128, 1), (2, 24, 32, 64, 3, 64, 1),
+                                 (1, 16, 32, 256, 3, 128, 1)])
+def test_tc_wgrad_variants(cuda, cfg, opts):
+    """The measured-and-not-default kernel variants of conv_tc_wgrad.cu stay correct (two launches in a row: the
+    dynamic mode's counter sets are reset by the kernel itself)."""
+    import contextlib
+    from optical_flow_b200 import conv_tc, _lib as L
+    N, H, W, Cin, K, Cout, s = cfg
+    x, w, b = make(cfg, 17)
+    xt, wt, bt = torch.tensor(x), torch.tensor(w, requires_grad=True), torch.tensor(b, requires_grad=True)
+    yt = T.conv2d_same(xt, wt, bt, s)
+    g = bf16_round(np.random.default_rng(18).standard_normal(tuple(yt.shape)).astype(np.float32))
+    yt.backward(torch.tensor(g))
+    xd, gd = torch.tensor(x, device=cuda).bfloat16(), torch.tensor(g, device=cuda).bfloat16()
+    with contextlib.ExitStack() as st:
+        for k, v in opts.items():
+            st.enter_context(L.option(k, v))
+        for _ in range(2):
+            dw, db = conv_tc.conv2d_wgrad_tc(xd, gd, (K, K), stride=s)
+            assert rel_err(dw, wt.grad.numpy()) <= 5e-5, rel_err(dw, wt.grad.numpy())
+            assert rel_err(db, bt.grad.numpy()) <= 5e-5
+
+
 def test_tc_wgrad_two_sources(cuda):
     from optical_flow_b200 import conv_tc
     r = np.random.default_rng(9)
