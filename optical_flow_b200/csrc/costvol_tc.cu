@@ -367,6 +367,8 @@ cvtc_fwd_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant_
       }
     }
   } else if (warp >= 6) {
+    // (a third TMEM accumulator in flight - 3 x 144 columns - was tried in round 2, call 60: 268.7 vs 269.0 us per step,
+    // no change; the kernel is bound by the MMAs of the banded formulation, not by the accumulator hand-over)
     // epilogue: row m of step i needs D[m][m + j], j = 0..6 - columns q*32 + lane + j of this warp's
     // 48-column slice; a 5-stage predicated shift network brings them to registers 0..6
     const int q = warp & 3;
