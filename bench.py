@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -698,22 +699,38 @@ def bench_train(args, dev, world, rank):
         u8 = ((b + means) * 255.0).round().clamp(0, 255).to(torch.uint8)                   # (B,H,W,6)
         fr = u8.view(B, H, W, 2, 3).permute(0, 3, 1, 2, 4).contiguous()                    # (B,2,H,W,3)
         h_frames.append(fr.cpu().pin_memory())
-    h_loss = torch.empty(1).pin_memory()
+    # every step's loss is copied to pinned host memory and read by the host; the read of step i happens after step
+    # i + 1 has been enqueued (the way a training loop logs its loss), so the GPU does not idle while the host waits
+    h_loss = torch.empty(2).pin_memory()
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    losses_seen = []
 
     def run_e2e(n):
         feed = HostFramePrefetcher((h_frames[i % nsets] for i in range(n)), dev, H, W, out=tr.graph_input())
+        pending = None
         for i, (d_in, release) in enumerate(feed):
             loss, _ = tr.train_step(d_in, i)
             release()
-            h_loss.copy_(loss.reshape(1), non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            h_loss[i % 2: i % 2 + 1].copy_(loss.reshape(1), non_blocking=True)
+            loss_ev[i % 2].record()
+            if pending is not None:
+                loss_ev[pending].synchronize()
+                losses_seen.append(float(h_loss[pending]))
+            pending = i % 2
+        if pending is not None:
+            loss_ev[pending].synchronize()
+            losses_seen.append(float(h_loss[pending]))
 
     run_e2e(2)
+    del losses_seen[:]
     ms_e = _timed(torch, dist, world, run_e2e, args.steps)
+    assert len(losses_seen) == args.steps and all(math.isfinite(v) for v in losses_seen), "e2e: a step's loss was not read"
+
     ck = clocks.stop()
     e2e = {"value": world * B / (ms_e / args.steps * 1e-3), "unit": "image-pairs/s",
            "h2d_bytes_per_step": h_frames[0].numel(), "d2h_bytes_per_step": 4,
-           "input": "pinned uint8 frame pairs (B,2,H,W,3) -> of_preprocess_batch -> train_step"}
+           "input": "pinned uint8 frame pairs (B,2,H,W,3) -> of_preprocess_batch -> train_step; every step's loss read "
+                    "on the host one step behind (asynchronously)"}
     flops = conv_flops(B, H, W)
     tc_flops = conv_flops(B, H, W, tc_only=True)
     step_tf = (tc_flops if args.conv_mode == "bf16" else flops) / (per * 1e-3) / 1e12
