@@ -15,9 +15,18 @@
 #define HD_SEG 64
 #define HD_WARPS 8
 #define HD_CTAS_PER_SM 6
+// Occupancy / prefetch-depth A/B (round 2, call 64; level 3 = 8 x 192 x 640 x 32 bf16, us): default (122 registers,
+// 2 CTAs per SM, 4 pixels ahead) 195 | HD_MINB 3 (80 registers + spills) 266 | HD_MINB 4 477 | HD_PF 8 (162 registers) 254
+// | HD_MINB 3 + HD_PF 8 406 | HD_PF 2 + HD_MINB 4 342.  The defaults stay.
+#ifndef HD_MINB
+#define HD_MINB 1          // __launch_bounds__ minimum CTAs per SM
+#endif
+#ifndef HD_PF
+#define HD_PF 4            // pixels whose loads are issued up front per iteration
+#endif
 
 template <typename TX>
-__global__ void __launch_bounds__(HD_WARPS * 32)
+__global__ void __launch_bounds__(HD_WARPS * 32, HD_MINB)
 flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ w,
                      float* __restrict__ dw, float* __restrict__ db, TX* __restrict__ dz, int N, int H, int W, int Cin,
                      int act) {
@@ -50,18 +59,18 @@ flow_head_bwd_kernel(const TX* __restrict__ x, const float* __restrict__ dy, con
     }
     // 4 pixels per iteration: their 12 window columns and 4 activations are loaded up front (16 independent
     // loads in flight per warp), then consumed in order - the walk is latency-bound otherwise
-    for (int q0 = x0; q0 < x1; q0 += 4) {
-      float2 cn[4][3];
-      float xin[4];
+    for (int q0 = x0; q0 < x1; q0 += HD_PF) {
+      float2 cn[HD_PF][3];
+      float xin[HD_PF];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
+      for (int k = 0; k < HD_PF; ++k) {
 #pragma unroll
         for (int rr = 0; rr < 3; ++rr)
           cn[k][rr] = (row_ok[rr] && q0 + k + 1 < W) ? __ldg(dy2 + rowbase[rr] + q0 + k + 1) : make_float2(0.f, 0.f);
         xin[k] = (ch_ok && q0 + k < x1) ? ld_f<TX>(x + (rowbase[1] + q0 + k) * Cin + ci) : 0.f;
       }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
+      for (int k = 0; k < HD_PF; ++k) {
         const int q = q0 + k;
         if (q < x1) {                                   // warp-uniform
 #pragma unroll
