@@ -253,7 +253,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="train", choices=["train", "loss", "kernels"])
-    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32", "bf16x3"])
     ap.add_argument("--batch", type=int, default=B_PER_GPU)
     ap.add_argument("--height", type=int, default=H_FULL)
     ap.add_argument("--width", type=int, default=W_FULL)
@@ -801,7 +801,8 @@ def bench_train(args, dev, world, rank):
     line = {"metric": train_metric(H, W), "value": value, "unit": "image-pairs/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": per,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
-            "dtype": "bf16" if args.conv_mode == "bf16" else "f32", "data": "synthetic",
+            "dtype": {"bf16": "bf16", "bf16x3": "bf16x3 (fp32 storage; three bf16 tensor-core passes per conv)"}.get(args.conv_mode, "f32"),
+            "data": "synthetic",
             "config": dict(train_config(B, H, W, world, args.conv_mode, args.scaling), launch=launch_mode),
             "roofline": roof, "e2e": e2e, "gpu_launches": launches if launches else None, "clocks": ck}
     if dist_stats is not None:

@@ -271,6 +271,11 @@ int of_scatter_upsample2(const void* dy, void* out, int N, int Ho, int Wo, int H
 /* db[c] = sum over pixels of dy[p, c] (dy has pixel stride dy_stride) */
 int of_colsum(const void* dy, float* db, size_t npix, int C, int dy_stride, int dtype, void* stream);
 
+/* conv_mode "bf16x3" (tensor-core parity mode; stands where SURVEY 7 step 7 planned a tf32 mode for the fp32 convolutions of
+ * model.py:12-15,104-114): v = hi + lo with hi = bf16(v), lo = bf16(v - hi); pixels of C channels written with pixel stride
+ * C_pad (padding channels zero); out_dtype OF_BF16 (operands) or OF_F32 (weights, bf16-representable values). */
+int of_split_bf16(const float* src, void* hi, void* lo, size_t npix, int C, int C_pad, int out_dtype, void* stream);
+
 /* dz = dy * act'(y)  (y = stored activation output) */
 int of_act_bwd(const void* y, const void* dy, void* dz, size_t n, int act, int dtype, void* stream);
 /* the same from a sign-bit mask (of_tc_conv.sign_out: 16 bytes per pixel, bit c = activated channel c > 0) instead

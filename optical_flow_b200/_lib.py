@@ -131,6 +131,7 @@ PROTOTYPES = {
     "of_relu_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "of_act_bwd": (_i, [_vp, _vp, _vp, _sz, _i, _i, _vp]),
     "of_act_bwd_bits": (_i, [_vp, _vp, _vp, _sz, _i, _i, _i, _vp]),
+    "of_split_bf16": (_i, [_vp, _vp, _vp, _sz, _i, _i, _i, _vp]),
     "of_conv2d_fprop": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_conv2d_dgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "of_conv2d_wgrad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -460,3 +460,95 @@ class Bf16Backend:
             L.check(L.load().of_copy_channels(d_cvflow.data_ptr() + fm.ncv * 2, 64, L.ptr(d_flow_up), 2, 2, B * h * w,
                                               L.OF_BF16, L.OF_F32, 0, L.stream_ptr()), "of_copy_channels")
         return d_f1, d_f2w, d_flow_up
+
+
+# ------------------------------------------------------------------ tensor-core parity mode --
+
+def split_bf16(t, pad_to=8, as_f32=False):
+    """(hi, lo) with t = hi + lo + O(2^-16 |t|); the last dimension is padded with zeros to a multiple of ``pad_to``
+    (TMA needs 16-byte pixel strides).  bf16 tensors (operands), or fp32 tensors holding bf16 values (weights)."""
+    assert t.dtype == torch.float32 and t.is_contiguous()
+    C = t.shape[-1]
+    Cp = _ceil(C, pad_to)
+    dt = torch.float32 if as_f32 else torch.bfloat16
+    hi = torch.empty(tuple(t.shape[:-1]) + (Cp,), dtype=dt, device=t.device)
+    lo = torch.empty_like(hi)
+    L.check(L.load().of_split_bf16(L.ptr(t), L.ptr(hi), L.ptr(lo), t.numel() // C, C, Cp, L.dtype_code(hi), L.stream_ptr()),
+            "of_split_bf16")
+    return hi, lo
+
+
+class Bf16x3Backend:
+    """conv_mode="bf16x3": the fp32 convolutions of the reference (layers.Conv2D, model.py:12-15,104-114;
+    resnet/models.py:17-34) on the tensor cores at fp32-class accuracy.  Storage stays fp32 (every non-conv kernel is
+    the fp32 mode's); a convolution splits both operands into bf16 hi + lo parts and runs THREE passes of the bf16
+    tcgen05 kernels with fp32 accumulation chained through the epilogue's add input:
+        x * w  ~  x_hi * w_hi + x_hi * w_lo + x_lo * w_hi        (the dropped lo * lo term is 2^-16 relative)
+    - closer to fp32 than a tf32 mode would be (tf32 keeps 10 mantissa bits, hi + lo keeps 16), with the kernels the
+    bf16 mode has already validated.  The stem (Cin = 3) and the flow heads (Cout = 2) use the SIMT fp32 kernels."""
+    act_dtype = torch.float32
+
+    def __init__(self, net):
+        self.net = net
+
+    @staticmethod
+    def _tc_ok(layer):
+        return layer.cin >= 32 and layer.cout >= 16 and layer.cout % 8 == 0
+
+    @staticmethod
+    def _src(t, valid):
+        return MultiSource([Source(t, valid, 0)])
+
+    def fprop(self, layer, x, w, b):
+        if not self._tc_ok(layer):
+            return F.conv2d_fprop(x, w, b, stride=layer.stride, act=layer.act, out_dtype=torch.float32)
+        xh, xl = split_bf16(x)
+        wh, wl = split_bf16(w, pad_to=1, as_f32=True)
+        cin = layer.cin
+        y = conv2d_fprop_tc(self._src(xh, cin), wh, b, stride=layer.stride, out_dtype=torch.float32)
+        y = conv2d_fprop_tc(self._src(xh, cin), wl, None, stride=layer.stride, out_dtype=torch.float32, add=y)
+        return conv2d_fprop_tc(self._src(xl, cin), wh, None, stride=layer.stride, act=layer.act, out_dtype=torch.float32, add=y)
+
+    def act_bwd(self, layer, y, dy):
+        if layer.act == L.OF_ACT_NONE:
+            return dy
+        return F.act_bwd(y, dy, layer.act)
+
+    def wgrad(self, layer, x, dz, dw, db):
+        if not self._tc_ok(layer):
+            F.conv2d_wgrad(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
+            return
+        from .model import _accumulate
+        xh, xl = split_bf16(x)
+        zh, zl = split_bf16(dz)
+        ks, cin = (layer.k, layer.k), layer.cin
+        conv2d_wgrad_tc(self._src(xh, cin), zh, ks, stride=layer.stride, dw=dw, need_bias_grad=False)
+        for a, g in ((xh, zl), (xl, zh)):
+            part, _ = conv2d_wgrad_tc(self._src(a, cin), g, ks, stride=layer.stride, need_bias_grad=False)
+            _accumulate(dw, part)
+        if db is not None:
+            N, Ho, Wo, Cout = dz.shape
+            L.check(L.load().of_colsum(L.ptr(dz), L.ptr(db), N * Ho * Wo, Cout, Cout, L.dtype_code(dz), L.stream_ptr()),
+                    "of_colsum")
+
+    def dgrad(self, layer, dz, w, in_hw, chain=None):
+        if not self._tc_ok(layer):
+            return F.conv2d_dgrad(dz, w, in_hw, stride=layer.stride, out_dtype=torch.float32)
+        zh, zl = split_bf16(dz)
+        wh, wl = split_bf16(w, pad_to=1, as_f32=True)
+        cin = layer.cin
+        from .model import _copy_channels
+        out = None
+        for c0 in range(0, cin, 256):                    # the kernels write at most 256 output channels per launch
+            cnt = min(256, cin - c0)
+            cp = _ceil(cnt, 8)
+            kw = dict(stride=layer.stride, seg=(c0, cnt), out_dtype=torch.float32, out_channels=cp)
+            dx = conv2d_dgrad_tc(zh, wh, in_hw, **kw)
+            dx = conv2d_dgrad_tc(zh, wl, in_hw, add=dx, **kw)
+            dx = conv2d_dgrad_tc(zl, wh, in_hw, add=dx, **kw)
+            if c0 == 0 and cnt == cin and cp == cin:
+                return dx
+            if out is None:
+                out = torch.empty(tuple(dx.shape[:3]) + (cin,), dtype=torch.float32, device=dx.device)
+            _copy_channels(dx, 0, out, c0, cnt)
+        return out

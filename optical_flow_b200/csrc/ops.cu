@@ -206,6 +206,28 @@ __global__ void __launch_bounds__(256) maxpool2_bwd_add_act8_kernel(const __nv_b
   }
 }
 
+// ---- bf16 hi / lo split (conv_mode "bf16x3") ----------------------------------------------------------------------
+// v = hi + lo + O(2^-16 |v|): hi = bf16(v), lo = bf16(v - hi).  Pixels of C channels are written with pixel stride C_pad
+// (>= C, padding channels zero).  OUT = __nv_bfloat16 (activations / gradients, the tensor-core operands) or float
+// (weights: values already bf16-representable, packed by of_conv_tc_pack_weights without further rounding).
+template <typename OUT>
+__global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ src, OUT* __restrict__ hi,
+                                                         OUT* __restrict__ lo, size_t npix, int C, int C_pad) {
+  const size_t total = npix * (size_t)C_pad;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t pix = e / C_pad;
+    const int c = (int)(e - pix * C_pad);
+    float h = 0.f, l = 0.f;
+    if (c < C) {
+      const float v = src[pix * C + c];
+      h = __bfloat162float(__float2bfloat16_rn(v));
+      l = __bfloat162float(__float2bfloat16_rn(v - h));
+    }
+    if constexpr (sizeof(OUT) == 2) { hi[e] = __float2bfloat16_rn(h); lo[e] = __float2bfloat16_rn(l); }
+    else { hi[e] = h; lo[e] = l; }
+  }
+}
+
 // ---- elementwise -------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) add_relu_kernel(const T* __restrict__ a, const T* __restrict__ b,
@@ -401,6 +423,18 @@ int of_maxpool2_bwd_add_act(const void* in, const void* d_out, const void* add, 
     maxpool2_bwd_add_act_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)in, (const __nv_bfloat16*)d_out, (const __nv_bfloat16*)add, (__nv_bfloat16*)dz, B, H, W, C, act);
   return of_launch_check("maxpool2_bwd_add_act");
+}
+
+int of_split_bf16(const float* src, void* hi, void* lo, size_t npix, int C, int C_pad, int out_dtype, void* stream) {
+  OF_REQUIRE(src && hi && lo, OF_ERR_ARG, "null pointer argument");
+  OF_REQUIRE(of_valid_dtype(out_dtype) && npix > 0 && C > 0 && C_pad >= C, OF_ERR_ARG, "bad split arguments");
+  const size_t total = npix * (size_t)C_pad;
+  if (out_dtype == OF_F32)
+    split_bf16_kernel<float><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, (float*)hi, (float*)lo, npix, C, C_pad);
+  else
+    split_bf16_kernel<__nv_bfloat16><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)hi,
+                                                                                      (__nv_bfloat16*)lo, npix, C, C_pad);
+  return of_launch_check("split_bf16_kernel");
 }
 
 int of_add_relu_fwd(const void* a, const void* b, void* out, size_t n, int dtype, void* stream) {

@@ -15,6 +15,7 @@ order, leaving d loss / d weight in ``net.store.grad`` (one flat fp32 buffer).
 Two convolution back-ends share this graph:
   conv_mode="fp32"  SIMT fp32 implicit GEMM - exact-parity mode (<= 1e-5 vs oracle)
   conv_mode="bf16"  tcgen05/TMEM implicit GEMM, bf16 operands, fp32 accumulate
+  conv_mode="bf16x3" tensor-core parity mode: fp32 storage, every conv as three bf16 tcgen05 passes (hi / lo split operands)
 """
 from __future__ import annotations
 
@@ -435,8 +436,11 @@ class FlowNet:
         elif conv_mode == "bf16":
             from .conv_tc import Bf16Backend
             self.backend = Bf16Backend(self)
+        elif conv_mode == "bf16x3":
+            from .conv_tc import Bf16x3Backend
+            self.backend = Bf16x3Backend(self)
         else:
-            raise AssertionError("conv_mode must be 'fp32' or 'bf16'")
+            raise AssertionError("conv_mode must be 'fp32', 'bf16' or 'bf16x3'")
         self.encoder = Encoder(self)
         self.flow_modules = [FlowModule(self, lvl) for lvl in range(4)]
         if pretrained_weights_path is not None:

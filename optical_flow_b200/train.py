@@ -305,7 +305,7 @@ def main(argv=None):
     ap.add_argument("--batch-size", type=int, default=batch_size)
     ap.add_argument("--epochs", type=int, default=nepochs)
     ap.add_argument("--batches-per-epoch", type=int, default=50)
-    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--conv-mode", default="bf16", choices=["bf16", "fp32", "bf16x3"])
     ap.add_argument("--warp-mode", default="ref_ij", choices=["ref_ij", "xy"])
     ap.add_argument("--save-dir", default="ckpts")
     args = ap.parse_args(argv)
