@@ -120,19 +120,27 @@ def test_loss_layer_oracle_at_bench_shape(cuda, B, H, W, flows_kind):
 
 
 # ------------------------------------------------------------------ (ii) fp32 step vs the oracle --
-def test_fp32_step_oracle_at_384x1280(cuda):
-    from optical_flow_b200.loss import LossLayer
-    from optical_flow_b200.model import build_flow_net
+@pytest.fixture(scope="module")
+def oracle_step_384x1280():
     B, H, W = 1, 384, 1280
     params, stats = T.init_params(seed=42, randomize_bn=True)
     imgs = T.synthetic_pairs(B, H, W, seed=21)
-    r_loss, r_flows, r_grads = T.FlowNetRef(params, stats).loss_and_grads(torch.tensor(imgs))
-    net = build_flow_net(H, W, None, conv_mode="fp32")
+    return (params, stats, imgs) + tuple(T.FlowNetRef(params, stats).loss_and_grads(torch.tensor(imgs)))
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16x3"])
+def test_fp32_step_oracle_at_384x1280(cuda, oracle_step_384x1280, mode):
+    """The fp32-accurate modes (SIMT fp32; tensor-core parity mode bf16x3) against the oracle at the benchmark resolution."""
+    from optical_flow_b200.loss import LossLayer
+    from optical_flow_b200.model import build_flow_net
+    B, H, W = 1, 384, 1280
+    params, stats, imgs, r_loss, r_flows, r_grads = oracle_step_384x1280
+    net = build_flow_net(H, W, None, conv_mode=mode)
     net.store.load_numpy(params, stats)
     x = torch.tensor(imgs, device=cuda)
     flows = net(x)
     for k, (f, e) in enumerate(zip(flows, r_flows)):
-        assert rel_err(f, e) < 1e-4, "flow %d: %g" % (k, rel_err(f, e))
+        assert rel_err(f, e) < (1e-4 if mode == "fp32" else 5e-4), "flow %d: %g" % (k, rel_err(f, e))
     layer = LossLayer()
     loss = layer(x, flows)
     assert abs(loss.item() - r_loss.item()) < 1e-4 * abs(r_loss.item())
@@ -143,10 +151,17 @@ def test_fp32_step_oracle_at_384x1280(cuda):
         if float(e.norm()) == 0:
             continue
         rows[name] = rel_l2(gt, e)
-    record("fp32_step_384x1280", {"loss": loss.item(), "ref_loss": r_loss.item(), "rel_l2": rows})
+    record("%s_step_384x1280" % mode, {"loss": loss.item(), "ref_loss": r_loss.item(), "rel_l2": rows})
     # a warp index flips where an fp32-noisy flow crosses an integer (isolated pixels); relative L2 per tensor
     worst = max(rows.items(), key=lambda kv: kv[1])
-    assert worst[1] < 1e-3, worst          # measured on B200: worst 1.1e-4 (flow1_conv3/kernel)
+    med = float(np.median(list(rows.values())))
+    if mode == "fp32":
+        assert worst[1] < 1e-3, worst      # measured on B200: worst 1.1e-4 (flow1_conv3/kernel), median 1.8e-5
+    else:
+        # hi + lo bf16 operands carry 16-17 mantissa bits (fp32: 24, tf32: 11): ~5e-6 per convolution, amplified through
+        # 40 layers and the sign() / floor() decisions of loss.py:28 and the warp.  Measured on B200: loss 2e-6 off,
+        # worst tensor 2.0e-3 (flow0_conv2/kernel), median 4.5e-4 - against 2.4e-2 / 1.1e-2 for the bf16 mode
+        assert worst[1] < 5e-3 and med < 1e-3, (worst, med)
 
 
 # ------------------------------------------------------------------ (iii) bf16 vs fp32 mode --
