@@ -510,3 +510,33 @@ def test_maxpool2_bwd_add_act_equals_three_passes(cuda, dtype):
     fused = F.maxpool2_bwd_add_act(x, d, add, L.OF_ACT_RELU)
     ref = (F.maxpool2_bwd(x, d).float() + add.float()) * (x.float() > 0)
     assert torch.equal(fused.float(), ref.to(dtype).float())
+
+
+# ------------------------------------------------------------------ bf16 streaming kernels, 16-byte paths --
+@pytest.mark.parametrize("shape", [(2, 12, 20, 64), (1, 6, 10, 24), (1, 4, 6, 12)])    # C % 8 == 0 twice, C % 8 != 0 once
+def test_bf16_streaming_kernels_16_byte_paths(cuda, shape):
+    """MaxPool2D forward, add + ReLU, activation backward and the stride-2 zero-insertion scatter on bf16 tensors:
+    the 16-byte (8-channel) kernels against torch on the same bf16 values (exact: max / select / one rounded add)."""
+    from optical_flow_b200 import functional as F, _lib as L
+    from optical_flow_b200.conv_tc import PackCache, zero_upsample2
+    B, H, W, C = shape
+    g = torch.Generator(device="cpu").manual_seed(3)
+    x = torch.randn(shape, generator=g).to(cuda).bfloat16()
+    y = torch.randn(shape, generator=g).to(cuda).bfloat16()
+    mp = F.maxpool2_fwd(x)
+    exp = torch.nn.functional.max_pool2d(x.float().permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1).bfloat16()
+    assert torch.equal(mp, exp)
+    ar = F.add_relu_fwd(x, y)
+    assert torch.equal(ar, torch.relu(x.float() + y.float()).bfloat16())
+    for act, slope in ((L.OF_ACT_RELU, 0.0), (L.OF_ACT_LEAKY, 0.3)):
+        dz = F.act_bwd(x, y, act)
+        exp = (y.float() * torch.where(x.float() > 0, torch.ones_like(x.float()), torch.full_like(x.float(), slope))).bfloat16()
+        assert torch.equal(dz, exp)
+    cache = PackCache()
+    up = zero_upsample2(x, 2 * H, 2 * W, cache=cache, key=1)
+    exp = torch.zeros((B, 2 * H, 2 * W, C), dtype=torch.bfloat16, device=cuda)
+    exp[:, ::2, ::2] = x
+    assert torch.equal(up, exp)
+    up2 = zero_upsample2(y, 2 * H, 2 * W, cache=cache, key=1)          # the cached buffer: only the quarter is rewritten
+    exp[:, ::2, ::2] = y
+    assert up2.data_ptr() == up.data_ptr() and torch.equal(up2, exp)
