@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2: 16-byte bf16 paths of maxpool forward / add+relu / act backward / zero-insertion scatter: tests + step A/B is by timeline
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_b1_gpu_ops.py -m gpu -x -q -k "streaming or maxpool or relu or act" 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_b1_gpu_ops.py tests/test_b3_gpu_net.py -m gpu -x -q -k "streaming or maxpool or relu or act or pool" 2>&1 | tail -3
 timeout 300 python bench.py --no-cpu-baseline --dump-timeline gpurun_out/r2_timeline_52.json > gpurun_out/r2_bench_52.json 2> gpurun_out/r2_bench_52.err
 python - <<'PY'
 import json, collections
