@@ -499,11 +499,23 @@ class Bf16x3Backend:
     def _src(t, valid):
         return MultiSource([Source(t, valid, 0)])
 
+    # Splits are shared inside a step: fprop's split of its input and of the weights serves the layer's wgrad / dgrad (same
+    # tensors, refreshed by every fprop), wgrad's split of dz serves the dgrad that follows it.
+    @staticmethod
+    def _cached(layer, slot, t, make):
+        c = getattr(layer, slot, None)
+        if c is not None and c[0] == t.data_ptr() and c[1] == tuple(t.shape):
+            return c[2]
+        v = make()
+        setattr(layer, slot, (t.data_ptr(), tuple(t.shape), v))
+        return v
+
     def fprop(self, layer, x, w, b):
         if not self._tc_ok(layer):
             return F.conv2d_fprop(x, w, b, stride=layer.stride, act=layer.act, out_dtype=torch.float32)
-        xh, xl = split_bf16(x)
-        wh, wl = split_bf16(w, pad_to=1, as_f32=True)
+        layer._x3 = layer._w3 = layer._dz3 = None
+        xh, xl = self._cached(layer, "_x3", x, lambda: split_bf16(x))
+        wh, wl = self._cached(layer, "_w3", w, lambda: split_bf16(w, pad_to=1, as_f32=True))
         cin = layer.cin
         y = conv2d_fprop_tc(self._src(xh, cin), wh, b, stride=layer.stride, out_dtype=torch.float32)
         y = conv2d_fprop_tc(self._src(xh, cin), wl, None, stride=layer.stride, out_dtype=torch.float32, add=y)
@@ -519,8 +531,9 @@ class Bf16x3Backend:
             F.conv2d_wgrad(x, dz, (layer.k, layer.k), stride=layer.stride, dw=dw, db=db, need_bias_grad=db is not None)
             return
         from .model import _accumulate
-        xh, xl = split_bf16(x)
-        zh, zl = split_bf16(dz)
+        xh, xl = self._cached(layer, "_x3", x, lambda: split_bf16(x))
+        zh, zl = self._cached(layer, "_dz3", dz, lambda: split_bf16(dz))
+        layer._x3 = None                                   # last use of the input's split
         ks, cin = (layer.k, layer.k), layer.cin
         conv2d_wgrad_tc(self._src(xh, cin), zh, ks, stride=layer.stride, dw=dw, need_bias_grad=False)
         for a, g in ((xh, zl), (xl, zh)):
@@ -534,8 +547,9 @@ class Bf16x3Backend:
     def dgrad(self, layer, dz, w, in_hw, chain=None):
         if not self._tc_ok(layer):
             return F.conv2d_dgrad(dz, w, in_hw, stride=layer.stride, out_dtype=torch.float32)
-        zh, zl = split_bf16(dz)
-        wh, wl = split_bf16(w, pad_to=1, as_f32=True)
+        zh, zl = self._cached(layer, "_dz3", dz, lambda: split_bf16(dz))
+        wh, wl = self._cached(layer, "_w3", w, lambda: split_bf16(w, pad_to=1, as_f32=True))
+        layer._dz3 = layer._w3 = None                      # last uses
         cin = layer.cin
         from .model import _copy_channels
         out = None

@@ -249,6 +249,24 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict
   }
 }
 
+// unpadded tensors (C_pad == C), 4 elements per thread: 16-byte loads, 8-byte bf16 / 16-byte fp32 stores
+template <typename OUT>
+__global__ void __launch_bounds__(256) split_bf16_flat4_kernel(const float* __restrict__ src, OUT* __restrict__ hi,
+                                                               OUT* __restrict__ lo, size_t n4) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n4; e += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(src) + e);
+    const float vv[4] = {v.x, v.y, v.z, v.w};
+    float h[4], l[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      h[k] = __bfloat162float(__float2bfloat16_rn(vv[k]));
+      l[k] = __bfloat162float(__float2bfloat16_rn(vv[k] - h[k]));
+    }
+    st4<OUT>(hi + e * 4, make_float4(h[0], h[1], h[2], h[3]));
+    st4<OUT>(lo + e * 4, make_float4(l[0], l[1], l[2], l[3]));
+  }
+}
+
 // ---- elementwise -------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) add_relu_kernel(const T* __restrict__ a, const T* __restrict__ b,
@@ -475,6 +493,14 @@ int of_split_bf16(const float* src, void* hi, void* lo, size_t npix, int C, int 
   OF_REQUIRE(src && hi && lo, OF_ERR_ARG, "null pointer argument");
   OF_REQUIRE(of_valid_dtype(out_dtype) && npix > 0 && C > 0 && C_pad >= C, OF_ERR_ARG, "bad split arguments");
   const size_t total = npix * (size_t)C_pad;
+  if (C_pad == C && total % 4 == 0 && (((uintptr_t)src | (uintptr_t)hi | (uintptr_t)lo) & 15) == 0) {
+    if (out_dtype == OF_F32)
+      split_bf16_flat4_kernel<float><<<ew_grid(total / 4), 256, 0, (cudaStream_t)stream>>>(src, (float*)hi, (float*)lo, total / 4);
+    else
+      split_bf16_flat4_kernel<__nv_bfloat16><<<ew_grid(total / 4), 256, 0, (cudaStream_t)stream>>>(
+          src, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, total / 4);
+    return of_launch_check("split_bf16_kernel");
+  }
   if (out_dtype == OF_F32)
     split_bf16_kernel<float><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, (float*)hi, (float*)lo, npix, C, C_pad);
   else
