@@ -63,7 +63,10 @@ struct Conv3Params {
 //   (add_mode 1);  always: bf16 output, full 16-channel chunks, 32-byte aligned rows
 #define T3_SPEC(act, add, sign, mkind, mact, split) ((act) | ((add) << 2) | ((sign) << 3) | ((mkind) << 4) | ((mact) << 6) | ((split) << 8))
 #define T3_SPEC_POST (1 << 9)
-template <bool COAL, int MINB = 1, int SPEC = -1>
+// KS: K steps (16 channels each) issued per 64-channel chunk.  4 by default; 2 for a single source of <= 32 channels (the
+// Cout = 2 flow heads' fprop and the dgrad of the 64->32 layers): the upper half of the chunk is TMA zero fill, and a
+// compile-time count costs the issuing thread nothing (the run-time skip of round 2 made every layer 6-15 % slower).
+template <bool COAL, int MINB = 1, int SPEC = -1, int KS = 4>
 __global__ void __launch_bounds__(T3_THREADS, MINB)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ Conv3Params P) {
@@ -201,7 +204,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             for (int hh = 0; hh < 2; ++hh) {
               const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
+              for (int k = 0; k < KS; ++k)
                 tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
                              (sl | kh | k) ? 1u : 0u);
             }
@@ -655,6 +658,9 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, S_FL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, -1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, -1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S_DML, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
 #define T3_ATTR(S) OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
     T3_ATTR(S_FL); T3_ATTR(S_FR); T3_ATTR(S_DML); T3_ATTR(S_DMR); T3_ATTR(S_DA); T3_ATTR(S_D0); T3_ATTR(S_DS);
     T3_ATTR(S_FRP); T3_ATTR(S_DAMR); T3_ATTR(S_FL0); T3_ATTR(S_FR0);
@@ -663,8 +669,15 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   }
   int grid = P.m_tiles < OF_NUM_SMS ? P.m_tiles : OF_NUM_SMS;
 #define T3_GO(MINB_, S) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, MINB_, S>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P))
+  if (two) grid = P.m_tiles < 2 * OF_NUM_SMS ? P.m_tiles : 2 * OF_NUM_SMS;
+  // half-K variants (KS = 2): one source of <= 32 channels
+  const bool half_k = c->num_src == 1 && c->src_c[0] <= 32 && !P.coal && !of_tune_env("OF_T3_NO_HALFK");
+#define T3_GOK(MINB_, S) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, MINB_, S, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P))
+  if (half_k && two && spec != S_FL) T3_GOK(2, -1);
+  else if (half_k && !two && spec == S_DML) T3_GOK(1, S_DML);
+  else if (half_k && !two && spec == -1) T3_GOK(1, -1);
+  else
   if (two) {
-    grid = P.m_tiles < 2 * OF_NUM_SMS ? P.m_tiles : 2 * OF_NUM_SMS;
     if (spec == S_FL) T3_GO(2, S_FL);
     else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   } else
@@ -682,6 +695,7 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   else if (spec == S_DAMR) T3_GO(1, S_DAMR);
   else OF_CUDA(of_launch_pdl(conv_tc3_kernel<false>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
 #undef T3_GO
+#undef T3_GOK
   if (int r = of_launch_check(c->n_valid < 16 ? "conv_tc3_kernel<head>" : "conv_tc3_kernel")) return r;   // Cout = 2 flow heads apart
   return 1;
 }
