@@ -66,6 +66,8 @@ struct Conv3Params {
 // KS: K steps (16 channels each) issued per 64-channel chunk.  4 by default; 2 for a single source of <= 32 channels (the
 // Cout = 2 flow heads' fprop and the dgrad of the 64->32 layers): the upper half of the chunk is TMA zero fill, and a
 // compile-time count costs the issuing thread nothing (the run-time skip of round 2 made every layer 6-15 % slower).
+// KS = 42: 4 per chunk and 2 on the last chunk of a single source with 96 (160, ...) channels - compiled only into the
+// two specialisations those layers use (fprop 96->64, dgrad of 128->96).
 template <bool COAL, int MINB = 1, int SPEC = -1, int KS = 4>
 __global__ void __launch_bounds__(T3_THREADS, MINB)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -156,6 +158,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     //  instruction stream made every layer 6-15 % slower - the issuing thread is on the critical path)
     if (OF_ONE_LANE()) {
       const uint32_t idesc = tc::idesc_bf16_f32(128, P.n_mma, 0, 0);
+      constexpr bool LH = (KS == 42);                    // 4 K steps per chunk, 2 on the slabs of the last chunk
+      constexpr int KSN = LH ? 4 : KS;
       const int slabs_per_tile = 3 * (P.kchunks[0] + (P.num_src > 1 ? P.kchunks[1] : 0));
       int as = 0, bs = 0; uint32_t aph = 0, bph = 0;
       int it = 0;
@@ -184,12 +188,9 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               for (int k = 0; k < 4; ++k)
                 tc::mma_bf16(tmem_base + (uint32_t)(buf * 256), bdesc + (uint64_t)(2 * k), pdesc + (uint64_t)(2 * k), idesc_sw,
                              (sl | kh | k) ? 1u : 0u);
-            } else
-#pragma unroll
-#ifdef T3_KSKIP
-            // the LAST 64-channel chunk of a single-source layer whose channel count is 32 or 96 (mod 64) holds zeros in
-            // its upper K steps (TMA zero fill): a separate, equally unrolled path issues only the real ones
-            if (sl >= P.klast_slab) {
+            } else if (LH && sl >= P.klast_slab) {
+              // KS == 42: the LAST 64-channel chunk of a single source with 32 channels (mod 64) holds zeros in its upper
+              // K steps (TMA zero fill): its slabs issue only the two real ones
 #pragma unroll
               for (int hh = 0; hh < 2; ++hh) {
                 const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
@@ -198,15 +199,15 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                   tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
                                (sl | kh | k) ? 1u : 0u);
               }
-            } else
-#endif
+            } else {
 #pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-              const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
+              for (int hh = 0; hh < 2; ++hh) {
+                const uint64_t adesc = tc::desc_sw128_kmajor(slab + (uint32_t)((tap_row + hh * P.TH) * P.TW * 128));
 #pragma unroll
-              for (int k = 0; k < KS; ++k)
-                tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                             (sl | kh | k) ? 1u : 0u);
+                for (int k = 0; k < KSN; ++k)
+                  tc::mma_bf16(d0 + (uint32_t)(hh * P.n_mma), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                               (sl | kh | k) ? 1u : 0u);
+              }
             }
             tc::mma_commit(&b_empty[bs]);
             if (++bs == P.nb) { bs = 0; bph ^= 1; }
@@ -661,6 +662,8 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 2, -1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, -1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S_DML, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S_FL, 42>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S_DML, 42>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
 #define T3_ATTR(S) OF_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<false, 1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
     T3_ATTR(S_FL); T3_ATTR(S_FR); T3_ATTR(S_DML); T3_ATTR(S_DMR); T3_ATTR(S_DA); T3_ATTR(S_D0); T3_ATTR(S_DS);
     T3_ATTR(S_FRP); T3_ATTR(S_DAMR); T3_ATTR(S_FL0); T3_ATTR(S_FR0);
@@ -672,10 +675,13 @@ int of_conv_tc3_try(const of_tc_conv* c, void* stream) {
   if (two) grid = P.m_tiles < 2 * OF_NUM_SMS ? P.m_tiles : 2 * OF_NUM_SMS;
   // half-K variants (KS = 2): one source of <= 32 channels
   const bool half_k = c->num_src == 1 && c->src_c[0] <= 32 && !P.coal && !of_tune_env("OF_T3_NO_HALFK");
+  const bool last_half = P.klast_n == 2 && P.kchunks[0] >= 2 && !P.coal && !of_tune_env("OF_T3_NO_HALFK");
 #define T3_GOK(MINB_, S) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, MINB_, S, 2>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P))
   if (half_k && two && spec != S_FL) T3_GOK(2, -1);
   else if (half_k && !two && spec == S_DML) T3_GOK(1, S_DML);
   else if (half_k && !two && spec == -1) T3_GOK(1, -1);
+  else if (last_half && !two && spec == S_FL) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 1, S_FL, 42>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
+  else if (last_half && !two && spec == S_DML) OF_CUDA(of_launch_pdl(conv_tc3_kernel<false, 1, S_DML, 42>, dim3(grid), dim3(T3_THREADS), smem, (cudaStream_t)stream, tmA[0], tmA[1], tmB, P));
   else
   if (two) {
     if (spec == S_FL) T3_GO(2, S_FL);
