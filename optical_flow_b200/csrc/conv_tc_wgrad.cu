@@ -10,9 +10,10 @@
 // decoder concat), all Cout columns, a group of taps (one TMEM accumulator per tap: the dy
 // tile is loaded once per K step and reused by every tap) and a slice of the pixel range
 // (split-K).  Partial results are reduced into dW with red.global.add.f32.
-// Bias gradient (db[co] = sum_pix dy[pix][co]) rides along: one job per pixel range (rotating) issues one more MMA group
-// per K step whose A operand is a constant all-ones tile, into a spare TMEM accumulator - the dy tile
-// is already in shared memory, so the separate column-sum pass over dy (1.25 ms / step) disappears.
+// Bias gradient (db[co] = sum_pix dy[pix][co]) rides along: one job per K tile (rotating) issues one more MMA group
+// against a constant all-ones tile into a spare TMEM accumulator - the dy tile is already in shared memory, so the
+// separate column-sum pass over dy (1.25 ms / step) disappears.  Default form (round 2): TRANSPOSED - the dy tile is the
+// A operand (M = its channels), ones the B operand, N = 16; see of_conv_tc_wgrad for the measurements.
 #include "common.cuh"
 #include "tc_common.cuh"
 
